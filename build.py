@@ -1,0 +1,131 @@
+#!/usr/bin/env python
+"""Build libppb200.so (every sm_100a kernel of the framework) in-tree with nvcc.
+
+    python build.py            # incremental: only re-compiles .cu files newer than their .o
+    python build.py --force    # rebuild everything
+    python build.py --sass     # also dump cuobjdump -sass summaries into docs/sass/
+
+The library is plain C ABI (include/ppb200.h), has no dependency on libtorch, and is loaded by
+`ppb200.ops._lib` through ctypes.  nvcc cross-compiles for sm_100a without a GPU present.
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import os
+import shutil
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(ROOT, "csrc")
+OUT_DIR = os.path.join(ROOT, "distributed-training-with-pipeline-parallelism_b200", "ops")
+BUILD = os.path.join(ROOT, "build")
+LIB = os.path.join(OUT_DIR, "libppb200.so")
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "-Xcompiler", "-fPIC",
+    "--expt-relaxed-constexpr",
+    "-I", os.path.join(ROOT, "include"),
+    "-I", CSRC,
+]
+
+
+def nvcc_path() -> str:
+    p = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(p):
+        raise RuntimeError("nvcc not found")
+    return p
+
+
+def sources() -> list[str]:
+    return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
+
+
+def _deps_mtime() -> float:
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    hdrs.append(os.path.join(ROOT, "include", "ppb200.h"))
+    return max(os.path.getmtime(h) for h in hdrs)
+
+
+def compile_one(src: str, force: bool, verbose: bool) -> tuple[str, str]:
+    obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+    spath = os.path.join(CSRC, src)
+    if (not force and os.path.exists(obj)
+            and os.path.getmtime(obj) > max(os.path.getmtime(spath), _deps_mtime())):
+        return obj, ""
+    cmd = [nvcc_path(), *NVCC_FLAGS, "-Xptxas", "-v" if verbose else "-warn-spills", "-c", spath, "-o", obj]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+    return obj, r.stderr
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    os.makedirs(BUILD, exist_ok=True)
+    os.makedirs(OUT_DIR, exist_ok=True)
+    srcs = sources()
+    logs = []
+    with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        results = list(ex.map(lambda s: compile_one(s, force, verbose), srcs))
+    objs = [o for o, _ in results]
+    logs = [l for _, l in results if l]
+    newest_obj = max(os.path.getmtime(o) for o in objs)
+    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest_obj:
+        cmd = [nvcc_path(), "-shared", "-o", LIB, *objs, "-lcudart"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    if verbose:
+        print("\n".join(logs))
+    return LIB
+
+
+def dump_sass() -> None:
+    """Write per-kernel SASS opcode histograms + the tcgen05/TMA evidence lines to docs/sass/."""
+    out_dir = os.path.join(ROOT, "docs", "sass")
+    os.makedirs(out_dir, exist_ok=True)
+    r = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(r.stderr)
+    kernels: dict[str, dict[str, int]] = {}
+    cur = None
+    for line in r.stdout.splitlines():
+        line = line.strip()
+        if line.startswith("Function :"):
+            cur = line.split(":", 1)[1].strip()
+            kernels[cur] = {}
+        elif cur and line.startswith("/*") and "*/" in line:
+            body = line.split("*/", 1)[1].strip()
+            if not body or body.startswith("/*"):
+                continue
+            op = body.split()[0].rstrip(";")
+            if op.startswith("@"):
+                parts = body.split()
+                op = parts[1].rstrip(";") if len(parts) > 1 else op
+            base = op.split(".")[0]
+            kernels[cur][base] = kernels[cur].get(base, 0) + 1
+    keys = ["UTCHMMA", "UTCBAR", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "SYNCS", "HMMA", "REDG", "ATOMG"]
+    with open(os.path.join(out_dir, "summary.md"), "w") as f:
+        f.write("# SASS evidence per kernel (cuobjdump -sass libppb200.so)\n\n")
+        f.write("Counts of the Blackwell-specific opcodes per kernel. `UTCHMMA` = tcgen05.mma, `LDTM`/`STTM` = "
+                "tcgen05.ld/st, `UTMALDG`/`UTMASTG`/`UTMAREDG` = TMA load/store/reduce, `SYNCS` = mbarrier.\n\n")
+        f.write("| kernel | instrs | " + " | ".join(keys) + " |\n|---|---|" + "---|" * len(keys) + "\n")
+        for k, hist in sorted(kernels.items()):
+            tot = sum(hist.values())
+            f.write(f"| `{k[:110]}` | {tot} | " + " | ".join(str(hist.get(x, 0)) for x in keys) + " |\n")
+    print(f"wrote {out_dir}/summary.md ({len(kernels)} kernels)")
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--force", action="store_true")
+    ap.add_argument("--verbose", "-v", action="store_true")
+    ap.add_argument("--sass", action="store_true")
+    a = ap.parse_args()
+    lib = build(force=a.force, verbose=a.verbose)
+    print(lib)
+    if a.sass:
+        dump_sass()

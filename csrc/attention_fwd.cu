@@ -1,0 +1,398 @@
+// K4 forward: flash attention on tcgen05 tensor cores with TMEM accumulators.
+//
+// One CTA handles MT (1 or 2) query tiles of 128 rows for one (batch, head) and streams 128-row K/V tiles:
+//   * warp 2*MT*... layout: warps [0, 4*MT) = softmax warpgroups (one per query tile; thread == query row,
+//     which is exactly the TMEM lane it may read with tcgen05.ld 32x32b, so row max / row sum need no shuffles),
+//     warp 4*MT = TMA producer, warp 4*MT+1 = MMA issuer (+ TMEM allocation);
+//   * S = Q K^T   : tcgen05.mma, both operands K-major from 128B-swizzled smem, accumulator S_t in TMEM;
+//   * softmax     : online (running max / sum in the exp2 domain), optional causal mask and probability
+//                   dropout (counter-based mask, regenerated in backward), P written as bf16 into swizzled smem;
+//   * O_tile = P V: tcgen05.mma with V as an MN-major B operand (no transpose of V anywhere), result in TMEM,
+//                   drained into fp32 registers and rescaled there (O never round-trips through HBM);
+//   * with MT = 2 the two softmax warpgroups ping-pong against the single MMA issuer, so the tensor pipe
+//     works on one query tile while the other one is in its exp2 phase.
+// Inputs are column-sliced views of the packed QKV activation ([tokens, 3*d]); heads are addressed through 4-D
+// TMA tensor maps (dh, head, seq, batch), so no split/transposes/.contiguous() copies exist.  Head dims that are
+// not multiples of 64 (96, 192 in the reference sweep) are zero-padded by TMA out-of-bounds fill.
+//
+// Replaces aten.bmm x2 + mul.Scalar + _safe_softmax + dropout of the reference's attention blocks
+// (self- and cross-attention of nn.TransformerDecoderLayer,
+// /root/reference/LLMsDistributedTrainingHelper.py:40-44, :52).
+#include "common.cuh"
+#include "host_common.h"
+#include "ppb200.h"
+
+namespace ppb {
+
+struct AttnParams {
+  int B, H, Sq, Skv, dh;
+  int causal;
+  float sl2;  // softmax scale * log2(e)
+  unsigned long long seed;
+  unsigned int drop_thresh;
+  float drop_scale;
+  float* lse;  // [B, H, Sq] natural-log LSE
+};
+
+template <int DQK, int DV, int MT>
+struct AttnFwdCfg {
+  static constexpr int NQK = DQK / 64, NV = DV / 64;
+  static constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 64 bf16 (one 128B-swizzled column chunk)
+  static constexpr int Q_BYTES = NQK * CHUNK_BYTES;
+  static constexpr int K_BYTES = NQK * CHUNK_BYTES;
+  static constexpr int V_BYTES = NV * CHUNK_BYTES;
+  static constexpr int P_BYTES = 2 * CHUNK_BYTES;
+  static constexpr int FIXED = MT * (Q_BYTES + P_BYTES);
+  static constexpr int STAGES = (FIXED + 2 * (K_BYTES + V_BYTES) <= 220 * 1024) ? 2 : 1;
+  static constexpr int SMEM_BYTES = FIXED + STAGES * (K_BYTES + V_BYTES) + 512 + 1024;
+  static constexpr int TMEM_NEED = MT * (128 + DV);
+  static constexpr int TMEM_COLS = TMEM_NEED <= 128 ? 128 : (TMEM_NEED <= 256 ? 256 : 512);
+  static constexpr int THREADS = (4 * MT + 2) * 32;
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DQK, int DV, int MT>
+__global__ void __launch_bounds__(AttnFwdCfg<DQK, DV, MT>::THREADS, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO, const AttnParams p) {
+  using Cfg = AttnFwdCfg<DQK, DV, MT>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t q_smem = smem_base;                          // [MT][Q_BYTES]
+  const uint32_t p_smem = q_smem + MT * Cfg::Q_BYTES;         // [MT][P_BYTES]
+  const uint32_t k_smem = p_smem + MT * Cfg::P_BYTES;         // [STAGES][K_BYTES]
+  const uint32_t v_smem = k_smem + STAGES * Cfg::K_BYTES;     // [STAGES][V_BYTES]
+  const uint32_t bar_base = v_smem + STAGES * Cfg::V_BYTES;
+  // barriers
+  const uint32_t q_full = bar_base;
+  auto k_full = [&](int s) { return bar_base + 8u * (1 + s); };
+  auto k_empty = [&](int s) { return bar_base + 8u * (3 + s); };
+  auto v_full = [&](int s) { return bar_base + 8u * (5 + s); };
+  auto v_empty = [&](int s) { return bar_base + 8u * (7 + s); };
+  auto s_full = [&](int t) { return bar_base + 8u * (9 + t); };
+  auto s_empty = [&](int t) { return bar_base + 8u * (11 + t); };
+  auto p_full = [&](int t) { return bar_base + 8u * (13 + t); };
+  auto pv_full = [&](int t) { return bar_base + 8u * (15 + t); };
+  auto pv_empty = [&](int t) { return bar_base + 8u * (17 + t); };
+  const uint32_t tmem_ptr_smem = bar_base + 8u * 19;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int TMA_WARP = 4 * MT, MMA_WARP = 4 * MT + 1;
+
+  const int q_tiles = (p.Sq + 128 * MT - 1) / (128 * MT);
+  const int qt = blockIdx.x % q_tiles;
+  const int bh = blockIdx.x / q_tiles;
+  const int h = bh % p.H, b = bh / p.H;
+  const int q0 = qt * 128 * MT;
+  int kv_len = p.Skv;
+  if (p.causal) kv_len = min(p.Skv, q0 + 128 * MT + (p.Skv - p.Sq));
+  const int n_kv = (kv_len + 127) / 128;
+
+  if (warp == TMA_WARP && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmO);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(k_full(s), 1);
+      mbar_init(k_empty(s), 1);
+      mbar_init(v_full(s), 1);
+      mbar_init(v_empty(s), 1);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(s_full(t), 1);
+      mbar_init(s_empty(t), 128);
+      mbar_init(p_full(t), 128);
+      mbar_init(pv_full(t), 1);
+      mbar_init(pv_empty(t), 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == MMA_WARP) tmem_alloc(tmem_ptr_smem, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_ptr_smem - smem_base));
+  auto s_tmem = [&](int t) { return tmem_base + t * (128 + DV); };
+  auto pv_tmem = [&](int t) { return tmem_base + t * (128 + DV) + 128; };
+
+  if (warp == TMA_WARP) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, MT * Cfg::Q_BYTES);
+      for (int t = 0; t < MT; ++t)
+        for (int c = 0; c < Cfg::NQK; ++c)
+          tma_load_4d(q_smem + t * Cfg::Q_BYTES + c * Cfg::CHUNK_BYTES, &tmQ, q_full, c * 64, h, q0 + t * 128, b);
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j % STAGES;
+        const uint32_t par = ((j / STAGES) & 1) ^ 1;
+        mbar_wait(k_empty(st), par);
+        mbar_expect_tx(k_full(st), Cfg::K_BYTES);
+        for (int c = 0; c < Cfg::NQK; ++c)
+          tma_load_4d(k_smem + st * Cfg::K_BYTES + c * Cfg::CHUNK_BYTES, &tmK, k_full(st), c * 64, h, j * 128, b);
+        mbar_wait(v_empty(st), par);
+        mbar_expect_tx(v_full(st), Cfg::V_BYTES);
+        for (int c = 0; c < Cfg::NV; ++c)
+          tma_load_4d(v_smem + st * Cfg::V_BYTES + c * Cfg::CHUNK_BYTES, &tmV, v_full(st), c * 64, h, j * 128, b);
+      }
+    }
+  } else if (warp == MMA_WARP) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_pv = make_idesc_bf16(128, DV, 0, 1);
+      auto issue_s = [&](int t, int j) {
+        const int st = j % STAGES;
+        const uint32_t qa = q_smem + t * Cfg::Q_BYTES;
+        const uint32_t kb = k_smem + st * Cfg::K_BYTES;
+#pragma unroll
+        for (int kk = 0; kk < DQK / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32;
+          umma_f16_ss(s_tmem(t), make_smem_desc_sw128(qa + off, 16, 1024), make_smem_desc_sw128(kb + off, 16, 1024),
+                      idesc_s, kk > 0 ? 1u : 0u);
+        }
+        umma_commit(s_full(t));
+      };
+      mbar_wait(q_full, 0);
+      mbar_wait(k_full(0), 0);
+      tc_fence_after();
+      for (int t = 0; t < MT; ++t) issue_s(t, 0);
+      umma_commit(k_empty(0));
+      for (int j = 0; j < n_kv; ++j) {
+        const int st = j % STAGES;
+        const uint32_t par = (j / STAGES) & 1;
+        mbar_wait(v_full(st), par);
+        if (j + 1 < n_kv) mbar_wait(k_full((j + 1) % STAGES), ((j + 1) / STAGES) & 1);
+        for (int t = 0; t < MT; ++t) {
+          mbar_wait(p_full(t), j & 1);
+          mbar_wait(pv_empty(t), (j & 1) ^ 1);
+          tc_fence_after();
+          const uint32_t pa = p_smem + t * Cfg::P_BYTES;
+          const uint32_t vb = v_smem + st * Cfg::V_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            umma_f16_ss(pv_tmem(t), make_smem_desc_sw128(pa + (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32, 16, 1024),
+                        make_smem_desc_sw128(vb + kk * 2048, Cfg::CHUNK_BYTES, 1024), idesc_pv, kk > 0 ? 1u : 0u);
+          }
+          umma_commit(pv_full(t));
+          if (t == MT - 1) umma_commit(v_empty(st));
+          if (j + 1 < n_kv) {
+            mbar_wait(s_empty(t), j & 1);
+            tc_fence_after();
+            issue_s(t, j + 1);
+            if (t == MT - 1) umma_commit(k_empty((j + 1) % STAGES));
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ======================= softmax warpgroup t: thread == query row =======================
+    const int t = warp >> 2;
+    const int row = (warp & 3) * 32 + lane;
+    const int q_idx = q0 + t * 128 + row;
+    const uint32_t lane_off = uint32_t((warp & 3) * 32) << 16;
+    const int causal_lim = q_idx + (p.Skv - p.Sq);  // last visible kv index for this row
+    const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * p.Sq + (unsigned long long)min(q_idx, p.Sq - 1)) *
+                                        (unsigned long long)p.Skv;
+    float o[DV];
+#pragma unroll
+    for (int i = 0; i < DV; ++i) o[i] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+    const uint32_t p_row = p_smem + t * Cfg::P_BYTES + row * 128;
+
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(s_full(t), j & 1);
+      tc_fence_after();
+      const int kv0 = j * 128;
+      const bool need_mask = (kv0 + 128 > p.Skv) || (p.causal && (kv0 + 127 > causal_lim));
+      // ---- pass 1: row max ----
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(s_tmem(t) + lane_off + c * 32, r);
+        tmem_ld_wait();
+        if (!need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int kv = kv0 + c * 32 + i;
+            const bool ok = (kv < p.Skv) && (!p.causal || kv <= causal_lim);
+            if (ok) mx = fmaxf(mx, __uint_as_float(r[i]));
+          }
+        }
+      }
+      const float m_new = fmaxf(m_run, mx * p.sl2);
+      const float alpha = (m_new == -INFINITY) ? 1.f : fast_exp2(m_run - m_new);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      // ---- fold the previous tile's P*V into the register accumulator, then rescale ----
+      if (j > 0) {
+        mbar_wait(pv_full(t), (j - 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < DV / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_x32(pv_tmem(t) + lane_off + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
+        }
+        tc_fence_before();
+        mbar_arrive(pv_empty(t));
+      }
+      if (alpha != 1.f) {
+#pragma unroll
+        for (int i = 0; i < DV; ++i) o[i] *= alpha;
+      }
+      l_run *= alpha;
+      m_run = m_new;
+      // ---- pass 2: probabilities -> bf16 P tile in swizzled smem ----
+      float lsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t r[32];
+        tmem_ld_x32(s_tmem(t) + lane_off + c * 32, r);
+        tmem_ld_wait();
+        float pr[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float e = fast_exp2(fmaf(__uint_as_float(r[i]), p.sl2, -m_use));
+          if (need_mask) {
+            const int kv = kv0 + c * 32 + i;
+            const bool ok = (kv < p.Skv) && (!p.causal || kv <= causal_lim);
+            e = ok ? e : 0.f;
+          }
+          lsum += e;
+          pr[i] = e;
+        }
+        if (p.drop_thresh) {
+          const unsigned long long base = drop_row + (unsigned long long)(kv0 + c * 32);
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const uint32_t hsh = dropout_pair_bits(p.seed, (base + i) >> 1);
+            pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] * p.drop_scale : 0.f;
+            pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] * p.drop_scale : 0.f;
+          }
+        }
+        const uint32_t atom = p_row + (c >> 1) * Cfg::CHUNK_BYTES;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t cc = (c & 1) * 4 + q;
+          const uint32_t dst = atom + ((cc ^ (row & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack_bf16(pr[8 * q], pr[8 * q + 1])),
+                       "r"(pack_bf16(pr[8 * q + 2], pr[8 * q + 3])), "r"(pack_bf16(pr[8 * q + 4], pr[8 * q + 5])),
+                       "r"(pack_bf16(pr[8 * q + 6], pr[8 * q + 7]))
+                       : "memory");
+        }
+      }
+      l_run += lsum;
+      tc_fence_before();
+      mbar_arrive(s_empty(t));  // S_t may be overwritten by the next QK^T
+      fence_proxy_async_smem();
+      mbar_arrive(p_full(t));   // P_t is visible to the tensor core
+    }
+    // ---- last P*V, normalise, store ----
+    mbar_wait(pv_full(t), (n_kv - 1) & 1);
+    tc_fence_after();
+#pragma unroll
+    for (int c = 0; c < DV / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_x32(pv_tmem(t) + lane_off + c * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
+    }
+    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+    if (q_idx < p.Sq) p.lse[((long long)(b * p.H + h)) * p.Sq + q_idx] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+    // stage O (bf16) through the (now free) P region of this warpgroup: NV chunks of [128 rows x 128 B]
+#pragma unroll
+    for (int c = 0; c < DV / 64; ++c) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const uint32_t dst = p_smem + t * Cfg::P_BYTES + c * Cfg::CHUNK_BYTES + row * 128 + ((q ^ (row & 7)) << 4);
+        const float* s = &o[c * 64 + q * 8];
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack_bf16(s[0] * inv_l, s[1] * inv_l)),
+                     "r"(pack_bf16(s[2] * inv_l, s[3] * inv_l)), "r"(pack_bf16(s[4] * inv_l, s[5] * inv_l)),
+                     "r"(pack_bf16(s[6] * inv_l, s[7] * inv_l))
+                     : "memory");
+      }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1 + t, 128);
+    if ((warp & 3) == 0 && lane == 0 && q0 + t * 128 < p.Sq) {
+      for (int c = 0; c < DV / 64; ++c)
+        if (c * 64 < p.dh) tma_store_4d(&tmO, p_smem + t * Cfg::P_BYTES + c * Cfg::CHUNK_BYTES, c * 64, h, q0 + t * 128, b);
+      tma_commit_group();
+      tma_wait_group<0>();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == MMA_WARP) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+bool make_head_tmap(CUtensorMap* tm, const void* ptr, int dh, int H, int S, int B, long long ld, int box_rows) {
+  uint64_t dims[4] = {(uint64_t)dh, (uint64_t)H, (uint64_t)S, (uint64_t)B};
+  uint64_t strides[3] = {(uint64_t)dh * 2, (uint64_t)ld * 2, (uint64_t)S * (uint64_t)ld * 2};
+  uint32_t box[4] = {64, 1, (uint32_t)box_rows, 1};
+  return make_tmap(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, ptr, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+template <int DQK, int DV, int MT>
+static int launch_attn_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to,
+                           const AttnParams& p, cudaStream_t stream) {
+  using Cfg = AttnFwdCfg<DQK, DV, MT>;
+  auto kfn = attn_fwd_kernel<DQK, DV, MT>;
+  PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+  const int q_tiles = (p.Sq + 128 * MT - 1) / (128 * MT);
+  kfn<<<p.B * p.H * q_tiles, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(tq, tk, tv, to, p);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq,
+                            int Skv, int dh, long long ldq, long long ldk, long long ldv, long long ldo, int causal,
+                            int reserved0, int reserved1, float scale, float dropout_p, unsigned long long seed,
+                            void* stream_) {
+  (void)reserved0;
+  (void)reserved1;
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(B > 0 && H > 0 && Sq > 0 && Skv > 0, "ppb_attn_fwd: empty problem");
+  PPB_REQUIRE(dh % 8 == 0 && dh >= 8 && dh <= 128, "ppb_attn_fwd: head dim must be a multiple of 8 in [8, 128] (got %d)", dh);
+  PPB_REQUIRE((ldq % 8) == 0 && (ldk % 8) == 0 && (ldv % 8) == 0 && (ldo % 8) == 0, "ppb_attn_fwd: row strides must be multiples of 8");
+  PPB_REQUIRE(!causal || Skv >= Sq, "ppb_attn_fwd: causal attention needs Skv >= Sq");
+  PPB_REQUIRE(dropout_p <= 0.f || (Skv % 2) == 0, "ppb_attn_fwd: dropout needs an even Skv");
+  CUtensorMap tq, tk, tv, to;
+  if (!make_head_tmap(&tq, q, dh, H, Sq, B, ldq, 128) || !make_head_tmap(&tk, k, dh, H, Skv, B, ldk, 128) ||
+      !make_head_tmap(&tv, v, dh, H, Skv, B, ldv, 128) || !make_head_tmap(&to, o, dh, H, Sq, B, ldo, 128))
+    return -3;
+  AttnParams p;
+  p.B = B;
+  p.H = H;
+  p.Sq = Sq;
+  p.Skv = Skv;
+  p.dh = dh;
+  p.causal = causal;
+  p.sl2 = scale * 1.4426950408889634f;
+  p.seed = seed;
+  p.drop_thresh = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
+  p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
+  p.lse = lse;
+  const bool two = Sq > 128;
+  if (dh <= 64) return two ? launch_attn_fwd<64, 64, 2>(tq, tk, tv, to, p, stream) : launch_attn_fwd<64, 64, 1>(tq, tk, tv, to, p, stream);
+  return two ? launch_attn_fwd<128, 128, 2>(tq, tk, tv, to, p, stream) : launch_attn_fwd<128, 128, 1>(tq, tk, tv, to, p, stream);
+}

@@ -1,0 +1,198 @@
+// K6 / K8: the bandwidth-bound helpers that are not absorbed by a GEMM epilogue.
+//   * embedding gather forward and scatter-add backward (aten.embedding / embedding_dense_backward;
+//     /root/reference/LLMsDistributedTrainingHelper.py:36,50)
+//   * bias gradient (column sums of dy, fp32 accumulate; aten.sum.dim_IntList of the reference op stream)
+//   * fan-in sum of up to three bf16 gradients (aten.add.Tensor in autograd's accumulation)
+//   * GELU forward (only for the GPT presets, where the pre-activation has to be kept for backward)
+//   * fp32 -> bf16 cast, fill
+#include "common.cuh"
+#include "host_common.h"
+#include "ppb200.h"
+
+namespace ppb {
+
+// one warp per token row; 16-byte vectors
+__global__ void __launch_bounds__(256) embedding_fwd_kernel(const long long* __restrict__ idx,
+                                                            const bf16* __restrict__ W, bf16* __restrict__ out, int T,
+                                                            int d, int V) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int nch = d >> 3;
+  for (int t = warp; t < T; t += nwarps) {
+    long long id = idx[t];
+    id = id < 0 ? 0 : (id >= V ? V - 1 : id);
+    const uint4* src = reinterpret_cast<const uint4*>(W + id * (long long)d);
+    uint4* dst = reinterpret_cast<uint4*>(out + (long long)t * d);
+    for (int c = lane; c < nch; c += 32) dst[c] = __ldg(src + c);
+  }
+}
+
+// dW[idx[t], :] += dy0[t,:] (+ dy1 + dy2)   fp32 vector atomics (red.global.add.v4.f32)
+__global__ void __launch_bounds__(256) embedding_bwd_kernel(const long long* __restrict__ idx,
+                                                            const bf16* __restrict__ dy0, const bf16* __restrict__ dy1,
+                                                            const bf16* __restrict__ dy2, float* __restrict__ dW, int T,
+                                                            int d, int V) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  const int nch = d >> 3;
+  for (int t = warp; t < T; t += nwarps) {
+    long long id = idx[t];
+    if (id < 0 || id >= V) continue;
+    float* dst = dW + id * (long long)d;
+    for (int c = lane; c < nch; c += 32) {
+      const long long off = (long long)t * d + c * 8;
+      const uint4 a = *reinterpret_cast<const uint4*>(dy0 + off);
+      uint4 b = make_uint4(0, 0, 0, 0), e = make_uint4(0, 0, 0, 0);
+      if (dy1) b = *reinterpret_cast<const uint4*>(dy1 + off);
+      if (dy2) e = *reinterpret_cast<const uint4*>(dy2 + off);
+      const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w}, ew[4] = {e.x, e.y, e.z, e.w};
+      float f[8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 x = unpack_bf16(aw[q]), y = unpack_bf16(bw[q]), z = unpack_bf16(ew[q]);
+        f[2 * q] = x.x + y.x + z.x;
+        f[2 * q + 1] = x.y + y.y + z.y;
+      }
+      atomicAdd(reinterpret_cast<float4*>(dst + c * 8), make_float4(f[0], f[1], f[2], f[3]));
+      atomicAdd(reinterpret_cast<float4*>(dst + c * 8 + 4), make_float4(f[4], f[5], f[6], f[7]));
+    }
+  }
+}
+
+// db[n] += sum_t dy[t, n].  grid = (column blocks of 256, row slabs); each thread owns 2 columns... one bf162
+__global__ void __launch_bounds__(256) colsum_kernel(const bf16* __restrict__ dy, long long ld, float* __restrict__ db,
+                                                     int T, int N, int rows_per_cta) {
+  __shared__ float2 red[8][32];
+  // thread layout: 32 column-pairs (64 columns) x 8 row lanes
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cx) * 2;
+  const int r0 = blockIdx.y * rows_per_cta;
+  const int r1 = min(T, r0 + rows_per_cta);
+  float2 acc = make_float2(0.f, 0.f);
+  if (col < N) {
+    for (int r = r0 + ry; r < r1; r += 8) {
+      const uint32_t u = *reinterpret_cast<const uint32_t*>(dy + (long long)r * ld + col);
+      const float2 f = unpack_bf16(u);
+      acc.x += f.x;
+      acc.y += f.y;
+    }
+  }
+  red[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && col < N) {
+    float2 s = red[0][cx];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+      s.x += red[i][cx].x;
+      s.y += red[i][cx].y;
+    }
+    atomicAdd(db + col, s.x);
+    if (col + 1 < N) atomicAdd(db + col + 1, s.y);
+  }
+}
+
+__global__ void __launch_bounds__(256) add_n_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b,
+                                                    const bf16* __restrict__ c, bf16* __restrict__ out, long long n8) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 x = reinterpret_cast<const uint4*>(a)[i];
+    uint4 y = make_uint4(0, 0, 0, 0), z = make_uint4(0, 0, 0, 0);
+    if (b) y = reinterpret_cast<const uint4*>(b)[i];
+    if (c) z = reinterpret_cast<const uint4*>(c)[i];
+    const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, yw[4] = {y.x, y.y, y.z, y.w}, zw[4] = {z.x, z.y, z.z, z.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = unpack_bf16(xw[q]), g = unpack_bf16(yw[q]), h = unpack_bf16(zw[q]);
+      o[q] = pack_bf16(f.x + g.x + h.x, f.y + g.y + h.y);
+    }
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) gelu_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, long long n8) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 u = reinterpret_cast<const uint4*>(x)[i];
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = unpack_bf16(w[q]);
+      o[q] = pack_bf16(gelu_erf(f.x), gelu_erf(f.y));
+    }
+    reinterpret_cast<uint4*>(y)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restrict__ x, bf16* __restrict__ y,
+                                                            long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = __float2bfloat16(x[i]);
+}
+
+static int ew_grid(long long work_items) {
+  long long b = (work_items + 255) / 256;
+  const long long cap = (long long)sm_count() * 8;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" int ppb_embedding_fwd(const long long* idx, const void* W, void* out, int T, int d, int V, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(T > 0 && d > 0 && (d % 8) == 0, "ppb_embedding_fwd: d must be a multiple of 8 (got %d)", d);
+  embedding_fwd_kernel<<<ew_grid((long long)T * 32), 256, 0, stream>>>(idx, (const bf16*)W, (bf16*)out, T, d, V);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_embedding_bwd(const long long* idx, const void* dy0, const void* dy1, const void* dy2, float* dW,
+                                 int T, int d, int V, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(T > 0 && d > 0 && (d % 8) == 0, "ppb_embedding_bwd: d must be a multiple of 8 (got %d)", d);
+  embedding_bwd_kernel<<<ew_grid((long long)T * 32), 256, 0, stream>>>(idx, (const bf16*)dy0, (const bf16*)dy1,
+                                                                       (const bf16*)dy2, dW, T, d, V);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_colsum_accum(const void* dy, long long ld, float* db, int T, int N, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(T > 0 && N > 0 && (ld % 2) == 0, "ppb_colsum_accum: ld must be even");
+  const int col_blocks = (N + 63) / 64;
+  int slabs = (sm_count() * 4 + col_blocks - 1) / col_blocks;
+  if (slabs > (T + 63) / 64) slabs = (T + 63) / 64;
+  if (slabs < 1) slabs = 1;
+  const int rows_per = (T + slabs - 1) / slabs;
+  dim3 grid(col_blocks, (T + rows_per - 1) / rows_per);
+  colsum_kernel<<<grid, 256, 0, stream>>>((const bf16*)dy, ld, db, T, N, rows_per);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_add_n_bf16(const void* a, const void* b, const void* c, void* out, long long n, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_add_n_bf16: element count must be a multiple of 8");
+  add_n_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)a, (const bf16*)b, (const bf16*)c, (bf16*)out, n / 8);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_gelu_fwd(const void* x, void* y, long long n, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_gelu_fwd: element count must be a multiple of 8");
+  gelu_fwd_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)x, (bf16*)y, n / 8);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (n <= 0) return 0;
+  cast_f32_bf16_kernel<<<ew_grid(n), 256, 0, stream>>>(x, (bf16*)y, n);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,450 @@
+// K1/K2/K3: persistent, warp-specialised bf16 GEMM on the 5th-gen tensor cores.
+//
+//   C[M,N] (+)= epilogue( op(A)[M,K] * op(B)[N,K]^T )          fp32 accumulation in TMEM
+//
+// * operands are staged by TMA (128B swizzle) into a multi-stage smem ring; both K-major ("row-major
+//   [rows,K]") and MN-major ("stored [K,rows]") operands are supported through the UMMA smem/instruction
+//   descriptors, which covers forward (x*W^T), dgrad (dy*W) and wgrad (dy^T*x) without any transposes;
+// * one elected thread issues tcgen05.mma (M=128, N=BN, K=16) into a double-buffered TMEM accumulator
+//   (2*BN columns), so the epilogue of tile i overlaps the main loop of tile i+1;
+// * four epilogue warps read the accumulator with tcgen05.ld (one row per thread), apply the fused
+//   epilogue (bias / ReLU / GELU / dropout / activation-gradient masks), stage through swizzled smem and
+//   write with TMA stores -- or TMA reduce-add in fp32, which is what makes split-K wgrad accumulation
+//   across micro-batches free of read-modify-write traffic.
+//
+// Replaces aten.mm/addmm (+add, +relu, +sum) of the reference's op stream; reference call
+// sites: nn.TransformerDecoderLayer linears and the LM head, /root/reference/LLMsDistributedTrainingHelper.py:40-46.
+#include "common.cuh"
+#include "host_common.h"
+#include "ppb200.h"
+
+namespace ppb {
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int GEMM_THREADS = 192;  // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer + TMEM owner
+constexpr int EPI_BUF_BYTES = 4096;  // 32 rows x 128 B per warp per buffer
+
+struct GemmParams {
+  int M, N, K;
+  int tiles_m, tiles_n, splits, kb_per_split;
+  int epi;
+  float alpha;
+  const bf16* bias;
+  const bf16* aux;
+  long long ld_aux;
+  unsigned long long seed;
+  unsigned int drop_thresh;
+  float drop_scale;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024 align slack
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+template <int BN, bool A_MN, bool B_MN, int OUT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t epi_base = smem_base + STAGES * Cfg::STAGE_BYTES;
+  const uint32_t bar_base = epi_base + Cfg::EPI_BYTES;
+  // barrier layout: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], tmem ptr
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * STAGES + 4);
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));  // generic pointer to the aligned base
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 5) tmem_alloc(tmem_ptr_smem, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_ptr_smem - smem_base));
+
+  const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
+  const int num_kb_total = (p.K + BK - 1) / BK;
+
+  if (warp == 4) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int mn = t % (p.tiles_m * p.tiles_n);
+        const int sp = t / (p.tiles_m * p.tiles_n);
+        const int m0 = (mn % p.tiles_m) * BM;
+        const int n0 = (mn / p.tiles_m) * BN;
+        const int kb0 = sp * p.kb_per_split;
+        const int kb1 = min(num_kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint32_t sb = sa + Cfg::A_BYTES;
+          if (!A_MN) {
+            tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m0);  // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int i = 0; i < BM / 64; ++i)  // box {64 m, 64 k}
+              tma_load_2d(sa + i * (BK * 128), &tmA, full_bar(stage), m0 + i * 64, kb * BK);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, n0);  // box {64 k, BN rows}
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tma_load_2d(sb + i * (BK * 128), &tmB, full_bar(stage), n0 + i * 64, kb * BK);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+        const int sp = t / (p.tiles_m * p.tiles_n);
+        const int kb0 = sp * p.kb_per_split;
+        const int kb1 = min(num_kb_total, kb0 + p.kb_per_split);
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
+          const uint32_t sb = sa + Cfg::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // K-major: 16 k-elements = 32 B inside the 128 B swizzled row; SBO = 8 rows * 128 B.
+            // MN-major: 16 k-rows = 2 atoms of 1024 B; LBO = stride between 64-wide MN chunks (one TMA box).
+            const uint64_t da = A_MN ? make_smem_desc_sw128(sa + k * 2048, BK * 128, 1024)
+                                     : make_smem_desc_sw128(sa + k * 32, 16, 1024);
+            const uint64_t db = B_MN ? make_smem_desc_sw128(sb + k * 2048, BK * 128, 1024)
+                                     : make_smem_desc_sw128(sb + k * 32, 16, 1024);
+            umma_f16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(empty_bar(stage));  // smem slot is free once these MMAs have read it
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+      }
+    }
+    __syncwarp();
+  } else {
+    // ======================= epilogue warps 0..3 =======================
+    constexpr int CHUNK = (OUT == 0) ? 64 : 32;  // columns per staged 128-byte row
+    const uint32_t my_epi = epi_base + warp * 2 * EPI_BUF_BYTES;
+    int it = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int mn = t % (p.tiles_m * p.tiles_n);
+      const int m0 = (mn % p.tiles_m) * BM;
+      const int n0 = (mn / p.tiles_m) * BN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + acc * BN + (uint32_t(warp * 32) << 16);
+      const int row = m0 + warp * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN / CHUNK; ++c) {
+        if (n0 + c * CHUNK >= p.N) break;  // fully out-of-range column chunk (uniform across the CTA)
+        uint32_t r[CHUNK];
+        tmem_ld_x32(t_row + c * CHUNK, r);
+        if constexpr (CHUNK == 64) tmem_ld_x32(t_row + c * CHUNK + 32, r + 32);
+        tmem_ld_wait();
+        float v[CHUNK];
+#pragma unroll
+        for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
+        const int nc = n0 + c * CHUNK;
+        if (p.epi == PPB_EPI_BIAS || p.epi == PPB_EPI_BIAS_RELU || p.epi == PPB_EPI_BIAS_GELU ||
+            p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
+#pragma unroll
+          for (int j = 0; j < CHUNK; ++j) {
+            const int n = nc + j;
+            const float b = (n < p.N) ? __bfloat162float(__ldg(p.bias + n)) : 0.f;
+            v[j] += b;
+          }
+          if (p.epi == PPB_EPI_BIAS_RELU || p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j) v[j] = fmaxf(v[j], 0.f);
+          } else if (p.epi == PPB_EPI_BIAS_GELU) {
+#pragma unroll
+            for (int j = 0; j < CHUNK; ++j) v[j] = gelu_erf(v[j]);
+          }
+          if (p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
+            const unsigned long long base = (unsigned long long)row * (unsigned long long)p.N + nc;
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 2) {
+              // N is even for every dropout caller, so (base + j) is even and shares one pair hash
+              const uint32_t h = dropout_pair_bits(p.seed, (base + j) >> 1);
+              v[j] = ((h & 0xFFFFu) >= p.drop_thresh) ? v[j] * p.drop_scale : 0.f;
+              v[j + 1] = ((h >> 16) >= p.drop_thresh) ? v[j + 1] * p.drop_scale : 0.f;
+            }
+          }
+        } else if (p.epi == PPB_EPI_MASK_POS || p.epi == PPB_EPI_GELU_BWD) {
+          // activation backward: aux holds the stashed (post-dropout) ReLU output, or the GELU pre-activation
+          if (row < p.M) {
+            const bf16* ap = p.aux + (long long)row * p.ld_aux + nc;
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 8) {
+              if (nc + j + 8 <= p.N) {
+                const uint4 a4 = *reinterpret_cast<const uint4*>(ap + j);
+                const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  const float2 a2 = unpack_bf16(aw[q]);
+                  if (p.epi == PPB_EPI_MASK_POS) {
+                    v[j + 2 * q] = a2.x > 0.f ? v[j + 2 * q] : 0.f;
+                    v[j + 2 * q + 1] = a2.y > 0.f ? v[j + 2 * q + 1] : 0.f;
+                  } else {
+                    v[j + 2 * q] *= gelu_erf_grad(a2.x);
+                    v[j + 2 * q + 1] *= gelu_erf_grad(a2.y);
+                  }
+                }
+              } else {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                  const int n = nc + j + q;
+                  if (n < p.N) {
+                    const float a = __bfloat162float(ap[j + q]);
+                    v[j + q] = (p.epi == PPB_EPI_MASK_POS) ? (a > 0.f ? v[j + q] : 0.f) : v[j + q] * gelu_erf_grad(a);
+                  }
+                }
+              }
+            }
+          }
+        }
+        // ---- stage into swizzled smem (row = lane, 8 x 16B chunks, chunk position XOR (row & 7)) ----
+        if (lane == 0) tma_wait_group_read<1>();  // the store issued from this buffer two chunks ago is done
+        __syncwarp();
+        const uint32_t srow = my_epi + buf * EPI_BUF_BYTES + lane * 128;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          uint32_t w0, w1, w2, w3;
+          if constexpr (OUT == 0) {
+            w0 = pack_bf16(v[8 * q + 0], v[8 * q + 1]);
+            w1 = pack_bf16(v[8 * q + 2], v[8 * q + 3]);
+            w2 = pack_bf16(v[8 * q + 4], v[8 * q + 5]);
+            w3 = pack_bf16(v[8 * q + 6], v[8 * q + 7]);
+          } else {
+            w0 = __float_as_uint(v[4 * q + 0]);
+            w1 = __float_as_uint(v[4 * q + 1]);
+            w2 = __float_as_uint(v[4 * q + 2]);
+            w3 = __float_as_uint(v[4 * q + 3]);
+          }
+          const uint32_t dst = srow + ((q ^ (lane & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(w0), "r"(w1), "r"(w2), "r"(w3)
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (OUT == 2)
+            tma_reduce_add_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+          else
+            tma_store_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+          tma_commit_group();
+        }
+        buf ^= 1;
+      }
+      // all TMEM reads of this accumulator are complete -> hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+    }
+    if (lane == 0) tma_wait_group<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+template <int BN, bool A_MN, bool B_MN, int OUT>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
+                       int grid, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kfn = gemm_tcgen05_kernel<BN, A_MN, B_MN, OUT>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  PPB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev >= 64 || !attr_done[dev]) {
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    if (dev < 64) attr_done[dev] = true;
+  }
+  kfn<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+template <int BN, int OUT>
+static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                          const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm<BN, false, false, OUT>(tmA, tmB, tmC, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm<BN, false, true, OUT>(tmA, tmB, tmC, p, grid, s);
+  if (a_mn && b_mn) return launch_gemm<BN, true, true, OUT>(tmA, tmB, tmC, p, grid, s);
+  return launch_gemm<BN, true, false, OUT>(tmA, tmB, tmC, p, grid, s);
+}
+
+// Pick (BN, splits) minimising a wave-quantised cost model.  Cycle costs per k-block (64 deep) follow the
+// tcgen05 pacing law of B300_MICROARCH.md: 4 MMAs x BN/2 cycles; plus a fixed per-tile overhead.
+static void choose_config(int M, int N, int K, int out_mode, int force_bn, int force_splits, int* bn_out,
+                          int* splits_out) {
+  const int sms = sm_count();
+  const int num_kb = (K + BK - 1) / BK;
+  const int cands[3] = {256, 128, 64};
+  double best = 1e30;
+  int best_bn = 128, best_sp = 1;
+  for (int ci = 0; ci < 3; ++ci) {
+    const int bn = cands[ci];
+    if (force_bn && bn != force_bn) continue;
+    if (!force_bn && bn > 64 && N <= bn / 2) continue;  // do not waste more than half a tile on padding
+    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+    const int max_sp = (out_mode == PPB_OUT_F32_ACCUM) ? 16 : 1;
+    for (int sp = 1; sp <= max_sp; ++sp) {
+      if (force_splits && sp != force_splits) continue;
+      const int kbs = (num_kb + sp - 1) / sp;
+      if (sp > 1 && kbs < 4) break;
+      if ((long long)(sp - 1) * kbs >= num_kb) continue;  // an empty split
+      const long long work = tiles * sp;
+      const long long waves = (work + sms - 1) / sms;
+      const double t_tile = kbs * (4.0 * bn / 2.0) + 600.0 + bn * 3.0;  // main loop + fill/drain + epilogue tail
+      const double cost = waves * t_tile;
+      if (cost < best) {
+        best = cost;
+        best_bn = bn;
+        best_sp = sp;
+      }
+    }
+  }
+  *bn_out = best_bn;
+  *splits_out = best_sp;
+}
+
+}  // namespace ppb
+
+using namespace ppb;
+
+extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                             long long ldc, int a_mn_major, int b_mn_major, int out_mode, int epi, float alpha,
+                             const void* bias, const void* aux, long long ld_aux, unsigned long long seed,
+                             float dropout_p, int force_bn, int force_splits, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(M > 0 && N > 0 && K > 0, "ppb_gemm_bf16: empty problem M=%d N=%d K=%d", M, N, K);
+  PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "ppb_gemm_bf16: lda/ldb must be multiples of 8 elements (TMA 16B stride)");
+  PPB_REQUIRE(out_mode == PPB_OUT_BF16 ? (ldc % 8) == 0 : (ldc % 4) == 0, "ppb_gemm_bf16: ldc must give a 16B-aligned row stride");
+  PPB_REQUIRE((reinterpret_cast<uintptr_t>(A) % 16) == 0 && (reinterpret_cast<uintptr_t>(B) % 16) == 0 &&
+                  (reinterpret_cast<uintptr_t>(C) % 16) == 0,
+              "ppb_gemm_bf16: operands must be 16-byte aligned");
+  PPB_REQUIRE(force_bn == 0 || force_bn == 64 || force_bn == 128 || force_bn == 256, "ppb_gemm_bf16: force_bn must be 0/64/128/256");
+  if (epi == PPB_EPI_BIAS || epi == PPB_EPI_BIAS_RELU || epi == PPB_EPI_BIAS_GELU || epi == PPB_EPI_BIAS_RELU_DROPOUT)
+    PPB_REQUIRE(bias != nullptr, "ppb_gemm_bf16: epilogue %d needs a bias vector", epi);
+  if (epi == PPB_EPI_MASK_POS || epi == PPB_EPI_GELU_BWD)
+    PPB_REQUIRE(aux != nullptr && (ld_aux % 8) == 0, "ppb_gemm_bf16: epilogue %d needs an aux matrix with ld %% 8 == 0", epi);
+  if (epi == PPB_EPI_BIAS_RELU_DROPOUT) PPB_REQUIRE((N % 2) == 0, "ppb_gemm_bf16: dropout epilogue needs even N");
+  if (out_mode != PPB_OUT_F32_ACCUM) PPB_REQUIRE(force_splits <= 1, "ppb_gemm_bf16: split-K needs the fp32 accumulate output mode");
+
+  int bn = 128, splits = 1;
+  choose_config(M, N, K, out_mode, force_bn, force_splits, &bn, &splits);
+
+  CUtensorMap tmA, tmB, tmC;
+  bool ok = true;
+  // operand maps: K-major -> dims {K, rows}, box {64, rows_per_tile}; MN-major -> dims {rows, K}, box {64, 64}
+  if (!a_mn_major)
+    ok = ok && make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, BM);
+  else
+    ok = ok && make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, BK);
+  if (!b_mn_major)
+    ok = ok && make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn);
+  else
+    ok = ok && make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK);
+  if (out_mode == PPB_OUT_BF16)
+    ok = ok && make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 2, 64, 32);
+  else
+    ok = ok && make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 4, 32, 32);
+  if (!ok) return -3;
+
+  GemmParams p;
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + bn - 1) / bn;
+  p.splits = splits;
+  p.kb_per_split = (((K + BK - 1) / BK) + splits - 1) / splits;
+  p.epi = epi;
+  p.alpha = alpha;
+  p.bias = reinterpret_cast<const bf16*>(bias);
+  p.aux = reinterpret_cast<const bf16*>(aux);
+  p.ld_aux = ld_aux;
+  p.seed = seed;
+  p.drop_thresh = dropout_thresh16(dropout_p);
+  p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
+  const long long total = (long long)p.tiles_m * p.tiles_n * splits;
+  const int grid = (int)(total < sm_count() ? total : sm_count());
+
+#define PPB_DISPATCH_OUT(BN_)                                                                               \
+  switch (out_mode) {                                                                                       \
+    case PPB_OUT_BF16: return dispatch_major<BN_, 0>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream); \
+    case PPB_OUT_F32: return dispatch_major<BN_, 1>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream);  \
+    case PPB_OUT_F32_ACCUM: return dispatch_major<BN_, 2>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream); \
+    default: break;                                                                                         \
+  }
+  if (bn == 256) {
+    PPB_DISPATCH_OUT(256)
+  } else if (bn == 128) {
+    PPB_DISPATCH_OUT(128)
+  } else {
+    PPB_DISPATCH_OUT(64)
+  }
+#undef PPB_DISPATCH_OUT
+  set_error("ppb_gemm_bf16: bad out_mode %d", out_mode);
+  return -2;
+}

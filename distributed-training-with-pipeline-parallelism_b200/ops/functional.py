@@ -1,0 +1,438 @@
+"""Functional op layer: every hot op of a pipeline stage, with explicit forward AND backward entry points.
+
+CUDA bf16 tensors go to the hand-written sm_100a kernels of libppb200.so (ctypes, C ABI, launched on the
+current torch stream, CUDA-graph capturable).  CPU tensors go to the fp32 references in ``ops.reference``.
+There is no PyTorch fallback for CUDA tensors: a missing library raises.
+
+The op set mirrors SURVEY.md section 8 (K1-K9) and replaces the ATen op stream of the reference
+(/root/reference/LLMsDistributedTrainingHelper.py:31-55).
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib, reference as ref
+
+OUT_BF16, OUT_F32, OUT_F32_ACCUM = 0, 1, 2
+EPI_NONE, EPI_BIAS, EPI_BIAS_RELU, EPI_BIAS_GELU, EPI_BIAS_RELU_DROPOUT, EPI_MASK_POS, EPI_GELU_BWD = range(7)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _lib_required():
+    return _lib.load(required=True)
+
+
+def _is_cuda(t: torch.Tensor) -> bool:
+    return t.is_cuda
+
+
+def _check_2d(t: torch.Tensor, name: str) -> None:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be 2-D with a contiguous last dim, got shape {tuple(t.shape)} stride {t.stride()}")
+
+
+def pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+# ------------------------------------------------------------------------------------------------------------
+# GEMM family
+# ------------------------------------------------------------------------------------------------------------
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, a_mn: bool, b_mn: bool,
+         out_mode: int = OUT_BF16, epi: int = EPI_NONE, alpha: float = 1.0, bias: Optional[torch.Tensor] = None,
+         aux: Optional[torch.Tensor] = None, seed: int = 0, dropout_p: float = 0.0, force_bn: int = 0,
+         force_splits: int = 0) -> torch.Tensor:
+    """Raw tcgen05 GEMM: out[M,N] (=|+=) epi(alpha * op(a)[M,K] @ op(b)[N,K]^T).  CUDA only."""
+    lib = _lib_required()
+    rc = lib.ppb_gemm_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, a.stride(0), b.stride(0),
+                           out.stride(0), int(a_mn), int(b_mn), out_mode, epi, float(alpha), _lib.ptr(bias),
+                           _lib.ptr(aux), 0 if aux is None else aux.stride(0), int(seed) & (2**64 - 1),
+                           float(dropout_p), force_bn, force_splits, _stream())
+    _lib.check(rc, "ppb_gemm_bf16")
+    _lib.count_launch()
+    return out
+
+
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+               dropout_p: float = 0.0, seed: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """y = dropout(act(x @ w^T + bias)).  x [T, in], w [out, in] -> y [T, out] (``out`` may be a padded-ld view)."""
+    _check_2d(x, "x")
+    _check_2d(w, "w")
+    if not _is_cuda(x):
+        y = ref.linear_fwd(x, w, bias, act, dropout_p, seed)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    T, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty((T, N), dtype=torch.bfloat16, device=x.device)
+    if bias is None:
+        if act is not None or dropout_p > 0:
+            raise ValueError("activation/dropout epilogues need a bias")
+        epi = EPI_NONE
+    elif act is None:
+        epi = EPI_BIAS
+    elif act == "relu":
+        epi = EPI_BIAS_RELU_DROPOUT if dropout_p > 0 else EPI_BIAS_RELU
+    elif act == "gelu":
+        if dropout_p > 0:
+            raise ValueError("gelu+dropout epilogue not implemented")
+        epi = EPI_BIAS_GELU
+    else:
+        raise ValueError(act)
+    return gemm(x, w, out, T, N, K, False, False, OUT_BF16, epi, 1.0, bias, None, seed, dropout_p)
+
+
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, mask_pos_aux: Optional[torch.Tensor] = None,
+                 gelu_aux: Optional[torch.Tensor] = None, alpha: float = 1.0,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx = alpha * (dy @ w) [* (aux > 0)] [* gelu'(aux)].  dy [T, out], w [out, in] -> dx [T, in]."""
+    _check_2d(dy, "dy")
+    _check_2d(w, "w")
+    if not _is_cuda(dy):
+        dx = ref.linear_dgrad(dy, w, mask_pos_aux, gelu_aux, alpha)
+        if out is not None:
+            out.copy_(dx)
+            return out
+        return dx
+    T, K = dy.shape  # K = out features
+    N = w.shape[1]
+    if out is None:
+        out = torch.empty((T, N), dtype=torch.bfloat16, device=dy.device)
+    epi, aux = EPI_NONE, None
+    if mask_pos_aux is not None:
+        epi, aux = EPI_MASK_POS, mask_pos_aux
+    elif gelu_aux is not None:
+        epi, aux = EPI_GELU_BWD, gelu_aux
+    return gemm(dy, w, out, T, N, K, False, True, OUT_BF16, epi, alpha, None, aux)
+
+
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
+                 db_accum: Optional[torch.Tensor] = None) -> None:
+    """dw_accum[out, in] += dy^T @ x (fp32, split-K + TMA reduce-add);  db_accum[out] += colsum(dy)."""
+    _check_2d(dy, "dy")
+    _check_2d(x, "x")
+    if not _is_cuda(dy):
+        ref.linear_wgrad(dy, x, dw_accum, db_accum)
+        return
+    T, Nout = dy.shape
+    Nin = x.shape[1]
+    gemm(dy, x, dw_accum, Nout, Nin, T, True, True, OUT_F32_ACCUM)
+    if db_accum is not None:
+        lib = _lib_required()
+        _lib.check(lib.ppb_colsum_accum(dy.data_ptr(), dy.stride(0), db_accum.data_ptr(), T, Nout, _stream()),
+                   "ppb_colsum_accum")
+        _lib.count_launch()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# fused residual + dropout + norm
+# ------------------------------------------------------------------------------------------------------------
+_scratch: dict = {}
+
+
+def _norm_scratch(device: torch.device, d: int) -> torch.Tensor:
+    lib = _lib_required()
+    key = (device.index, torch.cuda.current_stream().cuda_stream, "norm")
+    need = int(lib.ppb_norm_bwd_scratch_bytes(0, d))
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.zeros(need, dtype=torch.uint8, device=device)  # zero-filled once; the kernel self-resets
+        _scratch[key] = buf
+    return buf
+
+
+def add_dropout_norm_fwd(resid: Optional[torch.Tensor], a: Optional[torch.Tensor], gamma: torch.Tensor,
+                         beta: Optional[torch.Tensor], eps: float = 1e-5, dropout_p: float = 0.0, seed: int = 0,
+                         rms: bool = False, need_z: bool = True, out=None):
+    """z = resid + dropout(a); y = norm(z).  Returns (z, y, mean, rstd); ``out`` = optional (z, y, mean, rstd) buffers."""
+    t0 = resid if resid is not None else a
+    if not _is_cuda(t0):
+        z, y, mean, rstd = ref.add_dropout_norm_fwd(resid, a, gamma, beta, eps, dropout_p, seed, rms)
+        if out is not None:
+            for dst, src in zip(out, (z, y, mean, rstd)):
+                if dst is not None:
+                    dst.copy_(src)
+            return out
+        return z, y, mean, rstd
+    lib = _lib_required()
+    T, d = t0.shape
+    if out is None:
+        z = torch.empty_like(t0) if need_z else None
+        y = torch.empty_like(t0)
+        mean = torch.empty(T, dtype=torch.float32, device=t0.device)
+        rstd = torch.empty(T, dtype=torch.float32, device=t0.device)
+    else:
+        z, y, mean, rstd = out
+    rc = lib.ppb_add_dropout_norm_fwd(_lib.ptr(resid), _lib.ptr(a), gamma.data_ptr(), _lib.ptr(beta), _lib.ptr(z),
+                                      y.data_ptr(), _lib.ptr(mean), rstd.data_ptr(), T, d, float(eps),
+                                      float(dropout_p), int(seed) & (2**64 - 1), int(rms), _stream())
+    _lib.check(rc, "ppb_add_dropout_norm_fwd")
+    _lib.count_launch()
+    return z, y, mean, rstd
+
+
+def norm_bwd(dys: Sequence[Optional[torch.Tensor]], z: torch.Tensor, mean: Optional[torch.Tensor], rstd: torch.Tensor,
+             gamma: torch.Tensor, dgamma: torch.Tensor, dbeta: Optional[torch.Tensor], dropout_p: float = 0.0,
+             seed: int = 0, rms: bool = False, need_da: bool = True, out=None):
+    """Backward of add_dropout_norm_fwd.  dys: up to three gradients w.r.t. y (summed).  Returns (dz, da);
+    da is dz itself when there is no dropout."""
+    dys = [d for d in dys if d is not None]
+    if not _is_cuda(z):
+        dz, da = ref.norm_bwd(dys, z, mean, rstd, gamma, dgamma, dbeta, dropout_p, seed, rms, need_da)
+        if out is not None:
+            out[0].copy_(dz)
+            if da is not None and out[1] is not None:
+                out[1].copy_(da)
+                return out[0], out[1]
+            return out[0], out[0]
+        return dz, da
+    lib = _lib_required()
+    T, d = z.shape
+    if len(dys) > 3:
+        raise ValueError("norm_bwd sums at most three incoming gradients")
+    dys = dys + [None] * (3 - len(dys))
+    if out is None:
+        dz = torch.empty_like(z)
+        da = torch.empty_like(z) if (need_da and dropout_p > 0) else None
+    else:
+        dz, da = out
+        if not (need_da and dropout_p > 0):
+            da = None
+    scratch = _norm_scratch(z.device, d)
+    rc = lib.ppb_norm_bwd(dys[0].data_ptr(), _lib.ptr(dys[1]), _lib.ptr(dys[2]), z.data_ptr(), _lib.ptr(mean),
+                          rstd.data_ptr(), gamma.data_ptr(), dz.data_ptr(), _lib.ptr(da), dgamma.data_ptr(),
+                          _lib.ptr(dbeta), scratch.data_ptr(), scratch.numel(), T, d, float(dropout_p),
+                          int(seed) & (2**64 - 1), int(rms), _stream())
+    _lib.check(rc, "ppb_norm_bwd")
+    _lib.count_launch()
+    return dz, (da if da is not None else dz)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# loss
+# ------------------------------------------------------------------------------------------------------------
+def xent_fwd_bwd(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float = 1.0, write_grad: bool = True,
+                 row_loss: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Per-row cross-entropy; overwrites ``logits`` ([T, V] view, row stride % 8 == 0) with grad_scale*(softmax-onehot)."""
+    T, V = logits.shape
+    if not _is_cuda(logits):
+        loss = ref.xent_fwd_bwd(logits, targets, grad_scale, write_grad)
+        if row_loss is not None:
+            row_loss.copy_(loss)
+            return row_loss
+        return loss
+    lib = _lib_required()
+    if row_loss is None:
+        row_loss = torch.empty(T, dtype=torch.float32, device=logits.device)
+    rc = lib.ppb_xent_fwd_bwd(logits.data_ptr(), logits.stride(0), targets.data_ptr(), row_loss.data_ptr(), T, V,
+                              float(grad_scale), int(write_grad), _stream())
+    _lib.check(rc, "ppb_xent_fwd_bwd")
+    _lib.count_launch()
+    return row_loss
+
+
+def reduce_sum(x: torch.Tensor, out: torch.Tensor, scale: float = 1.0, accumulate: bool = False) -> torch.Tensor:
+    if not _is_cuda(x):
+        s = x.float().sum() * scale
+        out.copy_(out + s if accumulate else s)
+        return out
+    lib = _lib_required()
+    _lib.check(lib.ppb_reduce_sum_f32(x.data_ptr(), x.numel(), out.data_ptr(), float(scale), int(accumulate), _stream()),
+               "ppb_reduce_sum_f32")
+    _lib.count_launch()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# optimizer
+# ------------------------------------------------------------------------------------------------------------
+def adamw_step(param: Optional[torch.Tensor], master: torch.Tensor, m: torch.Tensor, v: torch.Tensor,
+               grad: torch.Tensor, lr: float, beta1: float, beta2: float, eps: float, weight_decay: float, step: int,
+               grad_scale: float = 1.0, clip_coef: Optional[torch.Tensor] = None, zero_grad: bool = True) -> None:
+    """One fused AdamW step over flat arenas (param = bf16 working copy or None; the rest fp32)."""
+    if not _is_cuda(master):
+        ref.adamw_step(param, master, m, v, grad, lr, beta1, beta2, eps, weight_decay, step, grad_scale, clip_coef,
+                       zero_grad)
+        return
+    lib = _lib_required()
+    rc = lib.ppb_adamw_step(_lib.ptr(param), master.data_ptr(), m.data_ptr(), v.data_ptr(), grad.data_ptr(),
+                            master.numel(), lr, beta1, beta2, eps, weight_decay, step, grad_scale,
+                            _lib.ptr(clip_coef), int(zero_grad), _stream())
+    _lib.check(rc, "ppb_adamw_step")
+    _lib.count_launch()
+
+
+def sumsq_accum(x: torch.Tensor, out: torch.Tensor) -> None:
+    if not _is_cuda(x):
+        out.add_((x.float() ** 2).sum())
+        return
+    lib = _lib_required()
+    _lib.check(lib.ppb_sumsq_f32(x.data_ptr(), x.numel(), out.data_ptr(), _stream()), "ppb_sumsq_f32")
+    _lib.count_launch()
+
+
+def clip_coef(sumsq: torch.Tensor, grad_scale: float, max_norm: float, coef: torch.Tensor) -> None:
+    if not _is_cuda(sumsq):
+        nrm = float(sumsq.sqrt()) * grad_scale
+        coef.fill_(min(1.0, max_norm / (nrm + 1e-6)))
+        return
+    lib = _lib_required()
+    _lib.check(lib.ppb_clip_coef(sumsq.data_ptr(), grad_scale, max_norm, coef.data_ptr(), _stream()), "ppb_clip_coef")
+    _lib.count_launch()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# embedding / small elementwise
+# ------------------------------------------------------------------------------------------------------------
+def embedding_fwd(idx: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if not _is_cuda(w):
+        y = ref.embedding_fwd(idx, w)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    lib = _lib_required()
+    T = idx.numel()
+    V, d = w.shape
+    if out is None:
+        out = torch.empty((T, d), dtype=w.dtype, device=w.device)
+    _lib.check(lib.ppb_embedding_fwd(idx.data_ptr(), w.data_ptr(), out.data_ptr(), T, d, V, _stream()),
+               "ppb_embedding_fwd")
+    _lib.count_launch()
+    return out
+
+
+def embedding_bwd(idx: torch.Tensor, dys: Sequence[Optional[torch.Tensor]], dw_accum: torch.Tensor) -> None:
+    dys = [d for d in dys if d is not None]
+    if not _is_cuda(dw_accum):
+        ref.embedding_bwd(idx, dys, dw_accum)
+        return
+    lib = _lib_required()
+    dys = dys + [None] * (3 - len(dys))
+    V, d = dw_accum.shape
+    _lib.check(lib.ppb_embedding_bwd(idx.data_ptr(), dys[0].data_ptr(), _lib.ptr(dys[1]), _lib.ptr(dys[2]),
+                                     dw_accum.data_ptr(), idx.numel(), d, V, _stream()), "ppb_embedding_bwd")
+    _lib.count_launch()
+
+
+def add_n(ts: Sequence[Optional[torch.Tensor]], out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    ts = [t for t in ts if t is not None]
+    if len(ts) == 1 and out is None:
+        return ts[0]
+    if not _is_cuda(ts[0]):
+        y = ref.add_n(ts)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    lib = _lib_required()
+    if out is None:
+        out = torch.empty_like(ts[0])
+    ts = ts + [None] * (3 - len(ts))
+    _lib.check(lib.ppb_add_n_bf16(ts[0].data_ptr(), _lib.ptr(ts[1]), _lib.ptr(ts[2]), out.data_ptr(), out.numel(),
+                                  _stream()), "ppb_add_n_bf16")
+    _lib.count_launch()
+    return out
+
+
+def gelu_fwd(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if not _is_cuda(x):
+        y = torch.nn.functional.gelu(x.float()).to(x.dtype)
+        if out is not None:
+            out.copy_(y)
+            return out
+        return y
+    lib = _lib_required()
+    if out is None:
+        out = torch.empty_like(x)
+    _lib.check(lib.ppb_gelu_fwd(x.data_ptr(), out.data_ptr(), x.numel(), _stream()), "ppb_gelu_fwd")
+    _lib.count_launch()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# attention
+# ------------------------------------------------------------------------------------------------------------
+def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, B: int, H: int, causal: bool = False,
+                  scale: Optional[float] = None, dropout_p: float = 0.0, seed: int = 0,
+                  out: Optional[torch.Tensor] = None, lse: Optional[torch.Tensor] = None):
+    """Flash attention forward.  q [B*Sq, H*dh], k/v [B*Skv, H*dh] (column-sliced views of packed QKV are fine).
+    Returns (o [B*Sq, H*dh], lse [B, H, Sq])."""
+    if not _is_cuda(q):
+        o, l = ref.attention_fwd(q, k, v, B, H, causal, scale, dropout_p, seed)
+        if out is not None:
+            out.copy_(o)
+            o = out
+        if lse is not None:
+            lse.copy_(l)
+            l = lse
+        return o, l
+    lib = _lib_required()
+    Tq, D = q.shape
+    dh = D // H
+    Sq, Skv = Tq // B, k.shape[0] // B
+    scale = scale if scale is not None else 1.0 / math.sqrt(dh)
+    if out is None:
+        out = torch.empty((Tq, D), dtype=q.dtype, device=q.device)
+    if lse is None:
+        lse = torch.empty((B, H, Sq), dtype=torch.float32, device=q.device)
+    rc = lib.ppb_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), lse.data_ptr(), B, H, Sq, Skv, dh,
+                          q.stride(0), k.stride(0), v.stride(0), out.stride(0), int(causal), 0, 0, float(scale),
+                          float(dropout_p), int(seed) & (2**64 - 1), _stream())
+    _lib.check(rc, "ppb_attn_fwd")
+    _lib.count_launch()
+    return out, lse
+
+
+def _attn_scratch(device: torch.device, B: int, H: int, Sq: int, dh: int) -> torch.Tensor:
+    lib = _lib_required()
+    need = int(lib.ppb_attn_bwd_scratch_bytes(B, H, Sq, dh))
+    key = (device.index, torch.cuda.current_stream().cuda_stream, "attn")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def attention_bwd(q, k, v, o, do, lse, B: int, H: int, causal: bool = False, scale: Optional[float] = None,
+                  dropout_p: float = 0.0, seed: int = 0, out=None):
+    """Flash attention backward -> (dq, dk, dv) with the layouts of q, k, v (``out`` = optional views to fill)."""
+    if not _is_cuda(q):
+        dq, dk, dv = ref.attention_bwd(q, k, v, o, do, lse, B, H, causal, scale, dropout_p, seed)
+        if out is not None:
+            out[0].copy_(dq)
+            out[1].copy_(dk)
+            out[2].copy_(dv)
+            return out
+        return dq, dk, dv
+    lib = _lib_required()
+    Tq, D = q.shape
+    dh = D // H
+    Sq, Skv = Tq // B, k.shape[0] // B
+    scale = scale if scale is not None else 1.0 / math.sqrt(dh)
+    if out is None:
+        dq = torch.empty((Tq, D), dtype=q.dtype, device=q.device)
+        dk = torch.empty((k.shape[0], D), dtype=q.dtype, device=q.device)
+        dv = torch.empty((k.shape[0], D), dtype=q.dtype, device=q.device)
+    else:
+        dq, dk, dv = out
+    if dq.stride(0) != q.stride(0) or dk.stride(0) != k.stride(0) or dv.stride(0) != v.stride(0) or do.stride(0) != o.stride(0):
+        raise ValueError("attention_bwd: gradient buffers must share the row stride of their forward tensors")
+    scratch = _attn_scratch(q.device, B, H, Sq, dh)
+    rc = lib.ppb_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
+                          dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), scratch.data_ptr(), 0, B, H, Sq, Skv, dh,
+                          q.stride(0), k.stride(0), v.stride(0), o.stride(0), int(causal), 0, 0, float(scale),
+                          float(dropout_p), int(seed) & (2**64 - 1), _stream())
+    _lib.check(rc, "ppb_attn_bwd")
+    _lib.count_launch(3)
+    return dq, dk, dv

@@ -1,0 +1,87 @@
+/* libppb200 -- C ABI of the sm_100a kernel library behind the pipeline-parallel training framework.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; ppb_last_error() returns the message of the
+ *     last failure on the calling thread;
+ *   - all pointers are device pointers on the CURRENT device unless stated otherwise; `stream` is a
+ *     cudaStream_t passed as void*; nothing synchronises the host;
+ *   - bf16 tensors are row-major with a leading dimension (`ld*`, in elements) that keeps rows 16-byte aligned;
+ *   - "accum" outputs are fp32 and are added to (they persist across micro-batches);
+ *   - no function allocates device memory: work space is passed in by the caller.
+ *
+ * The reference (aa5490/Distributed-Training-with-Pipeline-Parallelism) has no native code; each entry point
+ * cites the op(s) of the reference's ATen op stream it replaces.
+ */
+#ifndef PPB200_H_
+#define PPB200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ppb_last_error(void);
+int ppb_version(void);
+
+/* ---- K1/K2/K3: tcgen05 GEMM ------------------------------------------------------------------------------
+ * C[M,N] (=|+=) epilogue(alpha * op(A)[M,K] * op(B)[N,K]^T)
+ *   a_mn_major = 0: A is stored [M, lda] (K contiguous);  1: A is stored [K, lda] (M contiguous)
+ *   b_mn_major = 0: B is stored [N, ldb] (K contiguous);  1: B is stored [K, ldb] (N contiguous)
+ * forward x*W^T: (0,0); dgrad dy*W: (0,1); wgrad dy^T*x: (1,1).
+ * Replaces aten.mm / aten.addmm (+ bias add, relu, dropout) -- helper:40-46, torch transformer.py:1143-1199. */
+enum { PPB_OUT_BF16 = 0, PPB_OUT_F32 = 1, PPB_OUT_F32_ACCUM = 2 };
+enum {
+  PPB_EPI_NONE = 0,
+  PPB_EPI_BIAS = 1,              /* + bias[n]                                      */
+  PPB_EPI_BIAS_RELU = 2,         /* relu(. + bias)                                 */
+  PPB_EPI_BIAS_GELU = 3,         /* gelu_erf(. + bias)                             */
+  PPB_EPI_BIAS_RELU_DROPOUT = 4, /* dropout(relu(. + bias)), mask from (seed, m*N+n) */
+  PPB_EPI_MASK_POS = 5,          /* . * (aux[m,n] > 0)   (ReLU(+dropout) backward; pass alpha = 1/(1-p)) */
+  PPB_EPI_GELU_BWD = 6           /* . * gelu'(aux[m,n])  (aux = pre-activation)    */
+};
+int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                  long long ldc, int a_mn_major, int b_mn_major, int out_mode, int epi, float alpha, const void* bias,
+                  const void* aux, long long ld_aux, unsigned long long seed, float dropout_p, int force_bn,
+                  int force_splits, void* stream);
+
+/* ---- K5: fused residual-add + dropout + LayerNorm / RMSNorm ------------------------------------------------
+ * fwd: z = resid + dropout(a); y = norm(z)*gamma(+beta).  Either of resid / a may be NULL; z, mean may be NULL.
+ * bwd: dy = dy0(+dy1+dy2); dz = norm'(dy); da = dropout'(dz) (da may be NULL); dgamma/dbeta are fp32 accum.
+ * `scratch` needs ppb_norm_bwd_scratch_bytes() bytes, zero-filled once; concurrent launches must not share it.
+ * Replaces aten.add + bernoulli_/div_/mul + native_layer_norm(_backward) -- torch transformer.py:1144-1153. */
+int ppb_add_dropout_norm_fwd(const void* resid, const void* a, const void* gamma, const void* beta, void* z, void* y,
+                             float* mean, float* rstd, int T, int d, float eps, float dropout_p,
+                             unsigned long long seed, int rms, void* stream);
+long long ppb_norm_bwd_scratch_bytes(int T, int d);
+int ppb_norm_bwd(const void* dy0, const void* dy1, const void* dy2, const void* z, const float* mean,
+                 const float* rstd, const void* gamma, void* dz, void* da, float* dgamma, float* dbeta, void* scratch,
+                 long long scratch_bytes, int T, int d, float dropout_p, unsigned long long seed, int rms,
+                 void* stream);
+
+/* ---- K7: fused softmax-cross-entropy (loss rows + in-place dlogits) ----------------------------------------
+ * Replaces aten._log_softmax + nll_loss_forward/backward + logits.clone() -- helper:54, helper:197-201. */
+int ppb_xent_fwd_bwd(void* logits, long long ld, const long long* targets, float* row_loss, int T, int V,
+                     float grad_scale, int write_grad, void* stream);
+int ppb_reduce_sum_f32(const float* in, long long n, float* out, float scale, int accumulate, void* stream);
+
+/* ---- K9: fused AdamW over flat arenas (+ micro-batch grad averaging, + global-norm clip, + grad zeroing) ----
+ * The reference has no optimizer (helper:113-131); grad averaging replaces p.grad.div_(m), torch stage.py:589. */
+int ppb_adamw_step(void* param_bf16, float* master, float* m, float* v, float* grad, long long n, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale,
+                   const float* clip_coef, int zero_grad, void* stream);
+int ppb_sumsq_f32(const float* x, long long n, float* out, void* stream);
+int ppb_clip_coef(const float* sumsq, float grad_scale, float max_norm, float* coef, void* stream);
+
+/* ---- K6/K8: embedding, bias-grad, fan-in add, GELU, cast ---------------------------------------------------
+ * Replaces aten.embedding / embedding_dense_backward (helper:36,50), aten.sum.dim_IntList, aten.add.Tensor. */
+int ppb_embedding_fwd(const long long* idx, const void* W, void* out, int T, int d, int V, void* stream);
+int ppb_embedding_bwd(const long long* idx, const void* dy0, const void* dy1, const void* dy2, float* dW, int T, int d,
+                      int V, void* stream);
+int ppb_colsum_accum(const void* dy, long long ld, float* db, int T, int N, void* stream);
+int ppb_add_n_bf16(const void* a, const void* b, const void* c, void* out, long long n, void* stream);
+int ppb_gelu_fwd(const void* x, void* y, long long n, void* stream);
+int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PPB200_H_ */

@@ -1,0 +1,186 @@
+"""Numerics of every sm_100a kernel against the plain PyTorch fp32 reference of the same op (SURVEY.md section 4,
+"Kernel unit tests").  Shapes are the real shapes of SURVEY.md section 8 plus ragged edge cases."""
+import math
+
+import pytest
+import torch
+
+from ppb200.ops import functional as F
+from ppb200.ops import reference as R
+from ppb200.ops import _lib
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel_err(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def test_library_loaded():
+    assert _lib.load(required=True) is not None
+
+
+@pytest.mark.parametrize("M,N,K", [(1024, 2304, 768), (4096, 1024, 1024), (300, 200, 136), (128, 64, 64), (1024, 10000, 768)])
+@pytest.mark.parametrize("bn", [0, 64, 128, 256])
+def test_gemm_tn(M, N, K, bn):
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    b = torch.randn(N, K, device=DEV, dtype=torch.bfloat16)
+    ldc = F.pad8(N)
+    cbuf = torch.zeros(M, ldc, device=DEV, dtype=torch.bfloat16)
+    c = cbuf[:, :N]
+    F.gemm(a, b, c, M, N, K, False, False, force_bn=bn)
+    ref = a.float() @ b.float().t()
+    assert rel_err(c, ref) < 5e-3
+    if ldc > N:
+        assert cbuf[:, N:].abs().max().item() == 0  # TMA store clipped at N
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(512, 768, 1024), (200, 136, 264)])
+def test_gemm_majors(a_mn, b_mn, M, N, K):
+    torch.manual_seed(1)
+    a = torch.randn((K, M) if a_mn else (M, K), device=DEV, dtype=torch.bfloat16)
+    b = torch.randn((K, N) if b_mn else (N, K), device=DEV, dtype=torch.bfloat16)
+    c = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    F.gemm(a, b, c, M, N, K, a_mn, b_mn)
+    af = a.float().t() if a_mn else a.float()
+    bf = b.float().t() if b_mn else b.float()
+    assert rel_err(c, af @ bf.t()) < 5e-3
+
+
+@pytest.mark.parametrize("act,p", [(None, 0.0), ("relu", 0.0), ("gelu", 0.0), ("relu", 0.1)])
+def test_linear_fwd_epilogues(act, p):
+    torch.manual_seed(2)
+    T, K, N = 1024, 768, 2048
+    x = torch.randn(T, K, device=DEV, dtype=torch.bfloat16)
+    w = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.05
+    b = torch.randn(N, device=DEV, dtype=torch.bfloat16)
+    y = F.linear_fwd(x, w, b, act, p, seed=1234)
+    ref = R.linear_fwd(x, w, b, act, p, seed=1234)
+    assert rel_err(y, ref) < 1e-2
+    if p > 0:
+        frac = (y == 0).float().mean().item()
+        assert 0.5 < frac < 0.6  # relu zeros ~50% + dropout 10% of the rest
+
+
+def test_linear_dgrad_wgrad():
+    torch.manual_seed(3)
+    T, Nin, Nout = 1024, 768, 2048
+    x = torch.randn(T, Nin, device=DEV, dtype=torch.bfloat16)
+    w = torch.randn(Nout, Nin, device=DEV, dtype=torch.bfloat16) * 0.05
+    dy = torch.randn(T, Nout, device=DEV, dtype=torch.bfloat16)
+    h = torch.relu(torch.randn(T, Nin, device=DEV)).to(torch.bfloat16)
+    dx = F.linear_dgrad(dy, w)
+    assert rel_err(dx, dy.float() @ w.float()) < 5e-3
+    dxm = F.linear_dgrad(dy, w, mask_pos_aux=h, alpha=1.0 / 0.9)
+    assert rel_err(dxm, R.linear_dgrad(dy, w, mask_pos_aux=h, alpha=1.0 / 0.9)) < 5e-3
+    dxg = F.linear_dgrad(dy, w, gelu_aux=h)
+    assert rel_err(dxg, R.linear_dgrad(dy, w, gelu_aux=h)) < 5e-3
+    dw = torch.zeros(Nout, Nin, device=DEV)
+    db = torch.zeros(Nout, device=DEV)
+    F.linear_wgrad(dy, x, dw, db)
+    F.linear_wgrad(dy, x, dw, db)  # accumulates
+    assert rel_err(dw, 2 * (dy.float().t() @ x.float())) < 5e-3
+    assert rel_err(db, 2 * dy.float().sum(0)) < 5e-3
+
+
+@pytest.mark.parametrize("M,N,K,splits", [(1024, 1024, 4096, 0), (768, 768, 1024, 3), (2048, 768, 8192, 0)])
+def test_wgrad_splitk(M, N, K, splits):
+    torch.manual_seed(4)
+    dy = torch.randn(K, M, device=DEV, dtype=torch.bfloat16)
+    x = torch.randn(K, N, device=DEV, dtype=torch.bfloat16)
+    dw = torch.ones(M, N, device=DEV)
+    F.gemm(dy, x, dw, M, N, K, True, True, F.OUT_F32_ACCUM, force_splits=splits)
+    assert rel_err(dw, 1 + dy.float().t() @ x.float()) < 5e-3
+
+
+@pytest.mark.parametrize("T,d", [(1024, 768), (4096, 1024), (333, 1600), (64, 256)])
+@pytest.mark.parametrize("p", [0.0, 0.1])
+@pytest.mark.parametrize("rms", [False, True])
+def test_add_dropout_norm(T, d, p, rms):
+    torch.manual_seed(5)
+    resid = torch.randn(T, d, device=DEV, dtype=torch.bfloat16)
+    a = torch.randn(T, d, device=DEV, dtype=torch.bfloat16)
+    g = (1 + 0.1 * torch.randn(d, device=DEV)).to(torch.bfloat16)
+    b = None if rms else (0.1 * torch.randn(d, device=DEV)).to(torch.bfloat16)
+    z, y, mean, rstd = F.add_dropout_norm_fwd(resid, a, g, b, 1e-5, p, seed=77, rms=rms)
+    zr, yr, meanr, rstdr = R.add_dropout_norm_fwd(resid, a, g, b, 1e-5, p, seed=77, rms=rms)
+    assert rel_err(z, zr) < 1e-3
+    assert rel_err(y, yr) < 1e-2
+    assert rel_err(rstd, rstdr) < 1e-3
+    dys = [torch.randn(T, d, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    dg, dbt = torch.zeros(d, device=DEV), (None if rms else torch.zeros(d, device=DEV))
+    dgr, dbr = torch.zeros(d, device=DEV), (None if rms else torch.zeros(d, device=DEV))
+    for _ in range(2):  # twice: accumulators add up and the scratch self-resets
+        dz, da = F.norm_bwd(dys, z, mean, rstd, g, dg, dbt, p, seed=77, rms=rms)
+        dzr, dar = R.norm_bwd(dys, zr, meanr, rstdr, g, dgr, dbr, p, seed=77, rms=rms)
+    assert rel_err(dz, dzr) < 1e-2
+    assert rel_err(da, dar) < 1e-2
+    assert rel_err(dg, dgr) < 1e-2
+    if not rms:
+        assert rel_err(dbt, dbr) < 1e-2
+
+
+@pytest.mark.parametrize("T,V", [(1024, 10000), (512, 50257), (64, 32000), (8, 120000)])
+def test_xent(T, V):
+    torch.manual_seed(6)
+    ld = F.pad8(V)
+    buf = torch.zeros(T, ld, device=DEV, dtype=torch.bfloat16)
+    logits = buf[:, :V]
+    logits.copy_(torch.randn(T, V, device=DEV) * 3)
+    tgt = torch.randint(0, V, (T,), device=DEV)
+    lref = logits.clone()
+    loss_ref = R.xent_fwd_bwd(lref, tgt, 0.5)
+    loss = F.xent_fwd_bwd(logits, tgt, 0.5)
+    assert rel_err(loss, loss_ref) < 1e-3
+    assert rel_err(logits, lref) < 2e-2
+    out = torch.zeros(1, device=DEV)
+    F.reduce_sum(loss, out, 1.0 / T)
+    assert abs(out.item() - loss_ref.mean().item()) < 1e-3 * abs(loss_ref.mean().item())
+
+
+def test_adamw():
+    torch.manual_seed(7)
+    n = 1_000_003
+    master = torch.randn(n, device=DEV)
+    grad = torch.randn(n, device=DEV)
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    param = master.to(torch.bfloat16)
+    mr, gr, mmr, vr = master.clone(), grad.clone(), m.clone(), v.clone()
+    pr = param.clone()
+    coef = torch.tensor([0.5], device=DEV)
+    for step in (1, 2):
+        F.adamw_step(param, master, m, v, grad, 1e-3, 0.9, 0.95, 1e-8, 0.1, step, 0.25, coef, zero_grad=False)
+        R.adamw_step(pr, mr, mmr, vr, gr, 1e-3, 0.9, 0.95, 1e-8, 0.1, step, 0.25, coef, zero_grad=False)
+    assert rel_err(master, mr) < 1e-5
+    assert rel_err(param, pr) < 1e-3
+    assert rel_err(v, vr) < 1e-5
+    F.adamw_step(param, master, m, v, grad, 1e-3, 0.9, 0.95, 1e-8, 0.1, 3, 1.0, None, zero_grad=True)
+    assert grad.abs().max().item() == 0
+    ss = torch.zeros(1, device=DEV)
+    F.sumsq_accum(gr, ss)
+    assert abs(ss.item() - (gr ** 2).sum().item()) < 1e-3 * ss.item()
+    c = torch.zeros(1, device=DEV)
+    F.clip_coef(ss, 1.0, 1.0, c)
+    assert abs(c.item() - min(1.0, 1.0 / math.sqrt(ss.item()))) < 1e-5
+
+
+def test_embedding_and_small_ops():
+    torch.manual_seed(8)
+    V, d, T = 10000, 768, 1024
+    w = torch.randn(V, d, device=DEV, dtype=torch.bfloat16)
+    idx = torch.randint(0, V, (8, 128), device=DEV)
+    out = F.embedding_fwd(idx, w)
+    assert torch.equal(out, w[idx.reshape(-1)])
+    dys = [torch.randn(T, d, device=DEV, dtype=torch.bfloat16) for _ in range(3)]
+    dw, dwr = torch.zeros(V, d, device=DEV), torch.zeros(V, d, device=DEV)
+    F.embedding_bwd(idx, dys, dw)
+    R.embedding_bwd(idx, dys, dwr)
+    assert rel_err(dw, dwr) < 1e-5
+    s = F.add_n(dys)
+    assert rel_err(s, R.add_n(dys)) < 1e-2
+    g = F.gelu_fwd(dys[0])
+    assert rel_err(g, torch.nn.functional.gelu(dys[0].float())) < 1e-2
