@@ -421,9 +421,10 @@ def attention_bwd(q, k, v, o, do, lse, B: int, H: int, causal: bool = False, sca
     Sq, Skv = Tq // B, k.shape[0] // B
     scale = scale if scale is not None else 1.0 / math.sqrt(dh)
     if out is None:
-        dq = torch.empty((Tq, D), dtype=q.dtype, device=q.device)
-        dk = torch.empty((k.shape[0], D), dtype=q.dtype, device=q.device)
-        dv = torch.empty((k.shape[0], D), dtype=q.dtype, device=q.device)
+        # the kernel addresses dq/dk/dv with the row strides of q/k/v
+        dq = torch.empty((Tq, q.stride(0)), dtype=q.dtype, device=q.device)[:, :D]
+        dk = torch.empty((k.shape[0], k.stride(0)), dtype=q.dtype, device=q.device)[:, :D]
+        dv = torch.empty((k.shape[0], v.stride(0)), dtype=q.dtype, device=q.device)[:, :D]
     else:
         dq, dk, dv = out
     if dq.stride(0) != q.stride(0) or dk.stride(0) != k.stride(0) or dv.stride(0) != v.stride(0) or do.stride(0) != o.stride(0):

@@ -184,3 +184,50 @@ def test_embedding_and_small_ops():
     assert rel_err(s, R.add_n(dys)) < 1e-2
     g = F.gelu_fwd(dys[0])
     assert rel_err(g, torch.nn.functional.gelu(dys[0].float())) < 1e-2
+
+
+ATTN_CASES = [
+    # B, H, Sq, Skv, dh, causal, p
+    (2, 4, 256, 256, 64, False, 0.0),
+    (2, 4, 256, 256, 64, True, 0.0),
+    (2, 4, 256, 256, 64, False, 0.1),
+    (8, 8, 128, 128, 96, False, 0.1),
+    (1, 2, 1024, 1024, 64, True, 0.1),
+    (2, 2, 384, 384, 128, True, 0.0),
+    (2, 3, 200, 200, 64, False, 0.0),
+    (2, 3, 136, 328, 64, False, 0.0),
+    (1, 4, 128, 128, 32, False, 0.0),
+]
+
+
+def _attn_inputs(B, H, Sq, Skv, dh):
+    torch.manual_seed(9)
+    D = H * dh
+    qbuf = torch.randn(B * Sq, 3 * D, device=DEV, dtype=torch.bfloat16)
+    kvbuf = torch.randn(B * Skv, 3 * D, device=DEV, dtype=torch.bfloat16)
+    return qbuf[:, :D], kvbuf[:, D:2 * D], kvbuf[:, 2 * D:]
+
+
+@pytest.mark.parametrize("B,H,Sq,Skv,dh,causal,p", ATTN_CASES)
+def test_attention_fwd(B, H, Sq, Skv, dh, causal, p):
+    q, k, v = _attn_inputs(B, H, Sq, Skv, dh)
+    o, lse = F.attention_fwd(q, k, v, B, H, causal, None, p, seed=42)
+    oref, lref = R.attention_fwd(q, k, v, B, H, causal, None, p, seed=42)
+    assert rel_err(lse, lref) < 1e-3
+    assert rel_err(o, oref) < 2e-2
+
+
+@pytest.mark.parametrize("B,H,Sq,Skv,dh,causal,p", ATTN_CASES)
+def test_attention_bwd(B, H, Sq, Skv, dh, causal, p):
+    q, k, v = _attn_inputs(B, H, Sq, Skv, dh)
+    o, lse = F.attention_fwd(q, k, v, B, H, causal, None, p, seed=42)
+    torch.manual_seed(10)
+    do = torch.randn_like(o)
+    dq, dk, dv = F.attention_bwd(q, k, v, o, do, lse, B, H, causal, None, p, seed=42)
+    dqr, dkr, dvr = R.attention_bwd(q, k, v, o, do, lse, B, H, causal, None, p, seed=42)
+    assert rel_err(dv, dvr) < 2e-2
+    assert rel_err(dk, dkr) < 2e-2
+    assert rel_err(dq, dqr) < 2e-2
+    # second call re-uses (and re-zeroes) the scratch accumulator
+    dq2, _, _ = F.attention_bwd(q, k, v, o, do, lse, B, H, causal, None, p, seed=42)
+    assert rel_err(dq2, dqr) < 2e-2
