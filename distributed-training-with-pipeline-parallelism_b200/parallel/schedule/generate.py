@@ -1,0 +1,305 @@
+"""Schedule generators and lowering passes (pure Python, no process group needed).
+
+    compute order  ->  + REDUCE_GRAD  ->  (+ ALLREDUCE)  ->  + SEND/RECV  ->  (+ OPTIM)  ->  validate
+
+Behavioural spec: GPipe = torch schedules.py:684-800 (T4), 1F1B = :803-1044 (T5),
+Interleaved-1F1B = :2351-2618 (T10), lowering passes = :1047-1451 (T7).  The reference picks between them by
+name, /root/reference/LLMsDistributedTrainingHelper.py:215-220.  Everything here is an independent
+implementation: the generators are closed-form, the comm lowering is a round-robin list scheduler in which the
+SENDER places the receiver's RECV (that is what makes the resulting per-rank orders deadlock-free).
+"""
+from __future__ import annotations
+
+from collections import defaultdict
+from typing import Callable, Dict, List, Optional, Sequence
+
+from .ir import Action, ActionType as T
+
+Order = Dict[int, List[Action]]
+
+SCHEDULES = ("GPipe", "1F1B", "Interleaved1F1B")
+
+
+def stage_to_rank_loop(pp_size: int) -> Callable[[int], int]:
+    """'Loop' placement used by the reference for virtual stages: stage s lives on rank s % P
+    (helper:208 ``stage_idx = rank + world_size * i``; torch schedules.py T8)."""
+    return lambda s: s % pp_size
+
+
+# ------------------------------------------------------------------------------------------------------------
+# compute orders
+# ------------------------------------------------------------------------------------------------------------
+def gpipe_order(pp_size: int, n_microbatches: int) -> Order:
+    """All forwards, then all backwards in micro-batch order 0..m-1 (torch ScheduleGPipe runs the backward loop
+    in the same order as the forward loop)."""
+    m = n_microbatches
+    return {r: [Action(r, T.F, i) for i in range(m)] + [Action(r, T.B, i) for i in range(m)] for r in range(pp_size)}
+
+
+def one_f_one_b_order(pp_size: int, n_microbatches: int) -> Order:
+    """Warm-up of min(m, P - rank) forwards, then strictly alternating 1B-1F, then the backward drain."""
+    m = n_microbatches
+    if m < pp_size:
+        raise ValueError(f"1F1B needs n_microbatches ({m}) >= number of stages ({pp_size})")
+    order: Order = {}
+    for r in range(pp_size):
+        warm = min(m, pp_size - r)
+        acts = [Action(r, T.F, i) for i in range(warm)]
+        f, b = warm, 0
+        while b < m:
+            acts.append(Action(r, T.B, b))
+            b += 1
+            if f < m:
+                acts.append(Action(r, T.F, f))
+                f += 1
+        order[r] = acts
+    return order
+
+
+def interleaved_order(pp_size: int, n_virtual: int, n_microbatches: int) -> Order:
+    """Depth-first interleaved 1F1B with ``n_virtual`` stages per rank placed loop-wise.
+
+    rounds = max(1, m // P); micro-batches are processed in groups of m // rounds per virtual stage.
+    Rank r warms up with (v-1)*mb_per_round + 2*(P-1-r) forwards (capped at m*v), then runs (F, B) pairs and
+    drains the remaining backwards."""
+    P, v, m = pp_size, n_virtual, n_microbatches
+    rounds = max(1, m // P)
+    if m % rounds != 0:
+        raise ValueError(f"Interleaved1F1B needs n_microbatches ({m}) divisible by the number of rounds ({rounds})")
+    per_round = m // rounds
+    total = m * v
+    order: Order = {}
+    for r in range(P):
+        warm = min((v - 1) * per_round + 2 * (P - 1 - r), total)
+        fwd_mb: Dict[int, int] = defaultdict(int)
+        bwd_mb: Dict[int, int] = defaultdict(int)
+
+        def fwd_stage(step: int) -> int:
+            return ((step // per_round) % v) * P + r
+
+        def bwd_stage(step: int) -> int:
+            return (v - 1 - ((step - warm) // per_round) % v) * P + r
+
+        acts: List[Action] = []
+
+        def emit_f(step: int) -> None:
+            s = fwd_stage(step)
+            acts.append(Action(s, T.F, fwd_mb[s]))
+            fwd_mb[s] += 1
+
+        def emit_b(step: int) -> None:
+            s = bwd_stage(step)
+            acts.append(Action(s, T.B, bwd_mb[s]))
+            bwd_mb[s] += 1
+
+        for step in range(warm):
+            emit_f(step)
+        for step in range(warm, total):
+            emit_f(step)
+            emit_b(step)
+        for step in range(total, total + warm):
+            emit_b(step)
+        order[r] = acts
+    return order
+
+
+# ------------------------------------------------------------------------------------------------------------
+# lowering passes
+# ------------------------------------------------------------------------------------------------------------
+def add_reduce_grad(order: Order, n_microbatches: int, also_allreduce: bool = False) -> Order:
+    """Insert ``{s}REDUCE_GRAD`` right after a stage's m-th backward (B or W) -- and, for data-parallel replicas,
+    ``{s}ALLREDUCE`` right behind it, which is what lets the gradient all-reduce of the later stages hide inside
+    the 1F1B cool-down of the earlier ones."""
+    out: Order = {}
+    for r, acts in order.items():
+        seen: Dict[int, int] = defaultdict(int)
+        res: List[Action] = []
+        for a in acts:
+            res.append(a)
+            if a.type in (T.B, T.W):
+                seen[a.stage] += 1
+                if seen[a.stage] == n_microbatches:
+                    res.append(Action(a.stage, T.REDUCE_GRAD))
+                    if also_allreduce:
+                        res.append(Action(a.stage, T.ALLREDUCE))
+        out[r] = res
+    return out
+
+
+def add_unshard_reshard(order: Order, max_active_stages: int = 3) -> Order:
+    """Insert UNSHARD / RESHARD slots with a look-ahead residency policy: before each compute action the next
+    ``max_active_stages`` distinct stages must be resident; resident stages outside that window are released
+    first, everything is released at the end.  Without FSDP the slots do nothing at run time, but they take a
+    turn in the comm-lowering round-robin, which keeps the lowered order string-identical to the golden vectors
+    of SURVEY.md section 3.5 (torch inserts the same slots, schedules.py:1084-1164)."""
+    out: Order = {}
+    for r, acts in order.items():
+        active: List[int] = []
+        res: List[Action] = []
+        for i, a in enumerate(acts):
+            window: List[int] = []
+            for nxt in acts[i:]:
+                if nxt.stage not in window:
+                    window.append(nxt.stage)
+                    if len(window) == max_active_stages:
+                        break
+            for s in [s for s in active if s not in window]:
+                active.remove(s)
+                res.append(Action(s, T.RESHARD))
+            for s in window:
+                if s not in active:
+                    active.append(s)
+                    res.append(Action(s, T.UNSHARD))
+            res.append(a)
+        for s in list(active):
+            res.append(Action(s, T.RESHARD))
+        out[r] = res
+    return out
+
+
+def strip_fsdp_slots(order: Order) -> Order:
+    return {r: [a for a in acts if a.type not in (T.UNSHARD, T.RESHARD)] for r, acts in order.items()}
+
+
+def add_optimizer(order: Order) -> Order:
+    """Append one ``{s}OPTIM`` per local stage at the end of each rank's list."""
+    out: Order = {}
+    for r, acts in order.items():
+        stages = sorted({a.stage for a in acts if a.type in (T.F, T.B, T.I, T.W)})
+        out[r] = list(acts) + [Action(s, T.OPTIM) for s in stages]
+    return out
+
+
+def add_send_recv(order: Order, stage_to_rank: Callable[[int], int], num_stages: int) -> Order:
+    """Insert SEND/RECV actions.  Ranks are visited round-robin; a rank may emit its next compute action only
+    when the data it consumes has been produced (its RECV is already in its list, or the producing stage is
+    local).  When an action with a remote consumer is emitted, its SEND goes right behind it and the matching
+    RECV is appended to the CONSUMER's list at that moment.  Adjacent stages on the same rank exchange tensors
+    directly (no comm actions)."""
+    pending = {r: list(a) for r, a in order.items() if a}
+    out: Order = {r: [] for r in order}
+    done: Dict[int, set] = {r: set() for r in order}
+
+    def remote_consumer(a: Action) -> Optional[Action]:
+        if a.type == T.F and a.stage != num_stages - 1 and stage_to_rank(a.stage + 1) != stage_to_rank(a.stage):
+            return Action(a.stage + 1, T.RECV_F, a.mb)
+        if a.type in (T.B, T.I) and a.stage != 0 and stage_to_rank(a.stage - 1) != stage_to_rank(a.stage):
+            return Action(a.stage - 1, T.RECV_B, a.mb)
+        return None
+
+    def ready(a: Action, have: set) -> bool:
+        if a.type == T.F and a.stage != 0:
+            return Action(a.stage, T.RECV_F, a.mb) in have or Action(a.stage - 1, T.F, a.mb) in have
+        if a.type in (T.B, T.I) and a.stage != num_stages - 1:
+            return (Action(a.stage, T.RECV_B, a.mb) in have or Action(a.stage + 1, T.B, a.mb) in have
+                    or Action(a.stage + 1, T.I, a.mb) in have)
+        return True
+
+    while pending:
+        progress = False
+        for r in sorted(pending):
+            a = pending[r][0]
+            if not ready(a, done[r]):
+                continue
+            out[r].append(a)
+            done[r].add(a)
+            recv = remote_consumer(a)
+            if recv is not None:
+                send = Action(a.stage, T.SEND_F if a.type == T.F else T.SEND_B, a.mb)
+                out[r].append(send)
+                done[r].add(send)
+                dst = stage_to_rank(recv.stage)
+                out[dst].append(recv)
+                done[dst].add(recv)
+            pending[r].pop(0)
+            if not pending[r]:
+                del pending[r]
+            progress = True
+        if not progress:
+            raise RuntimeError("malformed compute schedule: no rank can make progress while placing sends/recvs\n"
+                               + "\n".join(f"rank{r}: next={pending[r][0]}" for r in sorted(pending)))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# validation + theory
+# ------------------------------------------------------------------------------------------------------------
+def validate_schedule(order: Order, num_stages: int, n_microbatches: int,
+                      stage_to_rank: Optional[Callable[[int], int]] = None) -> None:
+    """Raise ValueError unless every stage runs every micro-batch exactly once forward and once backward, on the
+    right rank, forward before backward, and every SEND has exactly one matching RECV on the consumer's rank."""
+    f_seen: Dict[tuple, int] = {}
+    b_seen: Dict[tuple, int] = {}
+    sends, recvs = set(), set()
+    for r, acts in order.items():
+        pos: Dict[Action, int] = {}
+        for i, a in enumerate(acts):
+            if a in pos and a.type not in (T.REDUCE_GRAD, T.ALLREDUCE, T.OPTIM):
+                raise ValueError(f"rank {r}: duplicate action {a}")
+            pos[a] = i
+            if stage_to_rank is not None and stage_to_rank(a.stage) != r:
+                raise ValueError(f"rank {r}: action {a} belongs to rank {stage_to_rank(a.stage)}")
+            if a.type == T.F:
+                f_seen[(a.stage, a.mb)] = f_seen.get((a.stage, a.mb), 0) + 1
+            elif a.type in (T.B, T.I):
+                b_seen[(a.stage, a.mb)] = b_seen.get((a.stage, a.mb), 0) + 1
+                if Action(a.stage, T.F, a.mb) not in pos:
+                    raise ValueError(f"rank {r}: {a} before its forward")
+            elif a.type in (T.SEND_F, T.SEND_B):
+                sends.add((a.type, a.stage, a.mb))
+                src = Action(a.stage, T.F if a.type == T.SEND_F else T.B, a.mb)
+                if src not in pos and Action(a.stage, T.I, a.mb) not in pos:
+                    raise ValueError(f"rank {r}: {a} before the compute that produces it")
+            elif a.type in (T.RECV_F, T.RECV_B):
+                recvs.add((a.type, a.stage, a.mb))
+        for a, i in pos.items():  # a consumer must come after its RECV
+            if a.type == T.F and Action(a.stage, T.RECV_F, a.mb) in pos and pos[Action(a.stage, T.RECV_F, a.mb)] > i:
+                raise ValueError(f"rank {r}: {a} before its RECV_F")
+            if a.type in (T.B, T.I) and Action(a.stage, T.RECV_B, a.mb) in pos and pos[Action(a.stage, T.RECV_B, a.mb)] > i:
+                raise ValueError(f"rank {r}: {a} before its RECV_B")
+    for s in range(num_stages):
+        for mb in range(n_microbatches):
+            if f_seen.get((s, mb), 0) != 1:
+                raise ValueError(f"stage {s} micro-batch {mb}: {f_seen.get((s, mb), 0)} forwards (want 1)")
+            if b_seen.get((s, mb), 0) != 1:
+                raise ValueError(f"stage {s} micro-batch {mb}: {b_seen.get((s, mb), 0)} backwards (want 1)")
+    for typ, s, mb in sends:
+        want = (T.RECV_F, s + 1, mb) if typ == T.SEND_F else (T.RECV_B, s - 1, mb)
+        if want not in recvs:
+            raise ValueError(f"{s}{typ.value}{mb} has no matching receive")
+    if len(sends) != len(recvs):
+        raise ValueError(f"{len(sends)} sends vs {len(recvs)} receives")
+
+
+def theoretical_bubble(pp_size: int, n_microbatches: int, n_virtual: int = 1) -> float:
+    """(p-1)/(v*m+p-1): GPipe and 1F1B have v = 1 (BASELINE.json bound)."""
+    p, m, v = pp_size, n_microbatches, n_virtual
+    return (p - 1) / (v * m + p - 1)
+
+
+def build_schedule(name: str, pp_size: int, n_microbatches: int, n_virtual: int = 1, dp_allreduce: bool = False,
+                   with_optimizer: bool = True, keep_fsdp_slots: bool = False) -> Order:
+    """Full lowering for one of 'GPipe' | '1F1B' | 'Interleaved1F1B' (names of helper:215-219)."""
+    if name == "GPipe":
+        if n_virtual != 1:
+            raise ValueError("GPipe runs one stage per rank")
+        order = gpipe_order(pp_size, n_microbatches)
+    elif name == "1F1B":
+        if n_virtual != 1:
+            raise ValueError("1F1B runs one stage per rank")
+        order = one_f_one_b_order(pp_size, n_microbatches)
+    elif name == "Interleaved1F1B":
+        order = interleaved_order(pp_size, n_virtual, n_microbatches)
+    else:
+        raise ValueError(f"unknown schedule {name!r}; expected one of {SCHEDULES}")
+    num_stages = pp_size * n_virtual
+    s2r = stage_to_rank_loop(pp_size)
+    order = add_unshard_reshard(order)
+    order = add_reduce_grad(order, n_microbatches, also_allreduce=dp_allreduce)
+    order = add_send_recv(order, s2r, num_stages)
+    if not keep_fsdp_slots:
+        order = strip_fsdp_slots(order)
+    if with_optimizer:
+        order = add_optimizer(order)
+    validate_schedule(order, num_stages, n_microbatches, s2r)
+    return order

@@ -1,0 +1,158 @@
+"""Unit tests of the schedule IR, generators, lowering and simulator ('Unit - schedule IR').
+Golden strings are the torch-generated IR recorded in SURVEY.md section 3.5 for the reference's largest
+interleaved case (P=4, v=2, m=4)."""
+import pytest
+
+from ppb200.parallel.schedule import (Action, ActionType, build_schedule, format_schedule, parse_schedule, simulate,
+                                      theoretical_bubble, validate_schedule, gpipe_order, one_f_one_b_order,
+                                      interleaved_order, add_reduce_grad, add_send_recv, stage_to_rank_loop)
+from ppb200.parallel.schedule import ir
+from ppb200.parallel.schedule.simulate import DeadlockError
+
+GOLDEN_RANK0 = ("0F0 0SEND_F0 4RECV_F0 0F1 0SEND_F1 4RECV_F1 0F2 0SEND_F2 4RECV_F2 0F3 0SEND_F3 4RECV_F3 "
+                "4F0 4SEND_F0 4F1 4SEND_F1 4F2 4SEND_F2 4F3 4SEND_F3 "
+                "4RECV_B0 4B0 4SEND_B0 4RECV_B1 4B1 4SEND_B1 4RECV_B2 4B2 4SEND_B2 4RECV_B3 4B3 4SEND_B3 4REDUCE_GRAD "
+                "0RECV_B0 0B0 0RECV_B1 0B1 0RECV_B2 0B2 0RECV_B3 0B3 0REDUCE_GRAD")
+GOLDEN_RANK3_PREFIX = "3RECV_F0 3F0 3SEND_F0"
+GOLDEN_RANK3_TAIL = ("7RECV_F0 7F0 7RECV_F1 7B0 7SEND_B0 7RECV_F2 7F1 7B1 7SEND_B1 "
+                     "7RECV_F3 7F2 3RECV_B0 7B2 7SEND_B2 7F3 3RECV_B1 7B3 7SEND_B3 3RECV_B2 7REDUCE_GRAD 3RECV_B3 "
+                     "3B0 3SEND_B0 3B1 3SEND_B1 3B2 3SEND_B2 3B3 3SEND_B3 3REDUCE_GRAD")
+
+
+def test_action_text_roundtrip():
+    for s in ["2F0", "3SEND_B1", "4REDUCE_GRAD", "11RECV_F31", "0B0", "5I2", "5W2", "1ALLREDUCE", "0OPTIM"]:
+        assert str(Action.from_str(s)) == s
+    with pytest.raises(ValueError):
+        Action.from_str("F0")
+    with pytest.raises(ValueError):
+        Action.from_str("2REDUCE_GRAD1")
+    with pytest.raises(ValueError):
+        Action.from_str("2F")
+
+
+def test_golden_interleaved_p4_v2_m4():
+    order = build_schedule("Interleaved1F1B", 4, 4, n_virtual=2, with_optimizer=False)
+    assert " ".join(map(str, order[0])) == GOLDEN_RANK0
+    r3 = " ".join(map(str, order[3]))
+    assert r3.startswith(GOLDEN_RANK3_PREFIX)
+    assert r3.endswith(GOLDEN_RANK3_TAIL)
+
+
+def test_text_and_csv_roundtrip():
+    order = build_schedule("1F1B", 4, 8)
+    assert parse_schedule(format_schedule(order)) == {r: list(a) for r, a in order.items()}
+    assert ir.from_csv(ir.to_csv(order)) == {r: list(a) for r, a in order.items()}
+    g = ir.grid(order, error_at=(1, 3))
+    assert "<-- ERROR HERE" in g and g.count("\n") == 3
+
+
+@pytest.mark.parametrize("name,P,v,m", [
+    ("GPipe", 2, 1, 4), ("GPipe", 4, 1, 8), ("GPipe", 8, 1, 32), ("GPipe", 4, 1, 3),
+    ("1F1B", 2, 1, 4), ("1F1B", 4, 1, 4), ("1F1B", 4, 1, 8), ("1F1B", 8, 1, 64),
+    ("Interleaved1F1B", 2, 2, 4), ("Interleaved1F1B", 4, 2, 4), ("Interleaved1F1B", 4, 2, 8),
+    ("Interleaved1F1B", 8, 2, 32), ("Interleaved1F1B", 4, 3, 12), ("Interleaved1F1B", 2, 4, 8),
+    ("Interleaved1F1B", 4, 1, 4),
+])
+def test_properties_and_no_deadlock(name, P, v, m):
+    order = build_schedule(name, P, m, n_virtual=v, dp_allreduce=True)
+    S = P * v
+    validate_schedule(order, S, m, stage_to_rank_loop(P))
+    for r, acts in order.items():
+        assert sum(a.type == ActionType.F for a in acts) == m * v
+        assert sum(a.type == ActionType.B for a in acts) == m * v
+        assert sum(a.type == ActionType.REDUCE_GRAD for a in acts) == v
+        assert sum(a.type == ActionType.ALLREDUCE for a in acts) == v
+        assert sum(a.type == ActionType.OPTIM for a in acts) == v
+        # REDUCE_GRAD sits right behind the stage's last backward (plus its send)
+        for i, a in enumerate(acts):
+            if a.type == ActionType.REDUCE_GRAD:
+                prev = [x for x in acts[:i] if x.type == ActionType.B and x.stage == a.stage]
+                assert len(prev) == m
+    res = simulate(order, S, comm_latency=0.0)
+    assert res.makespan > 0
+    theory = theoretical_bubble(P, m, v)
+    # with F=1, B=2 and free communication the simulated bubble can not beat the bound by more than rounding
+    assert res.bubble_max >= theory - 1e-9 or name == "Interleaved1F1B"
+    assert res.bubble_max < 1.0
+
+
+def test_one_f_one_b_matches_theory_exactly():
+    for P, m in [(2, 4), (4, 8), (8, 32)]:
+        order = build_schedule("1F1B", P, m)
+        res = simulate(order, P)
+        assert abs(res.bubble_max - theoretical_bubble(P, m)) < 1e-9
+        order = build_schedule("GPipe", P, m)
+        res = simulate(order, P)
+        assert abs(res.bubble_max - theoretical_bubble(P, m)) < 1e-9
+
+
+def test_interleaved_beats_1f1b_when_m_multiple_of_p():
+    P, m = 8, 32
+    b1 = simulate(build_schedule("1F1B", P, m), P).bubble_max
+    b2 = simulate(build_schedule("Interleaved1F1B", P, m, n_virtual=2), 2 * P, f_cost=0.5, b_cost=1.0).bubble_max
+    assert b2 < b1
+    assert abs(theoretical_bubble(8, 32, 2) - 0.0986) < 1e-3
+    assert abs(theoretical_bubble(4, 8) - 0.2727) < 1e-3
+    assert abs(theoretical_bubble(8, 32) - 0.1795) < 1e-3
+
+
+def test_memory_profile_1f1b_vs_gpipe():
+    """In-flight micro-batches on stage 0: GPipe holds m, 1F1B at most P."""
+    def peak_inflight(order, rank):
+        live = peak = 0
+        for a in order[rank]:
+            if a.type == ActionType.F:
+                live += 1
+            elif a.type == ActionType.B:
+                live -= 1
+            peak = max(peak, live)
+        return peak
+    assert peak_inflight(build_schedule("GPipe", 4, 16), 0) == 16
+    assert peak_inflight(build_schedule("1F1B", 4, 16), 0) == 4
+    assert peak_inflight(build_schedule("1F1B", 4, 16), 3) == 1
+
+
+def test_constraints():
+    with pytest.raises(ValueError):
+        build_schedule("1F1B", 4, 3)           # m >= stages (torch schedules.py:828)
+    with pytest.raises(ValueError):
+        build_schedule("Interleaved1F1B", 4, 9, n_virtual=2)  # m % rounds
+    with pytest.raises(ValueError):
+        build_schedule("Nope", 2, 4)
+
+
+def test_deadlock_detection():
+    order = build_schedule("GPipe", 2, 2, with_optimizer=False)
+    bad = {0: list(order[0]), 1: list(order[1])}
+    # make rank 1 wait for a micro-batch rank 0 never sends first: swap rank 0's forwards behind its backwards
+    f = [a for a in bad[0] if a.type in (ActionType.F, ActionType.SEND_F)]
+    rest = [a for a in bad[0] if a.type not in (ActionType.F, ActionType.SEND_F)]
+    bad[0] = rest + f
+    with pytest.raises(DeadlockError):
+        simulate(bad, 2)
+
+
+def test_matches_torch_generator_when_available():
+    """Cross-check the compute order + comm lowering against torch.distributed.pipelining (test oracle only)."""
+    sched = pytest.importorskip("torch.distributed.pipelining.schedules")
+    for P, v, m in [(2, 2, 4), (4, 2, 4), (4, 2, 8), (8, 2, 32), (4, 3, 12)]:
+        mine = interleaved_order(P, v, m)
+        try:
+            rounds = max(1, m // P)
+            per_round = m // rounds
+            for r in range(P):
+                warm = sched._get_warmup_ops(r, v, per_round, P, m, multiply_factor=2)
+                total = m * v
+
+                def fsi(step, r=r):
+                    return ((step // per_round) % v) * P + r
+
+                def bsi(step, r=r, warm=warm):
+                    return (v - 1 - ((step - warm) // per_round) % v) * P + r
+
+                ops = sched._get_1f1b_rank_ops(v, P, warm, total - warm, warm, r, fsi, bsi)
+                theirs = [f"{a.stage_index}{'F' if str(a.computation_type) == 'F' else 'B'}{a.microbatch_index}"
+                          for a in ops if a is not None]
+                assert [str(a) for a in mine[r]] == theirs, (P, v, m, r)
+        except (AttributeError, TypeError):
+            pytest.skip("torch internals changed")
