@@ -31,6 +31,7 @@ struct AttnBwdParams {
   float scale;
   float sl2;
   unsigned long long seed;
+  const unsigned long long* seed_off;
   unsigned int drop_thresh;
   float drop_scale;
   const float* lse;    // [B, H, Sq]
@@ -216,6 +217,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t t_dp = tmem_base + lane_off + Cfg::DP_COL + hf * 64;
     const uint32_t t_dq = tmem_base + lane_off + Cfg::DQ_COL + hf * (DQK / 2);
     const float LOG2E = 1.4426950408889634f;
+    const unsigned long long seed_eff = p.seed + ((p.drop_thresh && p.seed_off) ? *p.seed_off : 0ull);
 
     auto drain_dq = [&](int it_prev) {
       // dQ tile of iteration it_prev: TMEM -> fp32 staging -> TMA reduce-add into the accumulator
@@ -283,7 +285,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const unsigned long long base = drop_row + (unsigned long long)kvb;
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = dropout_pair_bits(p.seed, (base + i) >> 1);
+            const uint32_t hsh = dropout_pair_bits(seed_eff, (base + i) >> 1);
             const float k0 = ((hsh & 0xFFFFu) >= p.drop_thresh) ? p.drop_scale : 0.f;
             const float k1 = ((hsh >> 16) >= p.drop_thresh) ? p.drop_scale : 0.f;
             dsv[i] = pv[i] * (dsv[i] * k0 - dlt) * p.scale;
@@ -483,6 +485,7 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   p.scale = scale;
   p.sl2 = scale * 1.4426950408889634f;
   p.seed = seed;
+  p.seed_off = seed_offset_ptr();
   p.drop_thresh = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;

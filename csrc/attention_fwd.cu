@@ -29,6 +29,7 @@ struct AttnParams {
   int causal;
   float sl2;  // softmax scale * log2(e)
   unsigned long long seed;
+  const unsigned long long* seed_off;
   unsigned int drop_thresh;
   float drop_scale;
   float* lse;  // [B, H, Sq] natural-log LSE
@@ -201,6 +202,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int causal_lim = q_idx + (p.Skv - p.Sq);  // last visible kv index for this row
     const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * p.Sq + (unsigned long long)min(q_idx, p.Sq - 1)) *
                                         (unsigned long long)p.Skv;
+    const unsigned long long seed_eff = p.seed + ((p.drop_thresh && p.seed_off) ? *p.seed_off : 0ull);
     float o[DV];
 #pragma unroll
     for (int i = 0; i < DV; ++i) o[i] = 0.f;
@@ -278,7 +280,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const unsigned long long base = drop_row + (unsigned long long)(kv0 + c * 32);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = dropout_pair_bits(p.seed, (base + i) >> 1);
+            const uint32_t hsh = dropout_pair_bits(seed_eff, (base + i) >> 1);
             pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] * p.drop_scale : 0.f;
             pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] * p.drop_scale : 0.f;
           }
@@ -389,6 +391,7 @@ extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o
   p.causal = causal;
   p.sl2 = scale * 1.4426950408889634f;
   p.seed = seed;
+  p.seed_off = seed_offset_ptr();
   p.drop_thresh = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;

@@ -34,6 +34,7 @@ struct GemmParams {
   const bf16* aux;
   long long ld_aux;
   unsigned long long seed;
+  const unsigned long long* seed_off;
   unsigned int drop_thresh;
   float drop_scale;
 };
@@ -216,11 +217,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int j = 0; j < CHUNK; ++j) v[j] = gelu_erf(v[j]);
           }
           if (p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
+            const unsigned long long seed_eff = p.seed + (p.seed_off ? *p.seed_off : 0ull);
             const unsigned long long base = (unsigned long long)row * (unsigned long long)p.N + nc;
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 2) {
               // N is even for every dropout caller, so (base + j) is even and shares one pair hash
-              const uint32_t h = dropout_pair_bits(p.seed, (base + j) >> 1);
+              const uint32_t h = dropout_pair_bits(seed_eff, (base + j) >> 1);
               v[j] = ((h & 0xFFFFu) >= p.drop_thresh) ? v[j] * p.drop_scale : 0.f;
               v[j + 1] = ((h >> 16) >= p.drop_thresh) ? v[j + 1] * p.drop_scale : 0.f;
             }
@@ -425,6 +427,7 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.aux = reinterpret_cast<const bf16*>(aux);
   p.ld_aux = ld_aux;
   p.seed = seed;
+  p.seed_off = seed_offset_ptr();
   p.drop_thresh = dropout_thresh16(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;

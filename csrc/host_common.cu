@@ -30,6 +30,13 @@ int sm_count() {
   return cached[dev];
 }
 
+static const unsigned long long* g_seed_off[64] = {nullptr};
+const unsigned long long* seed_offset_ptr() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  return g_seed_off[dev];
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -80,3 +87,12 @@ bool make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, int rank, const void
 
 extern "C" const char* ppb_last_error() { return ppb::get_error(); }
 extern "C" int ppb_version() { return 100; }
+extern "C" int ppb_set_dropout_offset_ptr(const unsigned long long* p) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    ppb::set_error("ppb_set_dropout_offset_ptr: no current device");
+    return -1;
+  }
+  ppb::g_seed_off[dev] = p;
+  return 0;
+}

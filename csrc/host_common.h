@@ -11,6 +11,9 @@ namespace ppb {
 void set_error(const char* fmt, ...);
 const char* get_error();
 int sm_count();  // SM count of the current device (cached per device)
+// device pointer to a step-varying 64-bit value that every dropout-using kernel adds to its seed (may be null);
+// lets CUDA graphs replay with fresh masks without re-capturing.
+const unsigned long long* seed_offset_ptr();
 
 // inner-most dimension first, like the driver API. strides are in bytes for dims 1..rank-1.
 bool make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, int rank, const void* ptr, const uint64_t* dims,

@@ -33,6 +33,7 @@ struct LnFwdParams {
   int T, d;
   float eps;
   unsigned long long seed;
+  const unsigned long long* seed_off;
   unsigned int thresh;
   float scale;
   int rms;
@@ -43,6 +44,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = p.d >> 3;
   const float inv_d = 1.f / float(p.d);
+  const unsigned long long seed_eff = p.seed + ((p.thresh && p.seed_off) ? *p.seed_off : 0ull);
   for (int row = blockIdx.x * LN_WARPS + warp; row < p.T; row += gridDim.x * LN_WARPS) {
     float v[MAXV][8];
     const long long rbase = (long long)row * p.d;
@@ -62,7 +64,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p)
           const float2 r2 = unpack_bf16(rw[q]);
           float2 a2 = unpack_bf16(aw[q]);
           if (p.thresh) {
-            const uint32_t h = dropout_pair_bits(p.seed, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
+            const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
             a2.x = ((h & 0xFFFFu) >= p.thresh) ? a2.x * p.scale : 0.f;
             a2.y = ((h >> 16) >= p.thresh) ? a2.y * p.scale : 0.f;
           }
@@ -132,6 +134,7 @@ struct LnBwdParams {
   float* scratch;  // 256-byte header (arrival counter, zero between launches) + [grid, 2, d] partials
   int T, d;
   unsigned long long seed;
+  const unsigned long long* seed_off;
   unsigned int thresh;
   float scale;
   int rms;
@@ -144,6 +147,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = p.d >> 3;
   const float inv_d = 1.f / float(p.d);
+  const unsigned long long seed_eff = p.seed + ((p.thresh && p.seed_off) ? *p.seed_off : 0ull);
   float dg[MAXV][8], db[MAXV][8];
 #pragma unroll
   for (int i = 0; i < MAXV; ++i)
@@ -207,7 +211,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
           if (p.da) {
             float ax = gx, ay = gy;
             if (p.thresh) {
-              const uint32_t h = dropout_pair_bits(p.seed, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
+              const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
               ax = ((h & 0xFFFFu) >= p.thresh) ? gx * p.scale : 0.f;
               ay = ((h >> 16) >= p.thresh) ? gy * p.scale : 0.f;
             }
@@ -288,6 +292,7 @@ extern "C" int ppb_add_dropout_norm_fwd(const void* resid, const void* a, const 
   p.d = d;
   p.eps = eps;
   p.seed = seed;
+  p.seed_off = seed_offset_ptr();
   p.thresh = (a && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
   p.scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.rms = rms;
@@ -341,6 +346,7 @@ static void fill_ln_bwd_params(LnBwdParams& p, const void* dy0, const void* dy1,
   p.T = T;
   p.d = d;
   p.seed = seed;
+  p.seed_off = seed_offset_ptr();
   p.thresh = (da && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
   p.scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.rms = rms;

@@ -1,0 +1,374 @@
+"""The helper-compatible model (``Transformer``) and its explicit forward/backward stage program.
+
+API parity with /root/reference/LLMsDistributedTrainingHelper.py:31-55:
+  * ``Transformer(model_args)`` has ``.tok_embeddings``, ``.layers`` (``ModuleDict`` keyed by the GLOBAL layer
+    index as a string), ``.norm``, ``.output``; any of them may be ``None``/deleted, so a pruned copy IS a
+    pipeline stage (helper:48-55) and a stage's ``state_dict()`` is a strict subset of the full model's
+    (SURVEY.md section 2.3 lists the exact keys; they are reproduced here name for name, shape for shape).
+  * the decoder layer computes what ``nn.TransformerDecoderLayer(dim, heads, batch_first=True)`` computes when
+    called as ``layer(h, h)``: post-LN self-attention, cross-attention over the layer's own input, ReLU FFN,
+    six dropouts (torch transformer.py:1143-1199).
+
+What is different: nothing here goes through autograd op by op.  ``layer_forward`` / ``layer_backward`` call the
+fused ops of ``ppb200.ops.functional`` (hand-written sm_100a kernels on CUDA, fp32 torch math on CPU) and keep an
+explicit activation stash, so one (stage, micro-batch) forward or backward is a fixed launch sequence that the
+runner can capture in a CUDA graph.  ``Transformer.forward`` wraps the same program in a single
+``autograd.Function`` so that user code (``loss.backward()``) keeps working.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as F
+from .args import ModelArgs
+
+# dropout "sites" inside one decoder layer: each gets its own counter-based stream
+SITE_ATTN1, SITE_RES1, SITE_ATTN2, SITE_RES2, SITE_FFN, SITE_RES3 = range(6)
+_MASK64 = (1 << 64) - 1
+
+
+def site_seed(base_seed: int, layer_id: int, mb: int, site: int) -> int:
+    """Static part of a dropout seed (the step-varying part is added on the device, see StageProgram)."""
+    x = (base_seed * 0x9E3779B97F4A7C15 + (layer_id + 1) * 0xD1B54A32D192ED03 + (mb + 1) * 0x94D049BB133111EB +
+         (site + 1) * 0xBF58476D1CE4E5B9) & _MASK64
+    x ^= x >> 31
+    return (x * 0xD6E8FEB86659FD93) & _MASK64
+
+
+# ------------------------------------------------------------------------------------------------------------
+# parameter containers (names == the reference checkpoint keys)
+# ------------------------------------------------------------------------------------------------------------
+class _Proj(nn.Module):
+    def __init__(self, n_in: int, n_out: int, dtype):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(n_out, n_in, dtype=dtype))
+        self.bias = nn.Parameter(torch.zeros(n_out, dtype=dtype))
+        nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        bound = 1.0 / math.sqrt(n_in)
+        nn.init.uniform_(self.bias, -bound, bound)
+
+
+class _Attn(nn.Module):
+    """Holds ``in_proj_weight`` (packed q,k,v on dim 0), ``in_proj_bias``, ``out_proj.{weight,bias}``."""
+
+    def __init__(self, dim: int, dtype):
+        super().__init__()
+        self.in_proj_weight = nn.Parameter(torch.empty(3 * dim, dim, dtype=dtype))
+        self.in_proj_bias = nn.Parameter(torch.zeros(3 * dim, dtype=dtype))
+        self.out_proj = _Proj(dim, dim, dtype)
+        nn.init.xavier_uniform_(self.in_proj_weight)
+        nn.init.zeros_(self.out_proj.bias)
+
+
+class _Norm(nn.Module):
+    def __init__(self, dim: int, dtype, rms: bool):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim, dtype=dtype))
+        if not rms:
+            self.bias = nn.Parameter(torch.zeros(dim, dtype=dtype))
+        else:
+            self.register_parameter("bias", None)
+
+
+class DecoderLayer(nn.Module):
+    def __init__(self, args: ModelArgs):
+        super().__init__()
+        if args.norm_first:
+            raise NotImplementedError("pre-LN (GPT) block: explicit program not implemented yet; use the reference block")
+        d, dt, rms = args.dim, args.dtype, args.norm == "rmsnorm"
+        self.self_attn = _Attn(d, dt)
+        if args.cross_attn:
+            self.multihead_attn = _Attn(d, dt)
+        self.linear1 = _Proj(d, args.ffn_dim, dt)
+        self.linear2 = _Proj(args.ffn_dim, d, dt)
+        self.norm1 = _Norm(d, dt, rms)
+        if args.cross_attn:
+            self.norm2 = _Norm(d, dt, rms)
+        self.norm3 = _Norm(d, dt, rms)
+
+
+class _Embedding(nn.Module):
+    def __init__(self, vocab: int, dim: int, dtype):
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty(vocab, dim, dtype=dtype))
+        nn.init.normal_(self.weight)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# explicit per-layer program
+# ------------------------------------------------------------------------------------------------------------
+class GradSink:
+    """Maps parameter tensors to fp32 gradient accumulators (views of the stage's grad arena, or p.grad)."""
+
+    def __init__(self):
+        self._g: Dict[int, torch.Tensor] = {}
+
+    def bind(self, param: torch.Tensor, grad: torch.Tensor) -> None:
+        self._g[id(param)] = grad
+
+    def __call__(self, param: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        if param is None:
+            return None
+        return self._g[id(param)]
+
+
+class Ctx:
+    """Per-call context of the explicit program: micro-batch geometry, model args, dropout seeding."""
+
+    def __init__(self, args: ModelArgs, batch: int, seq: int, base_seed: int, mb: int, training: bool = True,
+                 step_offset: int = 0):
+        self.args = args
+        self.B, self.S = batch, seq
+        self.base_seed, self.mb = base_seed, mb
+        self.p = args.dropout if training else 0.0
+        self.step_offset = step_offset  # CPU path only: on CUDA the offset lives in device memory
+
+    def seed(self, layer_id: int, site: int) -> int:
+        return (site_seed(self.base_seed, layer_id, self.mb, site) + self.step_offset) & _MASK64
+
+
+def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Post-LN decoder layer forward on [T, d] tokens.  Fills the stash ``st`` and returns x3."""
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    st["x0"] = x0
+    # ---- self-attention ----
+    qkv = F.linear_fwd(x0, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    o1, lse1 = F.attention_fwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], ctx.B, H, a.causal, None, p,
+                               ctx.seed(layer_id, SITE_ATTN1))
+    a1 = F.linear_fwd(o1, L.self_attn.out_proj.weight, L.self_attn.out_proj.bias)
+    z1, x1, mean1, rstd1 = F.add_dropout_norm_fwd(x0, a1, L.norm1.weight, L.norm1.bias, eps, p,
+                                                  ctx.seed(layer_id, SITE_RES1), rms)
+    st.update(qkv=qkv, o1=o1, lse1=lse1, z1=z1, x1=x1, mean1=mean1, rstd1=rstd1)
+    x2 = x1
+    # ---- cross-attention over the layer input (memory = x0) ----
+    if a.cross_attn:
+        W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
+        q2 = F.linear_fwd(x1, W[:d], bvec[:d])
+        kv2 = F.linear_fwd(x0, W[d:], bvec[d:])
+        o2, lse2 = F.attention_fwd(q2, kv2[:, :d], kv2[:, d:], ctx.B, H, False, None, p, ctx.seed(layer_id, SITE_ATTN2))
+        a2 = F.linear_fwd(o2, L.multihead_attn.out_proj.weight, L.multihead_attn.out_proj.bias)
+        z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p,
+                                                      ctx.seed(layer_id, SITE_RES2), rms)
+        st.update(q2=q2, kv2=kv2, o2=o2, lse2=lse2, z2=z2, x2=x2, mean2=mean2, rstd2=rstd2)
+    # ---- feed-forward ----
+    if a.activation == "relu":
+        h = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
+        st["h"] = h
+    else:  # gelu: keep the pre-activation for backward (dropout on the hidden is not applied in this variant)
+        hpre = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias)
+        h = F.gelu_fwd(hpre)
+        st.update(hpre=hpre, h=h)
+    a3 = F.linear_fwd(h, L.linear2.weight, L.linear2.bias)
+    z3, x3, mean3, rstd3 = F.add_dropout_norm_fwd(x2, a3, L.norm3.weight, L.norm3.bias, eps, p,
+                                                  ctx.seed(layer_id, SITE_RES3), rms)
+    st.update(z3=z3, mean3=mean3, rstd3=rstd3)
+    return x3
+
+
+def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], ctx: Ctx, st: dict,
+                   G: GradSink) -> List[torch.Tensor]:
+    """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. x3 (summed on load by the norm
+    kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. x0."""
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms = a.norm == "rmsnorm"
+    x0 = st["x0"]
+    # ---- FFN ----
+    dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
+                          ctx.seed(layer_id, SITE_RES3), rms)
+    x2 = st["x2"] if a.cross_attn else st["x1"]
+    F.linear_wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
+    if a.activation == "relu":
+        dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
+    else:
+        dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
+    F.linear_wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias))
+    dx2 = F.linear_dgrad(dh, L.linear1.weight)
+    dys1 = [dz3, dx2]
+    dx0_extra = None
+    # ---- cross-attention ----
+    if a.cross_attn:
+        W = L.multihead_attn.in_proj_weight
+        gW, gb = G(W), G(L.multihead_attn.in_proj_bias)
+        dz2, da2 = F.norm_bwd(dys1, st["z2"], st["mean2"], st["rstd2"], L.norm2.weight, G(L.norm2.weight),
+                              G(L.norm2.bias), p, ctx.seed(layer_id, SITE_RES2), rms)
+        F.linear_wgrad(da2, st["o2"], G(L.multihead_attn.out_proj.weight), G(L.multihead_attn.out_proj.bias))
+        do2 = F.linear_dgrad(da2, L.multihead_attn.out_proj.weight)
+        kv2 = st["kv2"]
+        dq2 = torch.empty_like(st["q2"])
+        dkv2 = torch.empty_like(kv2)
+        F.attention_bwd(st["q2"], kv2[:, :d], kv2[:, d:], st["o2"], do2, st["lse2"], ctx.B, H, False, None, p,
+                        ctx.seed(layer_id, SITE_ATTN2), out=(dq2, dkv2[:, :d], dkv2[:, d:]))
+        F.linear_wgrad(dq2, st["x1"], gW[:d], gb[:d])
+        F.linear_wgrad(dkv2, x0, gW[d:], gb[d:])
+        dx1 = F.linear_dgrad(dq2, W[:d])
+        dx0_extra = F.linear_dgrad(dkv2, W[d:])
+        dys1 = [dz2, dx1]
+    # ---- self-attention ----
+    dz1, da1 = F.norm_bwd(dys1, st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias), p,
+                          ctx.seed(layer_id, SITE_RES1), rms)
+    F.linear_wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias))
+    do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
+    qkv = st["qkv"]
+    dqkv = torch.empty_like(qkv)
+    F.attention_bwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], st["o1"], do1, st["lse1"], ctx.B, H, a.causal, None, p,
+                    ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
+    F.linear_wgrad(dqkv, x0, G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
+    dx0 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
+    out = [dz1, dx0]
+    if dx0_extra is not None:
+        out.append(dx0_extra)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# stage-level program (embedding -> layers -> final norm -> LM head -> loss)
+# ------------------------------------------------------------------------------------------------------------
+def stage_forward(model: "Transformer", inp: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Forward of whatever pieces this (possibly pruned) model holds.  ``inp`` is int64 tokens [B, S] when the
+    model has the embedding, else activations [B*S, d].  Returns [T, d] activations, or logits [T, V] (a view of a
+    row-padded buffer) when the model holds the LM head."""
+    a = ctx.args
+    if model.tok_embeddings is not None:
+        st["tokens"] = inp
+        h = F.embedding_fwd(inp.reshape(-1), model.tok_embeddings.weight)
+    else:
+        h = inp.reshape(-1, a.dim)
+    st["layers"] = {}
+    for name, layer in model.layers.items():
+        ls: dict = {}
+        h = layer_forward(layer, int(name), h, ctx, ls)
+        st["layers"][name] = ls
+    if model.norm is not None:
+        st["norm_in"] = h
+        _, h, mean, rstd = F.add_dropout_norm_fwd(h, None, model.norm.weight, model.norm.bias, a.layer_norm_eps, 0.0, 0,
+                                                  a.norm == "rmsnorm", need_z=False)
+        st.update(norm_mean=mean, norm_rstd=rstd)
+    if model.output is not None:
+        st["head_in"] = h
+        V = model.output.weight.shape[0]
+        buf = torch.empty((h.shape[0], F.pad8(V)), dtype=h.dtype, device=h.device)
+        h = F.linear_fwd(h, model.output.weight, model.output.bias, out=buf[:, :V])
+    return h
+
+
+def stage_loss(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float, st: dict) -> torch.Tensor:
+    """Mean token cross-entropy (helper:197-201) of one micro-batch; overwrites ``logits`` with its gradient
+    (scaled by ``grad_scale``, e.g. 1 for a plain mean).  Returns a 1-element fp32 tensor."""
+    T = logits.shape[0]
+    rows = F.xent_fwd_bwd(logits, targets.reshape(-1), grad_scale / T, True)
+    loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
+    F.reduce_sum(rows, loss, 1.0 / T)
+    st["dlogits"] = logits
+    return loss
+
+
+def stage_backward(model: "Transformer", douts: Sequence[torch.Tensor], ctx: Ctx, st: dict, G: GradSink,
+                   need_input_grad: bool = True) -> Optional[torch.Tensor]:
+    """Backward of ``stage_forward``.  ``douts`` = gradient(s) w.r.t. the stage output (for the last stage: the
+    in-place dlogits).  Returns the gradient w.r.t. the stage input activations (None for the first stage)."""
+    a = ctx.args
+    dys: List[torch.Tensor] = [d.reshape(-1, d.shape[-1]) for d in douts]
+    if model.output is not None:
+        dlog = dys[0]
+        F.linear_wgrad(dlog, st["head_in"], G(model.output.weight), G(model.output.bias))
+        dys = [F.linear_dgrad(dlog, model.output.weight)]
+    if model.norm is not None:
+        dz, _ = F.norm_bwd(dys, st["norm_in"], st["norm_mean"], st["norm_rstd"], model.norm.weight, G(model.norm.weight),
+                           G(model.norm.bias), 0.0, 0, a.norm == "rmsnorm", need_da=False)
+        dys = [dz]
+    for name in reversed(list(model.layers.keys())):
+        dys = layer_backward(model.layers[name], int(name), dys, ctx, st["layers"][name], G)
+    if model.tok_embeddings is not None:
+        F.embedding_bwd(st["tokens"].reshape(-1), dys, G(model.tok_embeddings.weight))
+        return None
+    if not need_input_grad:
+        return None
+    return F.add_n(dys)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# nn.Module front-end
+# ------------------------------------------------------------------------------------------------------------
+class _StageFn(torch.autograd.Function):
+    """Bridges the explicit program into autograd: ONE node for the whole (pruned) model."""
+
+    @staticmethod
+    def forward(fctx, model, inp, dummy, *params):
+        B, S = inp.shape[0], inp.shape[1]
+        ctx = Ctx(model.args, B, S, model._seed, model._calls, model.training, 0)
+        model._calls += 1
+        st: dict = {}
+        with torch.no_grad():
+            out = stage_forward(model, inp, ctx, st)
+        fctx.model, fctx.ctx, fctx.st = model, ctx, st
+        fctx.inp_is_tokens = model.tok_embeddings is not None
+        fctx.in_shape = inp.shape
+        return out.reshape(B, S, -1)
+
+    @staticmethod
+    def backward(fctx, dout):
+        model, ctx, st = fctx.model, fctx.ctx, fctx.st
+        G = GradSink()
+        params = list(model.parameters())
+        acc = []
+        for p in params:  # fp32 accumulators (p.grad must have the parameter's dtype, so they are folded in below)
+            g = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+            acc.append(g)
+            G.bind(p, g)
+        with torch.no_grad():
+            dout = dout.contiguous()
+            if model.output is not None and dout.is_cuda:
+                V = dout.shape[-1]
+                buf = torch.empty((dout.shape[0] * dout.shape[1], F.pad8(V)), dtype=dout.dtype, device=dout.device)
+                buf[:, :V].copy_(dout.reshape(-1, V))
+                dout = buf[:, :V]
+            dx = stage_backward(model, [dout], ctx, st, G, need_input_grad=not fctx.inp_is_tokens)
+            for p, g in zip(params, acc):
+                if p.requires_grad:
+                    p.grad = g.to(p.dtype) if p.grad is None else p.grad + g.to(p.dtype)
+        if dx is not None:
+            dx = dx.reshape(fctx.in_shape)
+        return (None, dx, None) + (None,) * len(params)
+
+
+class Transformer(nn.Module):
+    """transformer model for pipeline parallelism (same constructor / attributes as helper:31-46)."""
+
+    def __init__(self, model_args: ModelArgs):
+        super().__init__()
+        self.args = model_args
+        dt = model_args.dtype
+        self.tok_embeddings = _Embedding(model_args.vocab_size, model_args.dim, dt)
+        self.layers = nn.ModuleDict()
+        for layer_id in range(model_args.n_layers):
+            self.layers[str(layer_id)] = DecoderLayer(model_args)
+        self.norm = _Norm(model_args.dim, dt, model_args.norm == "rmsnorm")
+        self.output = _Proj(model_args.dim, model_args.vocab_size, dt)
+        self._seed = 0
+        self._calls = 0
+        self._dummy = None
+
+    def set_seed(self, seed: int) -> None:
+        self._seed, self._calls = int(seed), 0
+
+    def forward(self, tokens: torch.Tensor) -> torch.Tensor:
+        """tokens: int64 [B, S] if this model holds the embedding, else activations [B, S, dim].
+        Returns [B, S, dim] activations or [B, S, vocab] logits (helper:48-55)."""
+        if tokens.dim() == 2 and self.tok_embeddings is None:
+            raise ValueError("this stage has no embedding: pass activations [B, S, dim]")
+        needs_grad = torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters())
+                                                  or (tokens.is_floating_point() and tokens.requires_grad))
+        if not needs_grad:
+            B, S = tokens.shape[0], tokens.shape[1]
+            ctx = Ctx(self.args, B, S, self._seed, self._calls, self.training, 0)
+            self._calls += 1
+            with torch.no_grad():
+                return stage_forward(self, tokens, ctx, {}).reshape(B, S, -1)
+        if self._dummy is None or self._dummy.device != tokens.device:
+            self._dummy = torch.zeros(1, device=tokens.device, requires_grad=True)
+        return _StageFn.apply(self, tokens, self._dummy, *list(self.parameters()))

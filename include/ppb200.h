@@ -21,6 +21,9 @@ extern "C" {
 
 const char* ppb_last_error(void);
 int ppb_version(void);
+/* Optional device pointer to a 64-bit value that every dropout-using kernel adds to its seed at run time (per
+ * device; NULL disables).  Lets CUDA graphs replay with fresh masks. */
+int ppb_set_dropout_offset_ptr(const unsigned long long* p);
 
 /* ---- K1/K2/K3: tcgen05 GEMM ------------------------------------------------------------------------------
  * C[M,N] (=|+=) epilogue(alpha * op(A)[M,K] * op(B)[N,K]^T)

@@ -1,0 +1,95 @@
+"""Model parity with the UNMODIFIED reference helper (SURVEY.md section 4 'Oracle vs. reference'): identical
+state_dict key layout, identical logits and parameter gradients (fp32, dropout off), on CPU."""
+import os
+import sys
+
+import pytest
+import torch
+
+from ppb200.models import ModelArgs, Transformer
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_DIRS = [os.path.join(ROOT, "baseline", "_ref"), "/root/reference"]
+
+
+def _load_ref():
+    for d in REF_DIRS:
+        if os.path.exists(os.path.join(d, "LLMsDistributedTrainingHelper.py")):
+            if d not in sys.path:
+                sys.path.insert(0, d)
+            import LLMsDistributedTrainingHelper as ref  # noqa: WPS433
+            return ref
+    pytest.skip("reference helper not available")
+
+
+def test_state_dict_layout_matches_reference():
+    ref = _load_ref()
+    rm = ref.Transformer(ref.ModelArgs(n_layers=2, n_heads=4))
+    mm = Transformer(ModelArgs(n_layers=2, n_heads=4))
+    rsd, msd = rm.state_dict(), mm.state_dict()
+    assert list(rsd.keys()) == list(msd.keys())
+    for k in rsd:
+        assert tuple(rsd[k].shape) == tuple(msd[k].shape), k
+    mm.load_state_dict(rsd)  # the checkpoint format is shared
+    assert sum(p.numel() for p in mm.parameters()) == ModelArgs(n_layers=2, n_heads=4).num_params()
+
+
+@pytest.mark.parametrize("heads", [4, 8, 12])
+def test_logits_and_grads_match_reference(heads):
+    ref = _load_ref()
+    torch.manual_seed(0)
+    rm = ref.Transformer(ref.ModelArgs(dim=96 * 2, n_layers=2, n_heads=heads, vocab_size=211)).eval()  # eval: dropout off
+    mm = Transformer(ModelArgs(dim=96 * 2, n_layers=2, n_heads=heads, vocab_size=211, dropout=0.0))
+    mm.load_state_dict(rm.state_dict())
+    x = torch.randint(0, 211, (3, 16))
+    y = torch.randint(0, 211, (3, 16))
+    lr = rm(x)
+    lm = mm(x)
+    assert torch.allclose(lr, lm, atol=2e-5, rtol=1e-4), (lr - lm).abs().max()
+    ce = torch.nn.CrossEntropyLoss()
+    ce(lr.reshape(-1, 211), y.reshape(-1)).backward()
+    ce(lm.reshape(-1, 211), y.reshape(-1)).backward()
+    rg = dict(rm.named_parameters())
+    for n, p in mm.named_parameters():
+        assert p.grad is not None, n
+        assert torch.allclose(p.grad, rg[n].grad, atol=3e-5, rtol=1e-3), (n, (p.grad - rg[n].grad).abs().max())
+
+
+def test_pruned_model_is_a_stage():
+    torch.manual_seed(1)
+    args = ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=97, dropout=0.0, ffn_dim=128)
+    full = Transformer(args)
+    x = torch.randint(0, 97, (2, 8))
+    want = full(x)
+    import copy
+    s0, s1 = copy.deepcopy(full), copy.deepcopy(full)
+    for i in ("2", "3"):
+        del s0.layers[i]
+    s0.norm = None
+    s0.output = None
+    for i in ("0", "1"):
+        del s1.layers[i]
+    s1.tok_embeddings = None
+    mid = s0(x)
+    assert mid.shape == (2, 8, 64)
+    got = s1(mid)
+    assert torch.allclose(want, got, atol=1e-5)
+    assert set(s0.state_dict()) | set(s1.state_dict()) == set(full.state_dict())
+    assert not (set(s0.state_dict()) & set(s1.state_dict()))
+
+
+def test_dropout_is_deterministic_and_active():
+    args = ModelArgs(dim=64, n_layers=1, n_heads=4, vocab_size=50, ffn_dim=128)
+    m = Transformer(args)
+    x = torch.randint(0, 50, (2, 8))
+    m.set_seed(5)
+    a = m(x)
+    m.set_seed(5)
+    b = m(x)
+    m.set_seed(6)
+    c = m(x)
+    assert torch.equal(a, b)
+    assert not torch.equal(a, c)
+    m.eval()
+    d1, d2 = m(x), m(x)
+    assert torch.equal(d1, d2)
