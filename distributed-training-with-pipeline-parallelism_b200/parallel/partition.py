@@ -1,0 +1,113 @@
+"""Stage partitioner: which layers (and which of embedding / final norm / LM head) a pipeline stage owns.
+
+``reference_ranges`` reproduces the helper's rule exactly (/root/reference/LLMsDistributedTrainingHelper.py:70-75):
+``layers_per_stage = n_layers // num_stages``, stage i keeps ``[i*lps, (i+1)*lps)`` and the LAST stage takes the
+remainder.  ``balanced_ranges`` is the cost-aware alternative: the LM head costs
+about as much as a decoder layer and the embedding is nearly free, so the last stage gets fewer layers.
+
+``prune_to_stage`` turns a full ``Transformer`` into the stage's sub-model in place by deleting ``ModuleDict``
+entries (global layer indices are preserved, so the union of the stages' ``state_dict()`` is the full checkpoint
+with no key translation -- SURVEY.md section 2.3).  ``build_stage_model`` constructs a stage directly without
+ever materialising the full model (reference quirk 5: every rank builds the whole model first, helper:207).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+
+from ..models import ModelArgs, Transformer
+from ..models.transformer import DecoderLayer
+
+
+def reference_ranges(n_layers: int, num_stages: int) -> List[Tuple[int, int]]:
+    lps = n_layers // num_stages
+    out = []
+    for s in range(num_stages):
+        start = s * lps
+        end = start + lps if s < num_stages - 1 else n_layers
+        out.append((start, end))
+    return out
+
+
+def balanced_ranges(n_layers: int, num_stages: int, args: Optional[ModelArgs] = None, seq_len: int = 1024) -> List[Tuple[int, int]]:
+    """Contiguous split minimising the most expensive stage, with the LM head (and loss) charged to the last one."""
+    if args is None:
+        layer_cost, head_cost = 1.0, 1.0
+    else:
+        d, f, V = args.dim, args.ffn_dim, args.vocab_size
+        blocks = 2 if args.cross_attn else 1
+        layer_cost = blocks * (8 * d * d + 4 * seq_len * d) + 4 * d * f
+        head_cost = 2 * d * V + 6 * V  # GEMM + the softmax-xent pass
+    # DP over (stage, first layer of the stage): minimise (most expensive stage, then sum of squared costs);
+    # every stage gets at least one layer when there are enough layers.
+    INF = (float("inf"), float("inf"))
+    S, L = num_stages, n_layers
+    min_layers = 1 if L >= S else 0
+    best = [[INF] * (L + 1) for _ in range(S + 1)]   # best[s][i]: stages s.. cover layers i..L-1
+    cut = [[L] * (L + 1) for _ in range(S + 1)]
+    for i in range(L + 1):
+        if L - i >= min_layers:
+            c = (L - i) * layer_cost + head_cost
+            best[S - 1][i] = (c, c * c)
+    for s in range(S - 2, -1, -1):
+        for i in range(L + 1):
+            for j in range(i + min_layers, L + 1):
+                nxt = best[s + 1][j]
+                if nxt[0] == float("inf"):
+                    continue
+                c = (j - i) * layer_cost
+                w = (max(c, nxt[0]), c * c + nxt[1])
+                if w < best[s][i]:
+                    best[s][i], cut[s][i] = w, j
+    out, i = [], 0
+    for s in range(S):
+        j = cut[s][i] if s < S - 1 else L
+        out.append((i, j))
+        i = j
+    return out
+
+
+def stage_ranges(n_layers: int, num_stages: int, rule: str = "reference", args: Optional[ModelArgs] = None,
+                 seq_len: int = 1024) -> List[Tuple[int, int]]:
+    if rule == "reference":
+        return reference_ranges(n_layers, num_stages)
+    if rule == "balanced":
+        return balanced_ranges(n_layers, num_stages, args, seq_len)
+    raise ValueError(f"unknown partition rule {rule!r}")
+
+
+def prune_to_stage(model: Transformer, stage_index: int, num_stages: int, rule: str = "reference",
+                   seq_len: int = 1024) -> Transformer:
+    """In-place pruning, same observable result as helper:60-91."""
+    n_layers = len(model.layers)
+    start, end = stage_ranges(n_layers, num_stages, rule, model.args, seq_len)[stage_index]
+    for i in [k for k in model.layers.keys() if not (start <= int(k) < end)]:
+        del model.layers[i]
+    if stage_index != 0:
+        model.tok_embeddings = None
+    if stage_index != num_stages - 1:
+        model.norm = None
+        model.output = None
+    return model
+
+
+def build_stage_model(args: ModelArgs, stage_index: int, num_stages: int, rule: str = "reference", seq_len: int = 1024,
+                      device: Optional[torch.device] = None, seed: Optional[int] = None) -> Transformer:
+    """Build ONLY the modules of one stage (meta-device skeleton, then materialise the slice)."""
+    start, end = stage_ranges(args.n_layers, num_stages, rule, args, seq_len)[stage_index]
+    with torch.device("meta"):
+        skel = Transformer(ModelArgs(**{**args.__dict__, "n_layers": 0}))
+    model = skel
+    model.args = args
+    gen_dev = device if device is not None else torch.device("cpu")
+    if seed is not None:
+        torch.manual_seed(seed + 7919 * stage_index)
+    with torch.device(gen_dev):
+        for i in range(start, end):
+            model.layers[str(i)] = DecoderLayer(args)
+        full_tail = Transformer(ModelArgs(**{**args.__dict__, "n_layers": 0}))
+    model.tok_embeddings = full_tail.tok_embeddings if stage_index == 0 else None
+    model.norm = full_tail.norm if stage_index == num_stages - 1 else None
+    model.output = full_tail.output if stage_index == num_stages - 1 else None
+    return model

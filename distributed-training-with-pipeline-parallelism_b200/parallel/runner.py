@@ -1,0 +1,354 @@
+"""Schedule runner: interprets a rank's lowered action list on CUDA streams (or on the CPU with gloo).
+
+Behavioural counterpart of torch's ``PipelineScheduleSingle/Multi.step`` + ``_PipelineScheduleRuntime``
+(schedules.py:506-630, :1855-2279), which the reference drives from
+/root/reference/LLMsDistributedTrainingHelper.py:113-131 (``schedule.step(x)`` on the first rank,
+``schedule.step(target=y, losses=losses)`` on the last, ``schedule.step()`` in between).
+
+Design:
+  * ONE interpreter for all three schedules: GPipe, 1F1B and Interleaved-1F1B differ only in the action list;
+  * no host-blocking waits on CUDA: receives are posted on dedicated anchor streams into a persistent, pre-sized
+    ring (one buffer per stage x direction x micro-batch) and consumers wait on CUDA events; sends are issued
+    right behind the producing compute and complete asynchronously on NCCL's per-peer streams, so the transfer
+    of micro-batch i+1 overlaps the compute of micro-batch i and the critical path carries no exposed copy;
+  * every compute action is bracketed by CUDA events -> measured timeline -> measured bubble fraction;
+  * gradient averaging over micro-batches and data-parallel replicas is folded into the fused optimizer kernel;
+    the optimizer step is part of the schedule (``{s}OPTIM``), i.e. inside the timed region.
+"""
+from __future__ import annotations
+
+import time
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
+
+import torch
+import torch.distributed as dist
+
+from .schedule import Action, ActionType as T, build_schedule, theoretical_bubble
+from .schedule import ir as sched_ir
+from .stage import PipelineStage
+
+
+class PipelineSchedule:
+    schedule_name = "1F1B"
+
+    def __init__(self, stages: Union[PipelineStage, Sequence[PipelineStage]], n_microbatches: int, loss_fn=None, *,
+                 schedule: Optional[str] = None, pp_group=None, dp_group=None, optimizer: Optional[dict] = None,
+                 scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None):
+        self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
+        if not self.stages:
+            raise ValueError("need at least one stage")
+        self.name = schedule or self.schedule_name
+        self.m = int(n_microbatches)
+        self.loss_fn = loss_fn
+        # a python loss_fn is honoured through one autograd hop; loss_fn=None or fused_loss=True uses the fused
+        # softmax-cross-entropy kernel (mean token CE, identical to helper:197-201)
+        self.fused_loss = (loss_fn is None) if fused_loss is None else fused_loss
+        self.pp_group = pp_group
+        self.dp_group = dp_group
+        self.optimizer = optimizer
+        self.scale_grads = scale_grads
+        self.record_timeline = record_timeline
+        if dist.is_available() and dist.is_initialized():
+            self.pp_size = dist.get_world_size(pp_group)
+            self.pp_rank = dist.get_rank(pp_group)
+            self.dp_size = dist.get_world_size(dp_group) if dp_group is not None else 1
+        else:
+            self.pp_size, self.pp_rank, self.dp_size = 1, 0, 1
+        self.n_virtual = len(self.stages)
+        self.num_stages = self.pp_size * self.n_virtual
+        for st in self.stages:
+            if st.num_stages != self.num_stages:
+                raise ValueError(f"stage {st.stage_index} was built for {st.num_stages} stages, schedule has {self.num_stages}")
+            if st.stage_index % self.pp_size != self.pp_rank:
+                raise ValueError(f"stage {st.stage_index} does not belong to pipeline rank {self.pp_rank} (loop placement)")
+        self.local: Dict[int, PipelineStage] = {st.stage_index: st for st in self.stages}
+        self.device = self.stages[0].device
+        self.cuda = self.device.type == "cuda"
+        order = build_schedule(self.name, self.pp_size, self.m, n_virtual=self.n_virtual,
+                               dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None)
+        self.full_order = order
+        self.order: List[Action] = order[self.pp_rank]
+        self.theory_bubble = theoretical_bubble(self.pp_size, self.m, self.n_virtual)
+        self._shape: Optional[Tuple[int, int]] = None
+        self._ring: Dict[Tuple[int, str, int], torch.Tensor] = {}
+        self._anchors: Dict[str, Any] = {}
+        self.timeline: List[Tuple[Action, Any, Any]] = []
+        self._step_span: Optional[Tuple[Any, Any]] = None
+        self.steps_done = 0
+        for st in self.stages:
+            st.materialize()
+
+    # ---- helpers ------------------------------------------------------------------------------------------------
+    def _global_rank(self, pp_rank: int) -> int:
+        if self.pp_group is None:
+            return pp_rank
+        return dist.get_global_rank(self.pp_group, pp_rank)
+
+    def _rank_of_stage(self, stage: int) -> int:
+        return stage % self.pp_size
+
+    def _sync_shape(self, x: Optional[torch.Tensor]) -> Tuple[int, int]:
+        """One-time (B, S) agreement: the rank that owns stage 0 knows it from its input.  Replaces torch's
+        pickle-based per-step shape inference (stage.py:1421-1533)."""
+        if self._shape is not None:
+            return self._shape
+        if self.pp_size == 1:
+            if x is None:
+                raise ValueError("the single pipeline rank needs the input batch")
+            self._shape = (int(x.shape[0]), int(x.shape[1]))
+            return self._shape
+        dev = self.device if self.cuda else torch.device("cpu")
+        t = torch.zeros(2, dtype=torch.int64, device=dev)
+        if 0 in self.local:
+            if x is None:
+                raise ValueError("the rank that owns stage 0 must be given the input batch")
+            t[0], t[1] = int(x.shape[0]), int(x.shape[1])
+        dist.broadcast(t, src=self._global_rank(self._rank_of_stage(0)), group=self.pp_group)
+        self._shape = (int(t[0].item()), int(t[1].item()))
+        return self._shape
+
+    def _mb_sizes(self, B: int) -> List[int]:
+        """torch.tensor_split semantics (uneven batches allowed; microbatch.py:315-427)."""
+        base, rem = divmod(B, self.m)
+        return [base + (1 if i < rem else 0) for i in range(self.m)]
+
+    def _ring_buf(self, stage: int, kind: str, mb: int, b: int, S: int) -> torch.Tensor:
+        key = (stage, kind, mb)
+        buf = self._ring.get(key)
+        if buf is None or buf.shape[0] != b:
+            st = self.local[stage]
+            buf = torch.empty((b, S, st.args.dim), dtype=st.dtype, device=self.device)
+            self._ring[key] = buf
+        return buf
+
+    # ---- the step -------------------------------------------------------------------------------------------------
+    def step(self, *args, target: Optional[torch.Tensor] = None, losses: Optional[list] = None,
+             return_outputs: bool = True):
+        """Run one full training step (all micro-batches forward + backward, gradient reduction, optimizer)."""
+        x = args[0] if args else None
+        B, S = self._sync_shape(x)
+        sizes = self._mb_sizes(B)
+        x_chunks = list(torch.tensor_split(x, self.m, dim=0)) if (x is not None and 0 in self.local) else None
+        last_stage = self.num_stages - 1
+        y_chunks = list(torch.tensor_split(target, self.m, dim=0)) if (target is not None and last_stage in self.local) else None
+        for st in self.stages:
+            st.begin_step()
+
+        cuda = self.cuda
+        compute = torch.cuda.current_stream(self.device) if cuda else None
+        if cuda and not self._anchors:
+            self._anchors = {"F": torch.cuda.Stream(self.device), "B": torch.cuda.Stream(self.device)}
+        if cuda:
+            ev0 = compute.record_event()
+            for a in self._anchors.values():
+                a.wait_event(ev0)  # ring buffers of the previous step are no longer in use
+
+        recv_state: Dict[Tuple[int, str, int], Any] = {}
+        fwd_out: Dict[Tuple[int, int], torch.Tensor] = {}
+        bwd_out: Dict[Tuple[int, int], torch.Tensor] = {}
+        local_in: Dict[Tuple[int, str, int], torch.Tensor] = {}
+        send_works: List[Any] = []
+        keep_alive: List[torch.Tensor] = []
+        allreduce_works: Dict[int, Any] = {}
+        timeline: List[Tuple[Action, Any, Any]] = []
+        rec = self.record_timeline
+
+        def tick():
+            if not rec:
+                return None
+            if cuda:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(compute)
+                return e
+            return time.perf_counter()
+
+        t_begin = tick()
+        idx = -1
+        try:
+            for idx, a in enumerate(self.order):
+                typ = a.type
+                if typ == T.RECV_F or typ == T.RECV_B:
+                    kind = "F" if typ == T.RECV_F else "B"
+                    src_stage = a.stage - 1 if kind == "F" else a.stage + 1
+                    buf = self._ring_buf(a.stage, kind, a.mb, sizes[a.mb], S)
+                    src = self._global_rank(self._rank_of_stage(src_stage))
+                    if cuda:
+                        anchor = self._anchors[kind]
+                        with torch.cuda.stream(anchor):
+                            w = dist.irecv(buf, src=src, group=self.pp_group)
+                            w.wait()  # stream-level: the anchor stream waits, the host does not
+                            ev = anchor.record_event()
+                        recv_state[(a.stage, kind, a.mb)] = (buf, ev)
+                    else:
+                        recv_state[(a.stage, kind, a.mb)] = (buf, dist.irecv(buf, src=src, group=self.pp_group))
+                elif typ == T.SEND_F or typ == T.SEND_B:
+                    if typ == T.SEND_F:
+                        t = fwd_out.pop((a.stage, a.mb))
+                        dst_stage = a.stage + 1
+                    else:
+                        t = bwd_out.pop((a.stage, a.mb))
+                        dst_stage = a.stage - 1
+                    t = t.view(sizes[a.mb], S, -1)
+                    dst = self._global_rank(self._rank_of_stage(dst_stage))
+                    send_works.append(dist.isend(t, dst=dst, group=self.pp_group))
+                    keep_alive.append(t)
+                elif typ == T.F:
+                    st = self.local[a.stage]
+                    if a.stage == 0:
+                        inp = x_chunks[a.mb]
+                    else:
+                        inp = self._take_input(recv_state, local_in, a.stage, "F", a.mb, compute)
+                    tgt = y_chunks[a.mb] if (a.stage == last_stage and y_chunks is not None) else None
+                    t0 = tick()
+                    out = st.forward_one_chunk(a.mb, inp, tgt, 1.0, None if self.fused_loss else self.loss_fn)
+                    timeline.append((a, t0, tick()))
+                    if a.stage != last_stage:
+                        if self._rank_of_stage(a.stage + 1) == self.pp_rank:
+                            local_in[(a.stage + 1, "F", a.mb)] = out.view(sizes[a.mb], S, -1)
+                        else:
+                            fwd_out[(a.stage, a.mb)] = out
+                elif typ == T.B:
+                    st = self.local[a.stage]
+                    dout = None
+                    if a.stage != last_stage:
+                        dout = self._take_input(recv_state, local_in, a.stage, "B", a.mb, compute)
+                    t0 = tick()
+                    din = st.backward_one_chunk(a.mb, dout)
+                    timeline.append((a, t0, tick()))
+                    if a.stage != 0:
+                        if self._rank_of_stage(a.stage - 1) == self.pp_rank:
+                            local_in[(a.stage - 1, "B", a.mb)] = din.view(sizes[a.mb], S, -1)
+                        else:
+                            bwd_out[(a.stage, a.mb)] = din
+                elif typ == T.REDUCE_GRAD:
+                    # micro-batch averaging: folded into the optimizer kernel; done explicitly when there is none
+                    if self.optimizer is None and self.scale_grads and self.local[a.stage].n_total:
+                        self.local[a.stage].grad.mul_(1.0 / self.m)
+                elif typ == T.ALLREDUCE:
+                    allreduce_works[a.stage] = self.local[a.stage].all_reduce_grads(async_op=True)
+                elif typ == T.OPTIM:
+                    w = allreduce_works.pop(a.stage, None)
+                    if w is not None:
+                        w.wait()
+                    t0 = tick()
+                    opt = dict(self.optimizer)
+                    gs = (1.0 / self.m if self.scale_grads else 1.0) / self.dp_size
+                    self.local[a.stage].optimizer_step(grad_scale=gs, **opt)
+                    timeline.append((a, t0, tick()))
+                elif typ in (T.UNSHARD, T.RESHARD):
+                    pass
+                else:
+                    raise NotImplementedError(f"action {a} is not executable by this runner")
+        except Exception as e:  # same diagnostics contract as torch's runtime (schedules.py:2257-2269)
+            grid = sched_ir.grid({self.pp_rank: self.order}, error_at=(self.pp_rank, idx))
+            raise RuntimeError(f"[rank {self.pp_rank}] schedule '{self.name}' failed at action {idx} "
+                               f"({self.order[idx] if idx >= 0 else '?'}): {e}\n{grid}") from e
+
+        for w in send_works:
+            w.wait()
+        for w in allreduce_works.values():
+            if w is not None:
+                w.wait()
+        t_end = tick()
+        self.timeline = timeline
+        self._step_span = (t_begin, t_end)
+        self._keep_alive = keep_alive
+        self.steps_done += 1
+
+        out = None
+        if last_stage in self.local:
+            st = self.local[last_stage]
+            if losses is not None:
+                losses.extend(st.losses[i] for i in sorted(st.losses))
+            if return_outputs and st.outputs:
+                out = torch.cat([st.outputs[i] for i in sorted(st.outputs)], dim=0)
+        return out
+
+    def _take_input(self, recv_state, local_in, stage: int, kind: str, mb: int, compute):
+        key = (stage, kind, mb)
+        if key in local_in:
+            return local_in.pop(key)
+        if key not in recv_state:
+            raise RuntimeError(f"compute for stage {stage} micro-batch {mb} ({kind}) started before its receive was posted")
+        buf, handle = recv_state.pop(key)
+        if self.cuda:
+            compute.wait_event(handle)
+        else:
+            handle.wait()
+        return buf
+
+    def eval_step(self, *args, target=None, losses=None):
+        """Forward-only pass (torch's schedule.eval(), schedules.py:248-457): runs the F actions of the GPipe
+        order with dropout off and no gradient work."""
+        saved = (self.order, [st.training for st in self.stages])
+        try:
+            for st in self.stages:
+                st.training = False
+            self.order = [a for a in self.order if a.type in (T.F, T.SEND_F, T.RECV_F)]
+            return self.step(*args, target=target, losses=losses)
+        finally:
+            self.order = saved[0]
+            for st, tr in zip(self.stages, saved[1]):
+                st.training = tr
+                st.stash.clear()
+
+    # ---- measurement ----------------------------------------------------------------------------------------------
+    def measured(self) -> Dict[str, float]:
+        """Resolve the last step's timeline: step span, busy time, measured bubble fraction (this rank)."""
+        if not self.timeline or self._step_span is None or self._step_span[0] is None:
+            return {}
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+            t0 = self._step_span[0]
+            span = t0.elapsed_time(self._step_span[1])
+            busy = sum(s.elapsed_time(e) for a, s, e in self.timeline if a.type.is_compute or a.type == T.OPTIM)
+        else:
+            span = (self._step_span[1] - self._step_span[0]) * 1e3
+            busy = sum((e - s) * 1e3 for a, s, e in self.timeline if a.type.is_compute or a.type == T.OPTIM)
+        return {"step_ms": span, "busy_ms": busy, "bubble_fraction": max(0.0, 1.0 - busy / span) if span > 0 else 0.0,
+                "bubble_theory": self.theory_bubble}
+
+    def trace_events(self) -> List[dict]:
+        """Chrome-trace events (ph='X') of the last step's MEASURED timeline, names = IR strings."""
+        if not self.timeline or self._step_span is None or self._step_span[0] is None:
+            return []
+        evs = []
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+            t0 = self._step_span[0]
+            for a, s, e in self.timeline:
+                evs.append({"name": str(a), "ph": "X", "pid": self.pp_rank, "tid": a.stage,
+                            "ts": t0.elapsed_time(s) * 1e3, "dur": s.elapsed_time(e) * 1e3, "cat": a.type.value})
+        else:
+            t0 = self._step_span[0]
+            for a, s, e in self.timeline:
+                evs.append({"name": str(a), "ph": "X", "pid": self.pp_rank, "tid": a.stage, "ts": (s - t0) * 1e6,
+                            "dur": (e - s) * 1e6, "cat": a.type.value})
+        return evs
+
+
+class ScheduleGPipe(PipelineSchedule):
+    """All forwards then all backwards (torch ScheduleGPipe, used at helper:216)."""
+    schedule_name = "GPipe"
+
+
+class Schedule1F1B(PipelineSchedule):
+    """One-forward-one-backward steady state (torch Schedule1F1B, used at helper:218)."""
+    schedule_name = "1F1B"
+
+
+class ScheduleInterleaved1F1B(PipelineSchedule):
+    """Virtual stages, depth-first interleaved 1F1B (torch ScheduleInterleaved1F1B, used at helper:220)."""
+    schedule_name = "Interleaved1F1B"
+
+
+def make_schedule(name: str, stages, n_microbatches: int, loss_fn=None, **kw) -> PipelineSchedule:
+    cls = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B, "Interleaved1F1B": ScheduleInterleaved1F1B}.get(name)
+    if cls is None:
+        raise ValueError(f"unknown schedule {name!r}")
+    if name != "Interleaved1F1B" and not isinstance(stages, PipelineStage):
+        stages = list(stages)
+        if len(stages) != 1:
+            raise ValueError(f"{name} runs one stage per rank")
+        stages = stages[0]
+    return cls(stages, n_microbatches, loss_fn, **kw)

@@ -1,0 +1,237 @@
+"""Stage runtime: one pipeline stage = a pruned ``Transformer`` + flat parameter/gradient/optimizer arenas +
+per-micro-batch activation stashes, with explicit ``forward_one_chunk`` / ``backward_one_chunk`` entry points.
+
+Behavioural counterpart of torch's ``PipelineStage`` + ``_PipelineStageBase`` (stage.py:116-1604; SURVEY.md
+section 2.2 T11-T13), which the reference instantiates at /root/reference/LLMsDistributedTrainingHelper.py:93.
+Deliberate differences (SURVEY.md section 3.3 "things the new runner must do differently"):
+  * shapes are static, so there is no pickle-based run-time shape inference and no neighbour handshake;
+  * backward is the explicit fused program of ``models.transformer`` (no autograd graph walk);
+  * parameters live in ONE bf16 arena with fp32 master/moment/gradient arenas (memory laid out for the fused
+    AdamW kernel and for a single gradient all-reduce), ``state_dict()`` keys/shapes are untouched;
+  * micro-batch gradient averaging (p.grad.div_(m), torch stage.py:589-591) is folded into the optimizer kernel.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+
+from ..models import Ctx, GradSink, Transformer, stage_backward, stage_forward, stage_loss
+from ..ops import _lib, functional as F
+
+
+_SEED_OFFSETS: Dict[int, torch.Tensor] = {}
+
+
+class PipelineStage:
+    """A stage of the pipeline.  ``submod`` is a (possibly pruned) :class:`Transformer`."""
+
+    def __init__(self, submodule: Transformer, stage_index: int, num_stages: int, device: torch.device,
+                 group=None, dp_group=None):
+        if not (0 <= stage_index < num_stages):
+            raise ValueError(f"stage_index {stage_index} out of range for {num_stages} stages")
+        self.submod = submodule
+        self.stage_index = stage_index
+        self.num_stages = num_stages
+        self.device = torch.device(device)
+        self.group = group
+        self.dp_group = dp_group
+        self.is_first = stage_index == 0
+        self.is_last = stage_index == num_stages - 1
+        self.args = submodule.args
+        self._materialized = False
+        self.stash: Dict[int, dict] = {}
+        self.ctxs: Dict[int, Ctx] = {}
+        self.outputs: Dict[int, torch.Tensor] = {}
+        self.losses: Dict[int, torch.Tensor] = {}
+        self.base_seed = 0
+        self.step_count = 0
+        self.training = True
+        self.has_params = any(True for _ in submodule.parameters())
+
+    # ---- memory layout --------------------------------------------------------------------------------------
+    def materialize(self, dtype: Optional[torch.dtype] = None) -> "PipelineStage":
+        """Move the stage to its device and flatten parameters into arenas (decay group first, then no-decay)."""
+        if self._materialized:
+            return self
+        dev = self.device
+        if dtype is None:
+            dtype = torch.bfloat16 if dev.type == "cuda" else torch.float32
+        self.dtype = dtype
+        params = [(n, p) for n, p in self.submod.named_parameters()]
+        decay = [(n, p) for n, p in params if p.dim() >= 2]
+        no_decay = [(n, p) for n, p in params if p.dim() < 2]
+        ordered = decay + no_decay
+        # 16-byte aligned offsets (in elements; 8 covers bf16 and fp32 vector paths)
+        offs, total = [], 0
+        for _, p in ordered:
+            offs.append(total)
+            total += (p.numel() + 7) // 8 * 8
+        self.n_decay = sum((p.numel() + 7) // 8 * 8 for _, p in decay)
+        self.n_total = total
+        self.param_arena = torch.zeros(max(total, 8), dtype=dtype, device=dev)
+        mixed = dtype != torch.float32
+        self.master = torch.zeros(max(total, 8), dtype=torch.float32, device=dev) if mixed else self.param_arena
+        self.grad = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
+        self.sink = GradSink()
+        self.param_names = []
+        with torch.no_grad():
+            for (n, p), o in zip(ordered, offs):
+                view = self.param_arena[o:o + p.numel()].view(p.shape)
+                src = p.detach()
+                if src.device.type == "meta":
+                    raise RuntimeError(f"parameter {n} is still on the meta device")
+                view.copy_(src.to(device=dev, dtype=dtype))
+                if mixed:
+                    self.master[o:o + p.numel()].view(p.shape).copy_(src.to(device=dev, dtype=torch.float32))
+                p.data = view
+                self.sink.bind(p, self.grad[o:o + p.numel()].view(p.shape))
+                self.param_names.append((n, o, tuple(p.shape)))
+        self.clip_sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.clip_coef = torch.ones(1, dtype=torch.float32, device=dev)
+        if dev.type == "cuda":
+            # step-varying part of every dropout seed lives in device memory (CUDA-graph friendly)
+            key = dev.index if dev.index is not None else torch.cuda.current_device()
+            if key not in _SEED_OFFSETS:  # one per device, shared by all (virtual) stages living on it
+                _SEED_OFFSETS[key] = torch.zeros(1, dtype=torch.int64, device=dev)
+                lib = _lib.load(required=True)
+                with torch.cuda.device(dev):
+                    _lib.check(lib.ppb_set_dropout_offset_ptr(_SEED_OFFSETS[key].data_ptr()), "ppb_set_dropout_offset_ptr")
+            self.seed_offset = _SEED_OFFSETS[key]
+        self._materialized = True
+        return self
+
+    def grad_views(self) -> Dict[str, torch.Tensor]:
+        return {n: self.grad[o:o + int(torch.Size(s).numel())].view(s) for n, o, s in self.param_names}
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """Checkpoint shard of this stage: the reference key layout with GLOBAL layer indices.
+        In mixed precision the fp32 master copy is what gets saved."""
+        if not self._materialized or self.master is self.param_arena:
+            return {k: v.detach().clone() for k, v in self.submod.state_dict().items()}
+        return {n: self.master[o:o + int(torch.Size(s).numel())].view(s).detach().clone() for n, o, s in self.param_names}
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor], strict: bool = True) -> None:
+        own = {n for n, _, _ in self.param_names} if self._materialized else set(self.submod.state_dict())
+        missing = own - set(sd)
+        if strict and missing:
+            raise KeyError(f"stage {self.stage_index}: checkpoint lacks {sorted(missing)[:5]}...")
+        with torch.no_grad():
+            if not self._materialized:
+                self.submod.load_state_dict({k: v for k, v in sd.items() if k in own}, strict=strict)
+                return
+            for n, o, s in self.param_names:
+                if n in sd:
+                    numel = int(torch.Size(s).numel())
+                    src = sd[n].to(self.device)
+                    self.param_arena[o:o + numel].view(s).copy_(src.to(self.dtype))
+                    if self.master is not self.param_arena:
+                        self.master[o:o + numel].view(s).copy_(src.to(torch.float32))
+
+    def optimizer_state_dict(self) -> Dict[str, Dict[str, torch.Tensor]]:
+        out = {}
+        for n, o, s in self.param_names:
+            numel = int(torch.Size(s).numel())
+            out[n] = {"exp_avg": self.exp_avg[o:o + numel].view(s).clone(), "exp_avg_sq": self.exp_avg_sq[o:o + numel].view(s).clone()}
+        return {"state": out, "step": self.step_count}
+
+    def load_optimizer_state_dict(self, osd) -> None:
+        for n, o, s in self.param_names:
+            if n in osd["state"]:
+                numel = int(torch.Size(s).numel())
+                self.exp_avg[o:o + numel].view(s).copy_(osd["state"][n]["exp_avg"].to(self.device))
+                self.exp_avg_sq[o:o + numel].view(s).copy_(osd["state"][n]["exp_avg_sq"].to(self.device))
+        self.step_count = int(osd.get("step", 0))
+
+    # ---- per-step / per-micro-batch ----------------------------------------------------------------------------
+    def begin_step(self) -> None:
+        """Counterpart of torch's stage.clear_runtime_states() (stage.py:512-530)."""
+        self.stash.clear()
+        self.ctxs.clear()
+        self.outputs.clear()
+        self.losses.clear()
+        if self.device.type == "cuda" and self._materialized:
+            self.seed_offset.fill_(self.step_count * 0x632BE5AB)
+
+    def _ctx(self, mb: int, batch: int, seq: int) -> Ctx:
+        off = 0 if self.device.type == "cuda" else self.step_count * 0x632BE5AB
+        return Ctx(self.args, batch, seq, self.base_seed, mb, self.training, off)
+
+    def forward_one_chunk(self, mb: int, inp: torch.Tensor, target: Optional[torch.Tensor] = None,
+                          loss_scale: float = 1.0, loss_fn=None) -> torch.Tensor:
+        """Run the stage forward for micro-batch ``mb``.  ``inp`` is tokens [b, S] on the first stage, activations
+        [b, S, d] otherwise.  On the last stage with a ``target`` the fused loss runs too (its gradient replaces the
+        logits in place).  Returns the stage output ([b*S, d] activations or logits)."""
+        if not self._materialized:
+            self.materialize()
+        b, S = inp.shape[0], inp.shape[1]
+        ctx = self._ctx(mb, b, S)
+        st: dict = {}
+        with torch.no_grad():
+            out = stage_forward(self.submod, inp, ctx, st)
+            if self.is_last and target is not None and self.submod.output is not None:
+                if loss_fn is None:
+                    self.losses[mb] = stage_loss(out, target, loss_scale, st)
+                else:  # arbitrary user loss: one autograd hop over the logits only
+                    with torch.enable_grad():
+                        lg = out.detach().float().view(b, S, -1).requires_grad_(True)
+                        loss = loss_fn(lg, target)
+                        (g,) = torch.autograd.grad(loss * loss_scale, lg)
+                    out.copy_(g.view(out.shape).to(out.dtype))
+                    st["dlogits"] = out
+                    self.losses[mb] = loss.detach().reshape(1).float()
+        self.stash[mb] = st
+        self.ctxs[mb] = ctx
+        if self.is_last and "dlogits" not in st:
+            self.outputs[mb] = out.view(b, S, -1)
+        return out
+
+    def backward_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """Backward for micro-batch ``mb``; ``dout`` is the gradient received from the next stage (None on the last
+        stage: the fused loss already left dlogits in the stash).  Returns the input gradient [b*S, d] or None."""
+        st = self.stash.pop(mb)
+        ctx = self.ctxs.pop(mb)
+        if dout is None:
+            if "dlogits" not in st:
+                raise RuntimeError(f"stage {self.stage_index}: backward of micro-batch {mb} without a gradient or a loss")
+            douts = [st["dlogits"]]
+        else:
+            douts = [dout]
+        with torch.no_grad():
+            return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+
+    # ---- gradient reduction + optimizer ---------------------------------------------------------------------------
+    def all_reduce_grads(self, async_op: bool = False):
+        """Data-parallel all-reduce of the whole gradient arena in one collective (baseline path: NCCL/gloo;
+        the fused in-kernel path lives in ops.collective)."""
+        import torch.distributed as dist
+        if self.dp_group is None or dist.get_world_size(self.dp_group) == 1 or self.n_total == 0:
+            return None
+        return dist.all_reduce(self.grad, group=self.dp_group, async_op=async_op)
+
+    def optimizer_step(self, lr: float = 1e-4, betas=(0.9, 0.95), eps: float = 1e-8, weight_decay: float = 0.1,
+                       grad_scale: float = 1.0, max_grad_norm: Optional[float] = None, clip_coef=None) -> None:
+        """Fused AdamW over the arenas: two launches (decay group / no-decay group)."""
+        if not self._materialized or self.n_total == 0:
+            return
+        self.step_count += 1
+        mixed = self.master is not self.param_arena
+        nd = self.n_decay
+        coef = clip_coef
+        for lo, hi, wd in ((0, nd, weight_decay), (nd, self.n_total, 0.0)):
+            if hi <= lo:
+                continue
+            F.adamw_step(self.param_arena[lo:hi] if mixed else None, self.master[lo:hi], self.exp_avg[lo:hi],
+                         self.exp_avg_sq[lo:hi], self.grad[lo:hi], lr, betas[0], betas[1], eps, wd, self.step_count,
+                         grad_scale, coef, zero_grad=True)
+
+    def zero_grad(self) -> None:
+        if self._materialized:
+            self.grad.zero_()
+
+    def grad_sumsq(self) -> torch.Tensor:
+        self.clip_sumsq.zero_()
+        F.sumsq_accum(self.grad[:self.n_total], self.clip_sumsq)
+        return self.clip_sumsq

@@ -1,0 +1,117 @@
+"""Worker functions for the multi-process tests (must live in an importable module for mp 'spawn')."""
+import copy
+import os
+import sys
+import traceback
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def parity_worker(rank, world_size, schedule_type, n_layers, v, m, results_queue, master_port=None, optimizer=None,
+                  dp=1, device="cpu"):
+    """Pipelined loss + per-parameter grads must equal the single-process full-model ones (same seed, dropout 0)."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.api import manual_model_split, make_schedule
+        from ppb200.parallel.mesh import init_mesh
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        mesh = init_mesh(dp_size=dp, pp_size=world_size // dp)
+        P = mesh.pp_size
+        args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0)
+        torch.manual_seed(1234)
+        full = Transformer(args)
+        B, S = 8 * dp, 16
+        g = torch.Generator().manual_seed(99)
+        x = torch.randint(0, 101, (B, S), generator=g)
+        y = torch.randint(0, 101, (B, S), generator=g)
+        # ---- single-process oracle: mean over micro-batches of the mean token CE (== plain mean for equal chunks)
+        oracle = copy.deepcopy(full)
+        logits = oracle(x)
+        loss_ref = torch.nn.functional.cross_entropy(logits.reshape(-1, 101), y.reshape(-1))
+        loss_ref.backward()
+        ref_grads = {n: p.grad.clone() for n, p in oracle.named_parameters()}
+        # ---- pipelined
+        num_stages = P * v
+        stages = []
+        for i in range(v):
+            mdl = copy.deepcopy(full)
+            st = manual_model_split(mdl, mesh.pp_idx + P * i, num_stages, torch.device("cpu"))
+            st.dp_group = mesh.dp_group
+            stages.append(st)
+        sched = make_schedule(schedule_type, stages, m, None, pp_group=mesh.pp_group, dp_group=mesh.dp_group,
+                              optimizer=None)
+        Bl = B // dp
+        xl, yl = x[mesh.dp_idx * Bl:(mesh.dp_idx + 1) * Bl], y[mesh.dp_idx * Bl:(mesh.dp_idx + 1) * Bl]
+        losses = []
+        first, last = 0 in sched.local, (num_stages - 1) in sched.local
+        sched.step(*((xl,) if first else ()), target=yl if last else None, losses=losses if last else None)
+        max_err = 0.0
+        for st in stages:
+            if dp > 1 and st.n_total:
+                st.grad.div_(dp)  # the schedule's ALLREDUCE action already summed over the replicas
+            for n, gview in st.grad_views().items():
+                err = (gview - ref_grads[n]).abs().max().item()
+                scale = ref_grads[n].abs().max().item() + 1e-8
+                max_err = max(max_err, err / scale)
+        out = {"rank": rank, "max_rel_grad_err": max_err}
+        if last:
+            lp = torch.stack([l.reshape(()) for l in losses]).mean()
+            if dp > 1:
+                dist.all_reduce(lp, group=mesh.dp_group)
+                lp = lp / dp
+            out["loss_err"] = abs(lp.item() - loss_ref.item())
+            out["n_losses"] = len(losses)
+        elif dp > 1:
+            pass
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, out)
+        if rank == 0:
+            results_queue.put({"ranks": gathered, "bubble": sched.measured()})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def train_worker(rank, world_size, schedule_type, results_queue, master_port=None, steps=6):
+    """A few optimizer steps must reduce the loss on a fixed batch (dropout on, AdamW on)."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.api import manual_model_split, make_schedule
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        args = ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.1)
+        v = 2 if schedule_type == "Interleaved1F1B" else 1
+        stages = []
+        for i in range(v):
+            torch.manual_seed(7)
+            st = manual_model_split(Transformer(args), rank + world_size * i, world_size * v, torch.device("cpu"))
+            stages.append(st)
+        sched = make_schedule(schedule_type, stages, 4, None, optimizer={"lr": 3e-3, "weight_decay": 0.0})
+        g = torch.Generator().manual_seed(5)
+        x = torch.randint(0, 101, (8, 16), generator=g)
+        y = torch.randint(0, 101, (8, 16), generator=g)
+        first, last = 0 in sched.local, (world_size * v - 1) in sched.local
+        hist = []
+        for _ in range(steps):
+            losses = []
+            sched.step(*((x,) if first else ()), target=y if last else None, losses=losses if last else None)
+            if last:
+                hist.append(torch.stack([l.reshape(()) for l in losses]).mean().item())
+        if last:
+            results_queue.put({"losses": hist})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

@@ -1,0 +1,56 @@
+"""Multi-process CPU (gloo) end-to-end tests: the parity oracle of SURVEY.md section 4 -- pipelined loss and
+per-parameter gradients == single-process full-model loss/gradients, for all three schedules, world sizes 2 and 4,
+virtual stages, and a (dp=2, pp=2) mesh; plus the reference-compatible experiment API."""
+import pytest
+
+from ppb200.parallel.launch import launch_workers
+from tests._workers import parity_worker, train_worker
+
+pytestmark = pytest.mark.timeout(600)
+
+
+@pytest.mark.parametrize("schedule,world,n_layers,v,m", [
+    ("GPipe", 2, 4, 1, 4),
+    ("1F1B", 2, 4, 1, 4),
+    ("Interleaved1F1B", 2, 4, 2, 4),
+    ("GPipe", 4, 4, 1, 8),
+    ("1F1B", 4, 5, 1, 4),          # 5 layers on 4 stages: the last stage takes the remainder (helper:74-75)
+    ("Interleaved1F1B", 4, 8, 2, 8),
+])
+def test_pipeline_matches_single_process(schedule, world, n_layers, v, m):
+    res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), timeout=400)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["max_rel_grad_err"] < 2e-4, r
+        if "loss_err" in r:
+            assert r["loss_err"] < 1e-5, r
+            assert r["n_losses"] == m
+    assert 0.0 <= res["bubble"]["bubble_fraction"] < 1.0
+
+
+def test_dp2_pp2_mesh_matches_single_process():
+    res = launch_workers(parity_worker, 4, ("1F1B", 4, 1, 4), {"dp": 2}, timeout=400)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["max_rel_grad_err"] < 2e-4, r
+        if "loss_err" in r:
+            assert r["loss_err"] < 1e-5, r
+
+
+@pytest.mark.parametrize("schedule", ["1F1B", "Interleaved1F1B"])
+def test_training_reduces_loss(schedule):
+    res = launch_workers(train_worker, 2, (schedule,), timeout=400)
+    assert "error" not in res, res
+    assert res["losses"][-1] < res["losses"][0] - 0.05, res
+
+
+def test_reference_api_run_one_experiment():
+    """BASELINE.json config 1 plumbing: GPipe, 4 stages x 8 micro-batches, world_size 4 on CPU/gloo."""
+    from ppb200.api import run_one_experiment
+    res = run_one_experiment(4, 4, 4, "GPipe", batch_size=16, seq_length=16, num_iterations=2, n_microbatches=8,
+                             dim=64, vocab_size=128, warmup=1)
+    assert "error" not in res, res
+    assert set(["elapsed_time", "throughput", "tokens_processed"]) <= set(res)
+    assert res["tokens_processed"] == 16 * 16 * 2
+    assert res["throughput"] > 0
+    assert abs(res["bubble_theory"] - 3 / 11) < 1e-9
