@@ -27,6 +27,7 @@ def _declare(lib) -> None:
     lib.ppb_last_error.argtypes = []
     lib.ppb_version.restype = I
     sigs = {
+        "ppb_set_dropout_offset_ptr": [P],
         "ppb_gemm_bf16": [P, P, P, I, I, I, L, L, L, I, I, I, I, F, P, P, L, U, F, I, I, P],
         "ppb_add_dropout_norm_fwd": [P, P, P, P, P, P, P, P, I, I, F, F, U, I, P],
         "ppb_norm_bwd": [P, P, P, P, P, P, P, P, P, P, P, P, L, I, I, F, U, I, P],
