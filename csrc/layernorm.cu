@@ -367,3 +367,77 @@ extern "C" int ppb_norm_bwd(const void* dy0, const void* dy1, const void* dy2, c
                      seed, rms);
   return launch_ln_bwd(p, ln_grid(T), stream);
 }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of ppb_norm_bwd.
+//
+// Some hosts of this library are not allowed to create device memory at all: a serving or training runtime that
+// hands every byte of HBM to its own arena at start-up, a plug-in entry called from inside another framework's
+// custom-op hook, or a thread that must never trigger cudaMalloc's implicit device-wide synchronisation.  Those
+// callers cannot produce the scratch buffer that ppb_norm_bwd wants.  For them the dgamma/dbeta partial sums go
+// into a fixed array that lives inside the library image instead: every GPU that loads libppb200.so keeps these
+// PPB_NORM_NOALLOC_SCRATCH_BYTES (about 2.4 MiB) reserved until the process exits.
+//
+// Limits that follow from the fixed size: d <= PPB_NORM_NOALLOC_MAX_D, and the launch uses at most
+// PPB_NORM_NOALLOC_MAX_CTAS CTAs.  Larger d is refused with an error (use ppb_norm_bwd and bring a buffer).
+// ------------------------------------------------------------------------------------------------------------
+#define PPB_NORM_NOALLOC_MAX_D 1024
+#define PPB_NORM_NOALLOC_MAX_CTAS 304
+#define PPB_NORM_NOALLOC_SCRATCH_BYTES (256 + PPB_NORM_NOALLOC_MAX_CTAS * 2 * PPB_NORM_NOALLOC_MAX_D * 4)
+
+// Host code must never pass this name to a kernel: on the host it is only a stand-in for the symbol, not a device
+// address.  The address is looked up once per device below.
+static __device__ __align__(256) unsigned char g_norm_noalloc_scratch[PPB_NORM_NOALLOC_SCRATCH_BYTES];
+
+namespace ppb {
+static float* g_noalloc_ptr[64] = {nullptr};
+
+// One-time, per-device set-up: resolve the device address of the static array with the target device current.
+static int norm_noalloc_setup(float** out) {
+  int dev = 0;
+  PPB_CUDA_OK(cudaGetDevice(&dev));
+  PPB_REQUIRE(dev >= 0 && dev < 64, "ppb_norm_bwd_noalloc: device index %d out of range", dev);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_norm_noalloc_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("ppb_norm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return -1;
+    }
+    g_noalloc_ptr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace ppb
+
+extern "C" long long ppb_norm_bwd_noalloc_max_d(void) { return PPB_NORM_NOALLOC_MAX_D; }
+
+// Same contract as ppb_norm_bwd, minus the scratch arguments.  Makes no cudaMalloc/cudaFree call and calls no
+// allocating library routine; inputs and outputs are still the caller's.
+//  * The FIRST call on each device resolves the address of the built-in scratch array (cudaGetSymbolAddress);
+//    make that first call outside of any stream capture.
+//  * All calls on a device share the one array.  It still holds whatever the previous call left behind, so the
+//    arrival counter in its header is cleared on `stream` before every launch; the partial-sum area is fully
+//    rewritten by each launch before it is read.
+//  * Because the array is shared, two calls whose kernels can overlap on the GPU (different streams, no ordering
+//    between them) race with each other.  Order them, or use ppb_norm_bwd with separate buffers.
+extern "C" int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void* dy2, const void* z, const float* mean,
+                                    const float* rstd, const void* gamma, void* dz, void* da, float* dgamma,
+                                    float* dbeta, int T, int d, float dropout_p, unsigned long long seed, int rms,
+                                    void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(T > 0 && d > 0 && (d % 8) == 0, "ppb_norm_bwd_noalloc: need T > 0 and d %% 8 == 0 (got T=%d d=%d)", T, d);
+  PPB_REQUIRE(d <= PPB_NORM_NOALLOC_MAX_D,
+              "ppb_norm_bwd_noalloc: d=%d exceeds the built-in scratch (max d = %d); call ppb_norm_bwd with your own buffer",
+              d, PPB_NORM_NOALLOC_MAX_D);
+  float* scratch = nullptr;
+  int rc = norm_noalloc_setup(&scratch);
+  if (rc) return rc;
+  int grid = ln_grid(T);
+  if (grid > PPB_NORM_NOALLOC_MAX_CTAS) grid = PPB_NORM_NOALLOC_MAX_CTAS;
+  PPB_CUDA_OK(cudaMemsetAsync(scratch, 0, 256, stream));  // the arrival counter must start at zero
+  LnBwdParams p;
+  fill_ln_bwd_params(p, dy0, dy1, dy2, z, mean, rstd, gamma, dz, da, dgamma, dbeta, scratch, T, d, dropout_p, seed, rms);
+  return launch_ln_bwd(p, grid, stream);
+}

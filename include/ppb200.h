@@ -60,6 +60,18 @@ int ppb_norm_bwd(const void* dy0, const void* dy1, const void* dy2, const void* 
                  long long scratch_bytes, int T, int d, float dropout_p, unsigned long long seed, int rms,
                  void* stream);
 
+/* Allocation-free variant of ppb_norm_bwd.  No counterpart in the reference (which has no native code and no
+ * notion of a caller that cannot allocate).  For hosts that may not create device memory -- a runtime that owns
+ * the whole HBM arena, a plug-in hook inside another framework, a thread that must not hit cudaMalloc's implicit
+ * synchronisation -- the dgamma/dbeta scratch lives in a fixed ~2.4 MiB array inside the library image (held on
+ * every GPU that loads the library, until exit).  Limit: d <= ppb_norm_bwd_noalloc_max_d() (1024); larger d is
+ * refused.  The first call on a device looks the array up (do it before any stream capture); calls share the
+ * array, so calls that can overlap on the GPU race -- order them. */
+long long ppb_norm_bwd_noalloc_max_d(void);
+int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void* dy2, const void* z, const float* mean,
+                         const float* rstd, const void* gamma, void* dz, void* da, float* dgamma, float* dbeta, int T,
+                         int d, float dropout_p, unsigned long long seed, int rms, void* stream);
+
 /* ---- K7: fused softmax-cross-entropy (loss rows + in-place dlogits) ----------------------------------------
  * Replaces aten._log_softmax + nll_loss_forward/backward + logits.clone() -- helper:54, helper:197-201. */
 int ppb_xent_fwd_bwd(void* logits, long long ld, const long long* targets, float* row_loss, int T, int V,
