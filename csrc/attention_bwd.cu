@@ -88,10 +88,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   auto qdo_full = [&](int s) { return bar_base + 8u * (1 + s); };
   auto qdo_empty = [&](int s) { return bar_base + 8u * (3 + s); };
   const uint32_t sdp_full = bar_base + 8u * 5;    // S and dP ready in TMEM            (tcgen05.commit)
-  const uint32_t sdp_empty = bar_base + 8u * 6;   // compute warps have read S and dP   (256 arrivals)
-  const uint32_t pds_full = bar_base + 8u * 7;    // P and dS tiles written to smem     (256 arrivals)
+  const uint32_t sdp_empty = bar_base + 8u * 6;   // compute warps have read S and dP   (8 warp-elected arrivals)
+  const uint32_t pds_full = bar_base + 8u * 7;    // P and dS tiles written to smem     (8 warp-elected arrivals)
   const uint32_t dq_full = bar_base + 8u * 8;     // dV/dK/dQ GEMMs of this tile done   (tcgen05.commit)
-  const uint32_t dq_empty = bar_base + 8u * 9;    // dQ drained from TMEM               (256 arrivals)
+  const uint32_t dq_empty = bar_base + 8u * 9;    // dQ drained from TMEM               (8 warp-elected arrivals)
   const uint32_t fin_full = bar_base + 8u * 10;   // all GEMMs of the CTA done
   const uint32_t tmem_ptr_smem = bar_base + 8u * 11;
 
@@ -121,10 +121,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_init(qdo_empty(s), 1);
     }
     mbar_init(sdp_full, 1);
-    mbar_init(sdp_empty, 256);
-    mbar_init(pds_full, 256);
+    mbar_init(sdp_empty, 8);
+    mbar_init(pds_full, 8);
     mbar_init(dq_full, 1);
-    mbar_init(dq_empty, 256);
+    mbar_init(dq_empty, 8);
     mbar_init(fin_full, 1);
     fence_mbar_init();
   }
@@ -240,8 +240,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
       tc_fence_before();
-      mbar_arrive(dq_empty);
       fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_empty);
       named_bar_sync(1, 256);
       if (warp == 0 && lane == 0) {
         const int qrow = (i_start + it_prev) * 128;
@@ -282,10 +283,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           dsv[i] = __uint_as_float(rd[i]);
         }
         if (p.drop_thresh) {
-          const unsigned long long base = drop_row + (unsigned long long)kvb;
+          const DropoutStream dstr(seed_eff, (drop_row + (unsigned long long)kvb) >> 1);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = dropout_pair_bits(seed_eff, (base + i) >> 1);
+            const uint32_t hsh = dstr.bits(i >> 1);
             const float k0 = ((hsh & 0xFFFFu) >= p.drop_thresh) ? p.drop_scale : 0.f;
             const float k1 = ((hsh >> 16) >= p.drop_thresh) ? p.drop_scale : 0.f;
             dsv[i] = pv[i] * (dsv[i] * k0 - dlt) * p.scale;
@@ -313,9 +314,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
       tc_fence_before();
-      mbar_arrive(sdp_empty);
       fence_proxy_async_smem();
-      mbar_arrive(pds_full);
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(sdp_empty);
+        mbar_arrive(pds_full);
+      }
     }
     drain_dq(n_it - 1);
     // ---- dV, dK: TMEM -> bf16 -> swizzled staging (the P / dS tiles are free now) -> TMA store ----

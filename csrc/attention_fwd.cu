@@ -110,10 +110,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     for (int t = 0; t < 2; ++t) {
       mbar_init(s_full(t), 1);
-      mbar_init(s_empty(t), 128);
-      mbar_init(p_full(t), 128);
+      mbar_init(s_empty(t), 4);
+      mbar_init(p_full(t), 4);
       mbar_init(pv_full(t), 1);
-      mbar_init(pv_empty(t), 128);
+      mbar_init(pv_empty(t), 4);
     }
     fence_mbar_init();
   }
@@ -249,7 +249,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
         }
         tc_fence_before();
-        mbar_arrive(pv_empty(t));
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pv_empty(t));
       }
       if (alpha != 1.f) {
 #pragma unroll
@@ -277,12 +278,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           pr[i] = e;
         }
         if (p.drop_thresh) {
-          const unsigned long long base = drop_row + (unsigned long long)(kv0 + c * 32);
+          // kept probabilities are NOT rescaled here: the constant 1/(1-p) is folded into the final 1/l
+          const DropoutStream ds(seed_eff, (drop_row + (unsigned long long)(kv0 + c * 32)) >> 1);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = dropout_pair_bits(seed_eff, (base + i) >> 1);
-            pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] * p.drop_scale : 0.f;
-            pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] * p.drop_scale : 0.f;
+            const uint32_t hsh = ds.bits(i >> 1);
+            pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
+            pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
           }
         }
         const uint32_t atom = p_row + (c >> 1) * Cfg::CHUNK_BYTES;
@@ -298,9 +300,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       l_run += lsum;
       tc_fence_before();
-      mbar_arrive(s_empty(t));  // S_t may be overwritten by the next QK^T
       fence_proxy_async_smem();
-      mbar_arrive(p_full(t));   // P_t is visible to the tensor core
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(s_empty(t));  // S_t may be overwritten by the next QK^T
+        mbar_arrive(p_full(t));   // P_t is visible to the tensor core
+      }
     }
     // ---- last P*V, normalise, store ----
     mbar_wait(pv_full(t), (n_kv - 1) & 1);
@@ -313,7 +318,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
       for (int i = 0; i < 32; ++i) o[c * 32 + i] += __uint_as_float(r[i]);
     }
-    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+    const float inv_l = (l_run > 0.f ? 1.f / l_run : 0.f) * (p.drop_thresh ? p.drop_scale : 1.f);
     if (q_idx < p.Sq) p.lse[((long long)(b * p.H + h)) * p.Sq + q_idx] = (m_run + log2f(l_run)) * 0.6931471805599453f;
     // stage O (bf16) through the (now free) P region of this warpgroup: NV chunks of [128 rows x 128 B]
 #pragma unroll

@@ -277,6 +277,23 @@ __host__ __device__ __forceinline__ uint32_t dropout_pair_bits(uint64_t seed, ui
   uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
   return mix32((lo ^ k0) + mix32(hi ^ k1 ^ 0x9e3779b9U));
 }
+// Fast path for runs of consecutive pair indices: the (expensive) mixing of the high word is hoisted out of the
+// inner loop.  bits(i) == dropout_pair_bits(seed, pair0 + i) for every i < 2^32, including across a low-word wrap.
+struct DropoutStream {
+  uint32_t k0, lo0, inner, inner_next;
+  __device__ __forceinline__ DropoutStream(uint64_t seed, uint64_t pair0) {
+    k0 = uint32_t(seed);
+    lo0 = uint32_t(pair0);
+    const uint32_t k1 = uint32_t(seed >> 32), hi = uint32_t(pair0 >> 32);
+    inner = mix32(hi ^ k1 ^ 0x9e3779b9U);
+    inner_next = mix32((hi + 1u) ^ k1 ^ 0x9e3779b9U);
+  }
+  __device__ __forceinline__ uint32_t bits(uint32_t i) const {
+    const uint32_t lo = lo0 + i;
+    return mix32((lo ^ k0) + (lo < lo0 ? inner_next : inner));
+  }
+};
+
 __host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
   float t = p * 65536.0f + 0.5f;
   return t <= 0.f ? 0u : (t >= 65535.f ? 65535u : uint32_t(t));

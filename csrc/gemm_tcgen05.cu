@@ -218,11 +218,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           if (p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
             const unsigned long long seed_eff = p.seed + (p.seed_off ? *p.seed_off : 0ull);
-            const unsigned long long base = (unsigned long long)row * (unsigned long long)p.N + nc;
+            // N is even for every dropout caller, so (row*N + nc + j) is even for even j and shares one pair hash
+            const DropoutStream ds(seed_eff, ((unsigned long long)row * (unsigned long long)p.N + nc) >> 1);
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 2) {
-              // N is even for every dropout caller, so (base + j) is even and shares one pair hash
-              const uint32_t h = dropout_pair_bits(seed_eff, (base + j) >> 1);
+              const uint32_t h = ds.bits(j >> 1);
               v[j] = ((h & 0xFFFFu) >= p.drop_thresh) ? v[j] * p.drop_scale : 0.f;
               v[j + 1] = ((h >> 16) >= p.drop_thresh) ? v[j + 1] * p.drop_scale : 0.f;
             }

@@ -6,8 +6,8 @@
 //
 // One warp owns one row; a row lives entirely in registers (d <= 2048), so every tensor is read exactly
 // once and written exactly once.  The dropout mask is regenerated from (seed, element index) and is never
-// stored.  dgamma/dbeta partials are reduced warp -> CTA -> scratch, and the last CTA to finish folds the
-// scratch into the fp32 gradient accumulators (which persist across micro-batches).
+// stored.  dgamma/dbeta partials are reduced warp -> CTA (smem tree) -> scratch, and a second small kernel folds the
+// scratch, column slab by column slab, into the fp32 gradient accumulators (which persist across micro-batches).
 //
 // Replaces aten.add + bernoulli_/div_/mul + native_layer_norm(_backward) of the reference's op stream
 // (torch nn.TransformerDecoderLayer post-LN blocks used at
@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p)
   for (int row = blockIdx.x * LN_WARPS + warp; row < p.T; row += gridDim.x * LN_WARPS) {
     float v[MAXV][8];
     const long long rbase = (long long)row * p.d;
+    const DropoutStream dstr(seed_eff, (unsigned long long)rbase >> 1);  // d is even: a row starts on a pair boundary
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
@@ -64,7 +65,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p)
           const float2 r2 = unpack_bf16(rw[q]);
           float2 a2 = unpack_bf16(aw[q]);
           if (p.thresh) {
-            const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
+            const uint32_t h = dstr.bits(c * 4 + q);
             a2.x = ((h & 0xFFFFu) >= p.thresh) ? a2.x * p.scale : 0.f;
             a2.y = ((h >> 16) >= p.thresh) ? a2.y * p.scale : 0.f;
           }
@@ -131,7 +132,7 @@ struct LnBwdParams {
   bf16* da;  // [T, d] nullable: dropout'(dz) for the sub-layer branch (null => caller aliases dz)
   float* dgamma;  // [d] fp32 accumulators (+=)
   float* dbeta;   // nullable
-  float* scratch;  // 256-byte header (arrival counter, zero between launches) + [grid, 2, d] partials
+  float* scratch;  // 256-byte reserved header + [grid, 2, d] partials
   int T, d;
   unsigned long long seed;
   const unsigned long long* seed_off;
@@ -142,8 +143,7 @@ struct LnBwdParams {
 
 template <int MAXV>
 __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p) {
-  extern __shared__ float red_smem[];  // [2][d] CTA-level partial accumulators
-  __shared__ bool is_last;
+  extern __shared__ float red_smem[];  // [LN_WARPS][2][d] per-warp partial accumulators
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = p.d >> 3;
   const float inv_d = 1.f / float(p.d);
@@ -153,11 +153,9 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
   for (int i = 0; i < MAXV; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
-  for (int i = threadIdx.x; i < 2 * p.d; i += LN_THREADS) red_smem[i] = 0.f;
-  __syncthreads();
-
   for (int row = blockIdx.x * LN_WARPS + warp; row < p.T; row += gridDim.x * LN_WARPS) {
     const long long rbase = (long long)row * p.d;
+    const DropoutStream dstr(seed_eff, (unsigned long long)rbase >> 1);
     const float mean = p.rms ? 0.f : p.mean[row];
     const float rstd = p.rstd[row];
     float xh[MAXV][8], gdy[MAXV][8];
@@ -211,7 +209,7 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
           if (p.da) {
             float ax = gx, ay = gy;
             if (p.thresh) {
-              const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)(rbase + c * 8 + 2 * q) >> 1);
+              const uint32_t h = dstr.bits(c * 4 + q);
               ax = ((h & 0xFFFFu) >= p.thresh) ? gx * p.scale : 0.f;
               ay = ((h >> 16) >= p.thresh) ? gy * p.scale : 0.f;
             }
@@ -224,42 +222,56 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
     }
   }
 
-  // warp partials -> CTA partial in smem (shared atomics, d/32 per lane, once per kernel)
+  // warp partials -> smem [warp][2][d] -> CTA partial (plain adds, no atomics) -> scratch[cta][2][d]
+  float* wsm = red_smem + (size_t)warp * 2 * p.d;
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     const int c = lane + 32 * i;
     if (c < nchunks) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        atomicAdd(&red_smem[c * 8 + j], dg[i][j]);
-        atomicAdd(&red_smem[p.d + c * 8 + j], db[i][j]);
-      }
+      *reinterpret_cast<float4*>(wsm + c * 8) = make_float4(dg[i][0], dg[i][1], dg[i][2], dg[i][3]);
+      *reinterpret_cast<float4*>(wsm + c * 8 + 4) = make_float4(dg[i][4], dg[i][5], dg[i][6], dg[i][7]);
+      *reinterpret_cast<float4*>(wsm + p.d + c * 8) = make_float4(db[i][0], db[i][1], db[i][2], db[i][3]);
+      *reinterpret_cast<float4*>(wsm + p.d + c * 8 + 4) = make_float4(db[i][4], db[i][5], db[i][6], db[i][7]);
     }
   }
   __syncthreads();
-  float* parts = p.scratch + 64;  // first 256 bytes of the scratch hold the arrival counter
+  float* parts = p.scratch + 64;  // the first 256 bytes of the scratch are a reserved header
   float* part = parts + (size_t)blockIdx.x * 2 * p.d;
-  for (int i = threadIdx.x; i < 2 * p.d; i += LN_THREADS) part[i] = red_smem[i];
-  __threadfence();
-  __syncthreads();
-  unsigned int* counter = reinterpret_cast<unsigned int*>(p.scratch);
-  if (threadIdx.x == 0) {
-    const unsigned int prev = atomicAdd(counter, 1u);
-    is_last = (prev == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (is_last) {
-    __threadfence();
-    for (int col = threadIdx.x; col < p.d; col += LN_THREADS) {
-      float sg = 0.f, sb = 0.f;
-      for (int b = 0; b < (int)gridDim.x; ++b) {
-        sg += __ldcg(parts + (size_t)b * 2 * p.d + col);
-        sb += __ldcg(parts + (size_t)b * 2 * p.d + p.d + col);
-      }
-      p.dgamma[col] += sg;
-      if (p.dbeta) p.dbeta[col] += sb;
+  for (int i = threadIdx.x * 4; i < 2 * p.d; i += LN_THREADS * 4) {
+    float4 acc = *reinterpret_cast<const float4*>(red_smem + i);
+#pragma unroll
+    for (int w = 1; w < LN_WARPS; ++w) {
+      const float4 t = *reinterpret_cast<const float4*>(red_smem + (size_t)w * 2 * p.d + i);
+      acc.x += t.x;
+      acc.y += t.y;
+      acc.z += t.z;
+      acc.w += t.w;
     }
-    if (threadIdx.x == 0) *counter = 0u;  // self-resetting: the scratch can be reused by the next launch
+    *reinterpret_cast<float4*>(part + i) = acc;
+  }
+}
+
+// Second phase: column slabs in parallel, each CTA folds `nparts` partial rows into the fp32 accumulators.
+__global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __restrict__ parts, int nparts, int d,
+                                                              float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float red[8][32 * 2 + 2];
+  // block = 32 columns x 8 row-lanes; blockIdx.x covers 2*d columns (dgamma then dbeta)
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = blockIdx.x * 32 + cx;
+  float acc = 0.f;
+  if (col < 2 * d) {
+    for (int b = ry; b < nparts; b += 8) acc += __ldcg(parts + (size_t)b * 2 * d + col);
+  }
+  red[ry][cx] = acc;
+  __syncthreads();
+  if (ry == 0 && col < 2 * d) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i][cx];
+    if (col < d)
+      dgamma[col] += s;
+    else if (dbeta)
+      dbeta[col - d] += s;
   }
 }
 
@@ -319,11 +331,18 @@ extern "C" long long ppb_norm_bwd_scratch_bytes(int T, int d) {
 namespace ppb {
 static int launch_ln_bwd(const LnBwdParams& p, int grid, cudaStream_t stream) {
   const int nchunks = p.d / 8;
-  const size_t smem = (size_t)2 * p.d * sizeof(float);
-  if (nchunks <= 32 * 4)
-    ln_bwd_kernel<4><<<grid, LN_THREADS, smem, stream>>>(p);
-  else
-    ln_bwd_kernel<8><<<grid, LN_THREADS, smem, stream>>>(p);
+  const size_t smem = (size_t)LN_WARPS * 2 * p.d * sizeof(float);  // <= 128 KB at d = 2048
+  if (nchunks <= 32 * 4) {
+    auto k = ln_bwd_kernel<4>;
+    if (smem > 48 * 1024) PPB_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, LN_THREADS, smem, stream>>>(p);
+  } else {
+    auto k = ln_bwd_kernel<8>;
+    if (smem > 48 * 1024) PPB_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k<<<grid, LN_THREADS, smem, stream>>>(p);
+  }
+  PPB_CUDA_OK(cudaGetLastError());
+  ln_bwd_finalize_kernel<<<(2 * p.d + 31) / 32, 256, 0, stream>>>(p.scratch + 64, grid, p.d, p.dgamma, p.dbeta);
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -417,9 +436,9 @@ extern "C" long long ppb_norm_bwd_noalloc_max_d(void) { return PPB_NORM_NOALLOC_
 // allocating library routine; inputs and outputs are still the caller's.
 //  * The FIRST call on each device resolves the address of the built-in scratch array (cudaGetSymbolAddress);
 //    make that first call outside of any stream capture.
-//  * All calls on a device share the one array.  It still holds whatever the previous call left behind, so the
-//    arrival counter in its header is cleared on `stream` before every launch; the partial-sum area is fully
-//    rewritten by each launch before it is read.
+//  * All calls on a device share the one array.  It still holds whatever the previous call left behind, so its
+//    256-byte header is cleared on `stream` before every launch; the partial-sum area is fully rewritten by each
+//    launch before it is read.
 //  * Because the array is shared, two calls whose kernels can overlap on the GPU (different streams, no ordering
 //    between them) race with each other.  Order them, or use ppb_norm_bwd with separate buffers.
 extern "C" int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void* dy2, const void* z, const float* mean,
@@ -436,7 +455,7 @@ extern "C" int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void
   if (rc) return rc;
   int grid = ln_grid(T);
   if (grid > PPB_NORM_NOALLOC_MAX_CTAS) grid = PPB_NORM_NOALLOC_MAX_CTAS;
-  PPB_CUDA_OK(cudaMemsetAsync(scratch, 0, 256, stream));  // the arrival counter must start at zero
+  PPB_CUDA_OK(cudaMemsetAsync(scratch, 0, 256, stream));  // the header must start at zero
   LnBwdParams p;
   fill_ln_bwd_params(p, dy0, dy1, dy2, z, mean, rstd, gamma, dz, da, dgamma, dbeta, scratch, T, d, dropout_p, seed, rms);
   return launch_ln_bwd(p, grid, stream);
