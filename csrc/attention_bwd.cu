@@ -274,19 +274,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tmem_ld_wait();
         float pv[32], dsv[32];
         const int kvb = kv0 + hf * 64 + c * 32;
+        const bool need_mask = !row_ok || (kvb + 32 > p.Skv) || (p.causal && (kvb + 31 > causal_lim));
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const int kv = kvb + i;
-          const bool ok = row_ok && (kv < p.Skv) && (!p.causal || kv <= causal_lim);
-          const float pr = ok ? ex2f(fmaf(__uint_as_float(rs[i]), p.sl2, -lse2)) : 0.f;
-          pv[i] = pr;
+          pv[i] = ex2f(fmaf(__uint_as_float(rs[i]), p.sl2, -lse2));
           dsv[i] = __uint_as_float(rd[i]);
+        }
+        if (need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int kv = kvb + i;
+            const bool ok = row_ok && (kv < p.Skv) && (!p.causal || kv <= causal_lim);
+            pv[i] = ok ? pv[i] : 0.f;
+          }
         }
         if (p.drop_thresh) {
           const DropoutStream dstr(seed_eff, (drop_row + (unsigned long long)kvb) >> 1);
+          const bool nw = dstr.nowrap(16);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = dstr.bits(i >> 1);
+            const uint32_t hsh = nw ? dstr.bits_nowrap(i >> 1) : dstr.bits(i >> 1);
             const float k0 = ((hsh & 0xFFFFu) >= p.drop_thresh) ? p.drop_scale : 0.f;
             const float k1 = ((hsh >> 16) >= p.drop_thresh) ? p.drop_scale : 0.f;
             dsv[i] = pv[i] * (dsv[i] * k0 - dlt) * p.scale;

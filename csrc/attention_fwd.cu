@@ -221,17 +221,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t r[32];
         tmem_ld_x32(s_tmem(t) + lane_off + c * 32, r);
         tmem_ld_wait();
-        if (!need_mask) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
-        } else {
+        if (need_mask) {  // rare (sequence tail / causal diagonal): overwrite masked scores with -inf
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int kv = kv0 + c * 32 + i;
-            const bool ok = (kv < p.Skv) && (!p.causal || kv <= causal_lim);
-            if (ok) mx = fmaxf(mx, __uint_as_float(r[i]));
+            if (!((kv < p.Skv) && (!p.causal || kv <= causal_lim))) r[i] = 0xff800000u;
           }
         }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(r[i]));
       }
       const float m_new = fmaxf(m_run, mx * p.sl2);
       const float alpha = (m_new == -INFINITY) ? 1.f : fast_exp2(m_run - m_new);
@@ -265,26 +263,36 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t r[32];
         tmem_ld_x32(s_tmem(t) + lane_off + c * 32, r);
         tmem_ld_wait();
+        if (need_mask) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const int kv = kv0 + c * 32 + i;
+            if (!((kv < p.Skv) && (!p.causal || kv <= causal_lim))) r[i] = 0xff800000u;  // exp2(-inf) == 0
+          }
+        }
         float pr[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          float e = fast_exp2(fmaf(__uint_as_float(r[i]), p.sl2, -m_use));
-          if (need_mask) {
-            const int kv = kv0 + c * 32 + i;
-            const bool ok = (kv < p.Skv) && (!p.causal || kv <= causal_lim);
-            e = ok ? e : 0.f;
-          }
-          lsum += e;
-          pr[i] = e;
+          pr[i] = fast_exp2(fmaf(__uint_as_float(r[i]), p.sl2, -m_use));
+          lsum += pr[i];
         }
         if (p.drop_thresh) {
           // kept probabilities are NOT rescaled here: the constant 1/(1-p) is folded into the final 1/l
           const DropoutStream ds(seed_eff, (drop_row + (unsigned long long)(kv0 + c * 32)) >> 1);
+          if (ds.nowrap(16)) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = ds.bits(i >> 1);
-            pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
-            pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
+            for (int i = 0; i < 32; i += 2) {
+              const uint32_t hsh = ds.bits_nowrap(i >> 1);
+              pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
+              pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const uint32_t hsh = ds.bits(i >> 1);
+              pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
+              pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
+            }
           }
         }
         const uint32_t atom = p_row + (c >> 1) * Cfg::CHUNK_BYTES;

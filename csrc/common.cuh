@@ -292,6 +292,9 @@ struct DropoutStream {
     const uint32_t lo = lo0 + i;
     return mix32((lo ^ k0) + (lo < lo0 ? inner_next : inner));
   }
+  // true when indices [0, n) stay inside one value of the high word, so bits_nowrap() may be used
+  __device__ __forceinline__ bool nowrap(uint32_t n) const { return lo0 + (n - 1u) >= lo0; }
+  __device__ __forceinline__ uint32_t bits_nowrap(uint32_t i) const { return mix32(((lo0 + i) ^ k0) + inner); }
 };
 
 __host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
