@@ -47,7 +47,7 @@ def parse():
     ap.add_argument("--microbatches", type=int, default=32)
     ap.add_argument("--virtual-stages", type=int, default=1)
     ap.add_argument("--dp", type=int, default=1)
-    ap.add_argument("--partition", default="reference", choices=["reference", "balanced"])
+    ap.add_argument("--partition", default="balanced", choices=["reference", "balanced"])
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
@@ -82,7 +82,7 @@ def sum_over_ranks(val: float, device) -> float:
 
 def barrier():
     if dist.is_initialized() and dist.get_world_size() > 1:
-        dist.barrier()
+        dist.barrier(device_ids=[torch.cuda.current_device()])
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -100,11 +100,14 @@ def run_ours(a, rank, local_rank, world):
     torch.cuda.set_device(dev)
     _lib.load(required=True)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # no device_id: lazy communicator creation keeps P2P on per-peer communicators/streams (eager init would
+        # serialise every send/recv with every other op of the group)
+        dist.init_process_group("nccl")
         mesh = init_mesh(dp_size=a.dp, pp_size=world // a.dp)
         pp_group, dp_group, pp_idx, dp_idx, P = mesh.pp_group, mesh.dp_group, mesh.pp_idx, mesh.dp_idx, mesh.pp_size
+        pp_group_bwd = mesh.pp_group_bwd
     else:
-        pp_group = dp_group = None
+        pp_group = dp_group = pp_group_bwd = None
         pp_idx = dp_idx = 0
         P = 1
     over = {"dtype": torch.bfloat16}
@@ -125,7 +128,8 @@ def run_ours(a, rank, local_rank, world):
         st.base_seed = 1234
         stages.append(st)
     opt = {"lr": 1e-4, "betas": (0.9, 0.95), "weight_decay": 0.1}
-    sched = make_schedule(a.schedule, stages, a.microbatches, None, pp_group=pp_group, dp_group=dp_group, optimizer=opt)
+    sched = make_schedule(a.schedule, stages, a.microbatches, None, pp_group=pp_group, pp_group_bwd=pp_group_bwd,
+                          dp_group=dp_group, optimizer=opt)
 
     B, S = a.global_batch // a.dp, a.seq_len
     first, last = 0 in sched.local, (num_stages - 1) in sched.local

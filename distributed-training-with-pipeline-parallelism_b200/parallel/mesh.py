@@ -22,6 +22,7 @@ class Mesh:
     pp_idx: int
     tp_idx: int
     pp_group: Optional[object] = None
+    pp_group_bwd: Optional[object] = None   # second communicator over the same ranks (gradient direction)
     dp_group: Optional[object] = None
     tp_group: Optional[object] = None
 
@@ -76,6 +77,11 @@ def init_mesh(dp_size: int = 1, pp_size: Optional[int] = None, tp_size: int = 1)
             g = dist.new_group(ranks)
             if rank in ranks:
                 mesh.pp_group = g
+    if pp_size > 1:
+        for ranks in pp_groups:
+            g = dist.new_group(ranks)
+            if rank in ranks:
+                mesh.pp_group_bwd = g
     if dp_size > 1:
         for ranks in dp_groups:
             g = dist.new_group(ranks)

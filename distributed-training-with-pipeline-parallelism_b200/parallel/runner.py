@@ -32,7 +32,8 @@ class PipelineSchedule:
     schedule_name = "1F1B"
 
     def __init__(self, stages: Union[PipelineStage, Sequence[PipelineStage]], n_microbatches: int, loss_fn=None, *,
-                 schedule: Optional[str] = None, pp_group=None, dp_group=None, optimizer: Optional[dict] = None,
+                 schedule: Optional[str] = None, pp_group=None, pp_group_bwd=None, dp_group=None,
+                 optimizer: Optional[dict] = None,
                  scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None):
         self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
         if not self.stages:
@@ -44,6 +45,9 @@ class PipelineSchedule:
         # softmax-cross-entropy kernel (mean token CE, identical to helper:197-201)
         self.fused_loss = (loss_fn is None) if fused_loss is None else fused_loss
         self.pp_group = pp_group
+        # gradients travel on their own communicator so that a receive posted early in one direction can never
+        # sit in front of a send of the other direction on the same NCCL stream
+        self.pp_group_bwd = pp_group_bwd if pp_group_bwd is not None else pp_group
         self.dp_group = dp_group
         self.optimizer = optimizer
         self.scale_grads = scale_grads
@@ -172,25 +176,28 @@ class PipelineSchedule:
                     src_stage = a.stage - 1 if kind == "F" else a.stage + 1
                     buf = self._ring_buf(a.stage, kind, a.mb, sizes[a.mb], S)
                     src = self._global_rank(self._rank_of_stage(src_stage))
+                    grp = self.pp_group if kind == "F" else self.pp_group_bwd
                     if cuda:
                         anchor = self._anchors[kind]
                         with torch.cuda.stream(anchor):
-                            w = dist.irecv(buf, src=src, group=self.pp_group)
+                            w = dist.irecv(buf, src=src, group=grp)
                             w.wait()  # stream-level: the anchor stream waits, the host does not
                             ev = anchor.record_event()
                         recv_state[(a.stage, kind, a.mb)] = (buf, ev)
                     else:
-                        recv_state[(a.stage, kind, a.mb)] = (buf, dist.irecv(buf, src=src, group=self.pp_group))
+                        recv_state[(a.stage, kind, a.mb)] = (buf, dist.irecv(buf, src=src, group=grp))
                 elif typ == T.SEND_F or typ == T.SEND_B:
                     if typ == T.SEND_F:
                         t = fwd_out.pop((a.stage, a.mb))
                         dst_stage = a.stage + 1
+                        grp = self.pp_group
                     else:
                         t = bwd_out.pop((a.stage, a.mb))
                         dst_stage = a.stage - 1
+                        grp = self.pp_group_bwd
                     t = t.view(sizes[a.mb], S, -1)
                     dst = self._global_rank(self._rank_of_stage(dst_stage))
-                    send_works.append(dist.isend(t, dst=dst, group=self.pp_group))
+                    send_works.append(dist.isend(t, dst=dst, group=grp))
                     keep_alive.append(t)
                 elif typ == T.F:
                     st = self.local[a.stage]
