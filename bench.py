@@ -191,8 +191,13 @@ def run_ours(a, rank, local_rank, world):
             write_chrome_trace(evs, a.trace)
     peak_mem = max_over_ranks(torch.cuda.max_memory_allocated(dev) / 2**30, dev)
     loss_t = torch.tensor([loss_val if loss_val is not None else -1.0], dtype=torch.float64, device=dev)
+    summ = {k: round(v, 3) for k, v in sched.summary().items()}
+    summ["layers"] = [len(st.submod.layers) for st in stages]
+    per_rank = [summ]
     if world > 1:
         dist.all_reduce(loss_t, op=dist.ReduceOp.MAX)
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, summ)
     if rank == 0:
         tokens = a.global_batch * S
         ms_step = ms_total / a.steps
@@ -209,6 +214,7 @@ def run_ours(a, rank, local_rank, world):
             "bubble_fraction_measured_max": bubble, "bubble_fraction_theory": sched.theory_bubble,
             "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
             "model_tflops_per_gpu": margs.flops_per_token(S) * tokens / (ms_step / 1e3) / 1e12 / world,
+            "per_rank": per_rank,
         })
     if world > 1:
         dist.barrier()

@@ -129,6 +129,23 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
     y[i] = __float2bfloat16(x[i]);
 }
 
+// dst_r[i] += src[i] * scale for every replica r (own + peers over NVLink): the all-reduce of the small, non-GEMM
+// gradients (biases, norm gains, embedding rows) in the same push style as the fused wgrad kernel.
+struct PushPtrs {
+  float* p[8];
+};
+__global__ void __launch_bounds__(256) push_add_kernel(const float* __restrict__ src, PushPtrs dst, int n_dst,
+                                                       long long n4, float scale) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(src)[i];
+    v.x *= scale;
+    v.y *= scale;
+    v.z *= scale;
+    v.w *= scale;
+    for (int r = 0; r < n_dst; ++r) atomicAdd(reinterpret_cast<float4*>(dst.p[r]) + i, v);
+  }
+}
+
 static int ew_grid(long long work_items) {
   long long b = (work_items + 255) / 256;
   const long long cap = (long long)sm_count() * 8;
@@ -193,6 +210,20 @@ extern "C" int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* 
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (n <= 0) return 0;
   cast_f32_bf16_kernel<<<ew_grid(n), 256, 0, stream>>>(x, (bf16*)y, n);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+
+extern "C" int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long long n, float scale,
+                                void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(n_dst >= 1 && n_dst <= 8, "ppb_push_add_f32: 1..8 destinations supported");
+  PPB_REQUIRE(n >= 0 && (n % 4) == 0, "ppb_push_add_f32: element count must be a multiple of 4");
+  if (n == 0) return 0;
+  PushPtrs d;
+  for (int r = 0; r < 8; ++r) d.p[r] = reinterpret_cast<float*>(dst_ptrs[r < n_dst ? r : 0]);
+  push_add_kernel<<<ew_grid(n / 4), 256, 0, stream>>>(src, d, n_dst, n / 4, scale);
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }

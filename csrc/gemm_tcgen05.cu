@@ -37,6 +37,14 @@ struct GemmParams {
   const unsigned long long* seed_off;
   unsigned int drop_thresh;
   float drop_scale;
+  // OUT == 3 (fused all-reduce push): previous local accumulator, added once (by split 0) before the push
+  const float* prev;
+  long long ld_prev;
+  int n_dst;
+};
+
+struct DstMaps {
+  CUtensorMap m[8];  // fp32 accumulators of every data-parallel replica (own + peers), peer-mapped over NVLink
 };
 
 template <int BN>
@@ -52,9 +60,8 @@ struct GemmCfg {
 };
 
 template <int BN, bool A_MN, bool B_MN, int OUT>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                          const GemmParams& p, const CUtensorMap* dst_maps) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -176,12 +183,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     __syncwarp();
   } else {
     // ======================= epilogue warps 0..3 =======================
-    constexpr int CHUNK = (OUT == 0) ? 64 : 32;  // columns per staged 128-byte row
+    constexpr int CHUNK = (OUT == 0) ? 64 : 32;  // columns per staged 128-byte row (bf16: 64, fp32: 32)
     const uint32_t my_epi = epi_base + warp * 2 * EPI_BUF_BYTES;
     int it = 0;
     int buf = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int mn = t % (p.tiles_m * p.tiles_n);
+      const int sp = t / (p.tiles_m * p.tiles_n);
       const int m0 = (mn % p.tiles_m) * BM;
       const int n0 = (mn / p.tiles_m) * BN;
       const int acc = it & 1;
@@ -201,6 +209,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
         for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
         const int nc = n0 + c * CHUNK;
+        if constexpr (OUT == 3) {
+          // the K-split that owns index 0 folds in what earlier micro-batches accumulated locally
+          if (sp == 0 && row < p.M) {
+            const float* pp = p.prev + (long long)row * p.ld_prev + nc;
+#pragma unroll
+            for (int j = 0; j < CHUNK; j += 4) {
+              if (nc + j + 4 <= p.N) {
+                const float4 q4 = *reinterpret_cast<const float4*>(pp + j);
+                v[j] += q4.x * p.alpha;
+                v[j + 1] += q4.y * p.alpha;
+                v[j + 2] += q4.z * p.alpha;
+                v[j + 3] += q4.w * p.alpha;
+              } else {
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                  if (nc + j + q < p.N) v[j + q] += pp[j + q] * p.alpha;
+              }
+            }
+          }
+        }
         if (p.epi == PPB_EPI_BIAS || p.epi == PPB_EPI_BIAS_RELU || p.epi == PPB_EPI_BIAS_GELU ||
             p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
 #pragma unroll
@@ -285,10 +313,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          if (OUT == 2)
+          if constexpr (OUT == 3) {
+            // one reduce-add per replica: own accumulator through L2, the peers' through NVLink
+            for (int r = 0; r < p.n_dst; ++r)
+              tma_reduce_add_2d(dst_maps + r, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+          } else if constexpr (OUT == 2) {
             tma_reduce_add_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
-          else
+          } else {
             tma_store_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+          }
           tma_commit_group();
         }
         buf ^= 1;
@@ -304,6 +337,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   tc_fence_before();
   __syncthreads();
   if (warp == 5) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+template <int BN, bool A_MN, bool B_MN, int OUT>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  gemm_body<BN, A_MN, B_MN, OUT>(tmA, tmB, tmC, p, nullptr);
+}
+
+// K10: the LAST micro-batch's weight-gradient GEMM of a stage, fused with the data-parallel
+// all-reduce and the 1/(m*dp) scaling.  Each CTA adds the locally accumulated gradient of the earlier
+// micro-batches to its tile (split 0 only) and reduce-adds the result straight into the gradient buffers of ALL
+// replicas -- its own through L2, the peers' through NVLink (peer-mapped symmetric memory, TMA
+// cp.reduce.async.bulk) -- so the collective's traffic overlaps the remaining tiles' math and no separate
+// all-reduce kernel ever runs.  No flags or in-kernel waits are needed: addition commutes, every replica pushes
+// into every replica, and one cross-replica barrier before the optimizer makes the sums complete.
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_allreduce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                              const __grid_constant__ DstMaps dst, const GemmParams p) {
+  gemm_body<BN, true, true, 3>(tmA, tmB, dst.m[0], p, dst.m);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -428,6 +482,9 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.ld_aux = ld_aux;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
+  p.prev = nullptr;
+  p.ld_prev = 0;
+  p.n_dst = 0;
   p.drop_thresh = dropout_thresh16(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
@@ -450,4 +507,59 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
 #undef PPB_DISPATCH_OUT
   set_error("ppb_gemm_bf16: bad out_mode %d", out_mode);
   return -2;
+}
+
+
+extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float* prev, void* const* dst_ptrs, int n_dst,
+                                       int M, int N, int K, long long lda, long long ldb, long long ldc, float alpha,
+                                       int force_bn, int force_splits, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(M > 0 && N > 0 && K > 0, "ppb_gemm_allreduce_bf16: empty problem");
+  PPB_REQUIRE(n_dst >= 1 && n_dst <= 8, "ppb_gemm_allreduce_bf16: 1..8 destination replicas supported (got %d)", n_dst);
+  PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldc % 4) == 0, "ppb_gemm_allreduce_bf16: misaligned leading dimension");
+  PPB_REQUIRE(prev != nullptr && (reinterpret_cast<uintptr_t>(prev) % 16) == 0, "ppb_gemm_allreduce_bf16: prev must be 16-byte aligned");
+  PPB_REQUIRE(force_bn == 0 || force_bn == 64 || force_bn == 128 || force_bn == 256, "ppb_gemm_allreduce_bf16: bad force_bn");
+  int bn = 128, splits = 1;
+  choose_config(M, N, K, PPB_OUT_F32_ACCUM, force_bn, force_splits, &bn, &splits);
+  if (!force_splits && splits > 4) splits = 4;  // every split crosses NVLink (n_dst - 1) times
+  CUtensorMap tmA, tmB;
+  DstMaps dst;
+  bool ok = make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, BK) &&
+            make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK);
+  for (int r = 0; ok && r < n_dst; ++r)
+    ok = make_tmap_2d(&dst.m[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, dst_ptrs[r], (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 4, 32, 32);
+  for (int r = n_dst; ok && r < 8; ++r) dst.m[r] = dst.m[0];
+  if (!ok) return -3;
+  GemmParams p;
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + bn - 1) / bn;
+  p.splits = splits;
+  p.kb_per_split = (((K + BK - 1) / BK) + splits - 1) / splits;
+  p.epi = PPB_EPI_NONE;
+  p.alpha = alpha;
+  p.bias = nullptr;
+  p.aux = nullptr;
+  p.ld_aux = 0;
+  p.seed = 0;
+  p.seed_off = nullptr;
+  p.drop_thresh = 0;
+  p.drop_scale = 1.f;
+  p.prev = prev;
+  p.ld_prev = ldc;
+  p.n_dst = n_dst;
+  const long long total = (long long)p.tiles_m * p.tiles_n * splits;
+  const int grid = (int)(total < sm_count() ? total : sm_count());
+#define PPB_LAUNCH_AR(BN_)                                                                                       \
+  {                                                                                                              \
+    auto kfn = gemm_tcgen05_allreduce_kernel<BN_>;                                                               \
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN_>::SMEM_BYTES)); \
+    kfn<<<grid, GEMM_THREADS, GemmCfg<BN_>::SMEM_BYTES, stream>>>(tmA, tmB, dst, p);                              \
+  }
+  if (bn == 256) PPB_LAUNCH_AR(256) else if (bn == 128) PPB_LAUNCH_AR(128) else PPB_LAUNCH_AR(64)
+#undef PPB_LAUNCH_AR
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
 }

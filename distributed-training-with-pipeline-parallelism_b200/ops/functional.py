@@ -116,8 +116,11 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, mask_pos_aux: Optional[torch
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
-                 db_accum: Optional[torch.Tensor] = None) -> None:
-    """dw_accum[out, in] += dy^T @ x (fp32, split-K + TMA reduce-add);  db_accum[out] += colsum(dy)."""
+                 db_accum: Optional[torch.Tensor] = None, ar=None) -> None:
+    """dw_accum[out, in] += dy^T @ x (fp32, split-K + TMA reduce-add);  db_accum[out] += colsum(dy).
+
+    ``ar``: an armed ``ops.collective.FusedGradAllReduce`` -- the GEMM then pushes (previous accumulation + this
+    micro-batch) into every data-parallel replica's reduced-gradient buffer instead (K10)."""
     _check_2d(dy, "dy")
     _check_2d(x, "x")
     if not _is_cuda(dy):
@@ -125,7 +128,10 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
         return
     T, Nout = dy.shape
     Nin = x.shape[1]
-    gemm(dy, x, dw_accum, Nout, Nin, T, True, True, OUT_F32_ACCUM)
+    if ar is not None and ar.armed:
+        ar.wgrad(dy, x, dw_accum)
+    else:
+        gemm(dy, x, dw_accum, Nout, Nin, T, True, True, OUT_F32_ACCUM)
     if db_accum is not None:
         lib = _lib_required()
         _lib.check(lib.ppb_colsum_accum(dy.data_ptr(), dy.stride(0), db_accum.data_ptr(), T, Nout, _stream()),

@@ -81,6 +81,12 @@ class PipelineSchedule:
         self.steps_done = 0
         for st in self.stages:
             st.materialize()
+            if st.dp_group is None:
+                st.dp_group = dp_group
+        self.fused_dp = False
+        if self.dp_size > 1 and optimizer is not None and self.cuda:
+            self.fused_dp = all([st.enable_fused_dp(self.m) for st in self.stages if st.n_total > 0])
+        self._b_seen: Dict[int, int] = {}
 
     # ---- helpers ------------------------------------------------------------------------------------------------
     def _global_rank(self, pp_rank: int) -> int:
@@ -154,6 +160,7 @@ class PipelineSchedule:
         send_works: List[Any] = []
         keep_alive: List[torch.Tensor] = []
         allreduce_works: Dict[int, Any] = {}
+        b_count: Dict[int, int] = {}
         timeline: List[Tuple[Action, Any, Any]] = []
         rec = self.record_timeline
 
@@ -167,6 +174,7 @@ class PipelineSchedule:
             return time.perf_counter()
 
         t_begin = tick()
+        host_t0 = time.perf_counter()
         idx = -1
         try:
             for idx, a in enumerate(self.order):
@@ -220,7 +228,8 @@ class PipelineSchedule:
                     if a.stage != last_stage:
                         dout = self._take_input(recv_state, local_in, a.stage, "B", a.mb, compute)
                     t0 = tick()
-                    din = st.backward_one_chunk(a.mb, dout)
+                    b_count[a.stage] = b_count.get(a.stage, 0) + 1
+                    din = st.backward_one_chunk(a.mb, dout, last=(b_count[a.stage] == self.m))
                     timeline.append((a, t0, tick()))
                     if a.stage != 0:
                         if self._rank_of_stage(a.stage - 1) == self.pp_rank:
@@ -257,6 +266,7 @@ class PipelineSchedule:
             if w is not None:
                 w.wait()
         t_end = tick()
+        self._host_ms = (time.perf_counter() - host_t0) * 1e3
         self.timeline = timeline
         self._step_span = (t_begin, t_end)
         self._keep_alive = keep_alive
@@ -314,6 +324,22 @@ class PipelineSchedule:
             busy = sum((e - s) * 1e3 for a, s, e in self.timeline if a.type.is_compute or a.type == T.OPTIM)
         return {"step_ms": span, "busy_ms": busy, "bubble_fraction": max(0.0, 1.0 - busy / span) if span > 0 else 0.0,
                 "bubble_theory": self.theory_bubble}
+
+    def summary(self) -> Dict[str, float]:
+        """Per-action-type mean durations of the last step (ms) + host time spent issuing the step."""
+        if not self.timeline or self._step_span is None or self._step_span[0] is None:
+            return {}
+        if self.cuda:
+            torch.cuda.synchronize(self.device)
+        acc: Dict[str, List[float]] = {}
+        for a, s, e in self.timeline:
+            d = s.elapsed_time(e) if self.cuda else (e - s) * 1e3
+            acc.setdefault(a.type.value, []).append(d)
+        out = {f"{k}_ms_mean": sum(v) / len(v) for k, v in acc.items()}
+        out.update({f"{k}_ms_max": max(v) for k, v in acc.items()})
+        out["host_issue_ms"] = getattr(self, "_host_ms", float("nan"))
+        out.update(self.measured())
+        return out
 
     def trace_events(self) -> List[dict]:
         """Chrome-trace events (ph='X') of the last step's MEASURED timeline, names = IR strings."""

@@ -47,6 +47,7 @@ class PipelineStage:
         self.base_seed = 0
         self.step_count = 0
         self.training = True
+        self.fused_ar = None
         self.has_params = any(True for _ in submodule.parameters())
 
     # ---- memory layout --------------------------------------------------------------------------------------
@@ -102,6 +103,20 @@ class PipelineStage:
             self.seed_offset = _SEED_OFFSETS[key]
         self._materialized = True
         return self
+
+    def enable_fused_dp(self, n_microbatches: int) -> bool:
+        """Switch the data-parallel gradient reduction of this stage to the fused in-kernel path (K10).  Returns
+        False (and keeps the NCCL all-reduce) when the stage is not on CUDA, has no replicas, or owns no parameters.
+        Collective over the dp group: every replica must call it."""
+        import os
+        import torch.distributed as dist
+        if (self.device.type != "cuda" or self.dp_group is None or dist.get_world_size(self.dp_group) == 1
+                or self.n_total == 0 or os.environ.get("PPB_FUSED_DP", "1") == "0"):
+            return False
+        from ..ops.collective import FusedGradAllReduce
+        dp = dist.get_world_size(self.dp_group)
+        self.fused_ar = FusedGradAllReduce(self.grad, self.n_total, self.dp_group, 1.0 / (n_microbatches * dp))
+        return True
 
     def grad_views(self) -> Dict[str, torch.Tensor]:
         return {n: self.grad[o:o + int(torch.Size(s).numel())].view(s) for n, o, s in self.param_names}
@@ -188,7 +203,7 @@ class PipelineStage:
             self.outputs[mb] = out.view(b, S, -1)
         return out
 
-    def backward_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+    def backward_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None, last: bool = False) -> Optional[torch.Tensor]:
         """Backward for micro-batch ``mb``; ``dout`` is the gradient received from the next stage (None on the last
         stage: the fused loss already left dlogits in the stash).  Returns the input gradient [b*S, d] or None."""
         st = self.stash.pop(mb)
@@ -199,8 +214,15 @@ class PipelineStage:
             douts = [st["dlogits"]]
         else:
             douts = [dout]
-        with torch.no_grad():
-            return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+        fused = self.fused_ar if (last and self.fused_ar is not None) else None
+        if fused is not None:
+            fused.begin_last_backward()   # this backward's weight-gradient GEMMs carry the DP all-reduce
+            self.sink.fused_ar = fused
+        try:
+            with torch.no_grad():
+                return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+        finally:
+            self.sink.fused_ar = None
 
     # ---- gradient reduction + optimizer ---------------------------------------------------------------------------
     def all_reduce_grads(self, async_op: bool = False):
@@ -208,6 +230,9 @@ class PipelineStage:
         the fused in-kernel path lives in ops.collective)."""
         import torch.distributed as dist
         if self.dp_group is None or dist.get_world_size(self.dp_group) == 1 or self.n_total == 0:
+            return None
+        if self.fused_ar is not None:
+            self.fused_ar.finish()   # pushes the non-GEMM gradients + device-side barrier; nothing left to wait for
             return None
         return dist.all_reduce(self.grad, group=self.dp_group, async_op=async_op)
 
@@ -220,12 +245,18 @@ class PipelineStage:
         mixed = self.master is not self.param_arena
         nd = self.n_decay
         coef = clip_coef
+        grad = self.grad
+        if self.fused_ar is not None:   # already reduced over replicas and scaled by 1/(m*dp) in the GEMM epilogues
+            grad, grad_scale = self.fused_ar.final, 1.0
         for lo, hi, wd in ((0, nd, weight_decay), (nd, self.n_total, 0.0)):
             if hi <= lo:
                 continue
             F.adamw_step(self.param_arena[lo:hi] if mixed else None, self.master[lo:hi], self.exp_avg[lo:hi],
-                         self.exp_avg_sq[lo:hi], self.grad[lo:hi], lr, betas[0], betas[1], eps, wd, self.step_count,
+                         self.exp_avg_sq[lo:hi], grad[lo:hi], lr, betas[0], betas[1], eps, wd, self.step_count,
                          grad_scale, coef, zero_grad=True)
+        if self.fused_ar is not None:
+            self.grad.zero_()
+            self.fused_ar.after_optimizer()
 
     def zero_grad(self) -> None:
         if self._materialized:

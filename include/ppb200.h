@@ -46,6 +46,18 @@ int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, lo
                   const void* aux, long long ld_aux, unsigned long long seed, float dropout_p, int force_bn,
                   int force_splits, void* stream);
 
+/* ---- K10: last-micro-batch wgrad GEMM fused with the data-parallel gradient all-reduce ---------------------------
+ * dst_r[M,N] += alpha * (prev[M,N] + A^T B) for every replica r in dst_ptrs (own buffer and peer-mapped symmetric
+ * memory of the other replicas; host array of n_dst device pointers, all with leading dimension ldc).  A is stored
+ * [K, lda], B is stored [K, ldb] (the wgrad form).  Every replica calls it on its own data; after a cross-replica
+ * barrier all dst buffers hold alpha * sum_r(prev_r + A_r^T B_r).  ppb_push_add_f32 does the same for the small
+ * non-GEMM gradients.  The reference has no data parallelism at all; the baseline this
+ * replaces is cuBLAS wgrad + ncclAllReduce. */
+int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float* prev, void* const* dst_ptrs, int n_dst, int M,
+                            int N, int K, long long lda, long long ldb, long long ldc, float alpha, int force_bn,
+                            int force_splits, void* stream);
+int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long long n, float scale, void* stream);
+
 /* ---- K5: fused residual-add + dropout + LayerNorm / RMSNorm ------------------------------------------------
  * fwd: z = resid + dropout(a); y = norm(z)*gamma(+beta).  Either of resid / a may be NULL; z, mean may be NULL.
  * bwd: dy = dy0(+dy1+dy2); dz = norm'(dy); da = dropout'(dz) (da may be NULL); dgamma/dbeta are fp32 accum.

@@ -231,3 +231,24 @@ def test_attention_bwd(B, H, Sq, Skv, dh, causal, p):
     # second call re-uses (and re-zeroes) the scratch accumulator
     dq2, _, _ = F.attention_bwd(q, k, v, o, do, lse, B, H, causal, None, p, seed=42)
     assert rel_err(dq2, dqr) < 2e-2
+
+
+@pytest.mark.parametrize("M,N,K,n_dst,splits", [(1024, 1024, 4096, 1, 0), (768, 2304, 1024, 2, 0), (2048, 1024, 4096, 3, 2), (200, 136, 520, 2, 0)])
+def test_gemm_allreduce_push_single_gpu(M, N, K, n_dst, splits):
+    """K10 numerics on one GPU: the 'replicas' are n_dst separate buffers of the same device."""
+    from ppb200.ops.collective import gemm_allreduce, push_add
+    torch.manual_seed(12)
+    dy = torch.randn(K, M, device=DEV, dtype=torch.bfloat16)
+    x = torch.randn(K, N, device=DEV, dtype=torch.bfloat16)
+    prev = torch.randn(M, N, device=DEV)
+    dsts = [torch.full((M, N), float(i + 1), device=DEV) for i in range(n_dst)]
+    alpha = 0.125
+    gemm_allreduce(dy, x, prev, [d.data_ptr() for d in dsts], alpha, force_splits=splits)
+    want = alpha * (prev + dy.float().t() @ x.float())
+    for i, d in enumerate(dsts):
+        assert rel_err(d - (i + 1), want) < 5e-3
+    src = torch.randn(4096, device=DEV)
+    outs = [torch.ones(4096, device=DEV) for _ in range(n_dst)]
+    push_add(src, [o.data_ptr() for o in outs], 0.5)
+    for o in outs:
+        assert rel_err(o, 1 + 0.5 * src) < 1e-6

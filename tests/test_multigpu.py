@@ -1,0 +1,39 @@
+"""Multi-GPU tests (need >= 2 GPUs; skipped otherwise): NCCL pipeline parity and the fused DP all-reduce (K10)
+against the NCCL all-reduce path."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _torchrun(n, script_args, env=None, timeout=600):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
+           "--master-port", str(29600 + os.getpid() % 300)] + script_args
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, cwd=ROOT, env=e)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r.stdout
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_fused_dp_allreduce_matches_nccl():
+    out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_dp_check.py")])
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert res["fused_enabled"] is True
+    assert res["max_rel_param_diff"] < 2e-3, res
+    assert res["loss_diff"] < 1e-3, res
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_pipeline_pp2_loss_matches_single_gpu():
+    out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_pp_check.py")])
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert abs(res["loss_pp2"] - res["loss_pp1"]) < 2e-2 * abs(res["loss_pp1"]), res
+    assert res["loss_after"] < res["loss_pp2"], res
