@@ -37,9 +37,8 @@ struct GemmParams {
   const unsigned long long* seed_off;
   unsigned int drop_thresh;
   float drop_scale;
-  // OUT == 3 (fused all-reduce push): previous local accumulator, added once (by split 0) before the push
-  const float* prev;
-  long long ld_prev;
+  // OUT == 3 (fused all-reduce): per-(tile, epilogue-warp) arrival counters + number of replicas to push to
+  unsigned int* tile_counters;
   int n_dst;
 };
 
@@ -91,6 +90,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), 4);
     }
+    for (int w = 0; w < 8; ++w) mbar_init(bar_base + 8u * (2 * STAGES + 5 + w), 1);  // fused all-reduce slab loads
     fence_mbar_init();
   }
   if (warp == 5) tmem_alloc(tmem_ptr_smem, Cfg::TMEM_COLS);
@@ -187,9 +187,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     const uint32_t my_epi = epi_base + warp * 2 * EPI_BUF_BYTES;
     int it = 0;
     int buf = 0;
+    uint32_t push_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int mn = t % (p.tiles_m * p.tiles_n);
-      const int sp = t / (p.tiles_m * p.tiles_n);
       const int m0 = (mn % p.tiles_m) * BM;
       const int n0 = (mn / p.tiles_m) * BN;
       const int acc = it & 1;
@@ -209,26 +209,6 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
         for (int j = 0; j < CHUNK; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
         const int nc = n0 + c * CHUNK;
-        if constexpr (OUT == 3) {
-          // the K-split that owns index 0 folds in what earlier micro-batches accumulated locally
-          if (sp == 0 && row < p.M) {
-            const float* pp = p.prev + (long long)row * p.ld_prev + nc;
-#pragma unroll
-            for (int j = 0; j < CHUNK; j += 4) {
-              if (nc + j + 4 <= p.N) {
-                const float4 q4 = *reinterpret_cast<const float4*>(pp + j);
-                v[j] += q4.x * p.alpha;
-                v[j + 1] += q4.y * p.alpha;
-                v[j + 2] += q4.z * p.alpha;
-                v[j + 3] += q4.w * p.alpha;
-              } else {
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                  if (nc + j + q < p.N) v[j + q] += pp[j + q] * p.alpha;
-              }
-            }
-          }
-        }
         if (p.epi == PPB_EPI_BIAS || p.epi == PPB_EPI_BIAS_RELU || p.epi == PPB_EPI_BIAS_GELU ||
             p.epi == PPB_EPI_BIAS_RELU_DROPOUT) {
 #pragma unroll
@@ -313,11 +293,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
-          if constexpr (OUT == 3) {
-            // one reduce-add per replica: own accumulator through L2, the peers' through NVLink
-            for (int r = 0; r < p.n_dst; ++r)
-              tma_reduce_add_2d(dst_maps + r, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
-          } else if constexpr (OUT == 2) {
+          if constexpr (OUT == 2 || OUT == 3) {
             tma_reduce_add_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
           } else {
             tma_store_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
@@ -330,8 +306,48 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if constexpr (OUT == 3) {
+        // ---- fused all-reduce: the LAST K-split to finish this 32-row slab streams the completed gradient slab
+        //      to every replica (own reduced buffer through L2, the peers' over NVLink) with TMA only ----
+        uint32_t last = 0;
+        if (lane == 0) {
+          tma_wait_group<0>();   // my reduce-adds into the local accumulator are complete
+          __threadfence();
+          const unsigned int old = atomicAdd(p.tile_counters + (size_t)mn * 4 + warp, 1u);
+          last = (old == (unsigned int)p.splits - 1u) ? 1u : 0u;
+          if (last) {
+            p.tile_counters[(size_t)mn * 4 + warp] = 0u;   // self-reset for the next launch
+            __threadfence();
+          }
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (last && lane == 0) {
+          // two-deep pipeline: the TMA load of slab chunk c+1 is in flight while chunk c is pushed
+          const uint32_t lbar0 = bar_base + 8u * (2 * STAGES + 5 + 2 * warp);
+          int nchunk = 0;
+          for (int c = 0; c < BN / 32 && n0 + c * 32 < p.N; ++c) ++nchunk;
+          tma_wait_group_read<0>();
+          mbar_expect_tx(lbar0 + 8u * (buf & 1), 32 * 32 * 4);
+          tma_load_2d(my_epi + buf * EPI_BUF_BYTES, &tmC, lbar0 + 8u * (buf & 1), n0, m0 + warp * 32);
+          for (int c = 0; c < nchunk; ++c) {
+            const int nc = n0 + c * 32;
+            if (c + 1 < nchunk) {
+              tma_wait_group_read<0>();  // the push that last used the other buffer has been read out
+              mbar_expect_tx(lbar0 + 8u * ((buf ^ 1) & 1), 32 * 32 * 4);
+              tma_load_2d(my_epi + (buf ^ 1) * EPI_BUF_BYTES, &tmC, lbar0 + 8u * ((buf ^ 1) & 1), nc + 32, m0 + warp * 32);
+            }
+            mbar_wait(lbar0 + 8u * (buf & 1), (push_phase >> (buf & 1)) & 1u);
+            push_phase ^= (1u << (buf & 1));
+            for (int r = 0; r < p.n_dst; ++r)
+              tma_reduce_add_2d(dst_maps + r, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+            tma_commit_group();
+            buf ^= 1;
+          }
+        }
+        __syncwarp();
+      }
     }
-    if (lane == 0) tma_wait_group<0>();
+    if (lane == 0) tma_wait_group_read<0>();  // smem may be released; global writes complete before grid end
   }
 
   tc_fence_before();
@@ -347,17 +363,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // K10: the LAST micro-batch's weight-gradient GEMM of a stage, fused with the data-parallel
-// all-reduce and the 1/(m*dp) scaling.  Each CTA adds the locally accumulated gradient of the earlier
-// micro-batches to its tile (split 0 only) and reduce-adds the result straight into the gradient buffers of ALL
-// replicas -- its own through L2, the peers' through NVLink (peer-mapped symmetric memory, TMA
-// cp.reduce.async.bulk) -- so the collective's traffic overlaps the remaining tiles' math and no separate
-// all-reduce kernel ever runs.  No flags or in-kernel waits are needed: addition commutes, every replica pushes
-// into every replica, and one cross-replica barrier before the optimizer makes the sums complete.
+// all-reduce.  The GEMM accumulates into the local fp32 gradient like every other micro-batch (split-K, TMA
+// reduce-add).  Every (tile, 32-row slab) has an arrival counter; the K-split that completes a slab last reads the
+// finished slab back with TMA (it is still in L2) and reduce-adds it into the reduced-gradient buffer of EVERY
+// replica -- its own through L2, the peers' through NVLink (peer-mapped symmetric memory,
+// cp.reduce.async.bulk.tensor) -- while the other CTAs keep computing their tiles, so the collective overlaps the
+// math tile by tile and each gradient byte crosses the link exactly once.  No in-kernel waits on other GPUs:
+// addition commutes, every replica pushes into every replica, and one cross-replica barrier before the optimizer
+// makes the sums complete.
 template <int BN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tcgen05_allreduce_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                              const __grid_constant__ DstMaps dst, const GemmParams p) {
-  gemm_body<BN, true, true, 3>(tmA, tmB, dst.m[0], p, dst.m);
+                              const __grid_constant__ CUtensorMap tmC, const __grid_constant__ DstMaps dst,
+                              const GemmParams p) {
+  gemm_body<BN, true, true, 3>(tmA, tmB, tmC, p, dst.m);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -389,38 +408,32 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& tmA, const CUte
   return launch_gemm<BN, true, false, OUT>(tmA, tmB, tmC, p, grid, s);
 }
 
-// Pick (BN, splits) minimising a wave-quantised cost model.  Cycle costs per k-block (64 deep) follow the
-// tcgen05 pacing law of B300_MICROARCH.md: 4 MMAs x BN/2 cycles; plus a fixed per-tile overhead.
+// Pick (BN, splits).  Calibrated on a measured sweep (benchmarks/gemm_sweep.py, profiles/gemm_sweep_r1.json):
+// the widest tile that N can fill always wins (BN = 256 halves the smem operand traffic per FLOP; BN = 64 is smem-
+// bandwidth bound and 2x slower), and for the accumulate mode the split count minimises
+// waves * (k-blocks per split * cycles per k-block + fixed tile overhead).
 static void choose_config(int M, int N, int K, int out_mode, int force_bn, int force_splits, int* bn_out,
                           int* splits_out) {
   const int sms = sm_count();
   const int num_kb = (K + BK - 1) / BK;
-  const int cands[3] = {256, 128, 64};
+  int bn = force_bn ? force_bn : (N > 128 ? 256 : (N > 64 ? 128 : 64));
+  const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+  const int max_sp = (out_mode == PPB_OUT_F32_ACCUM) ? 16 : 1;
   double best = 1e30;
-  int best_bn = 128, best_sp = 1;
-  for (int ci = 0; ci < 3; ++ci) {
-    const int bn = cands[ci];
-    if (force_bn && bn != force_bn) continue;
-    if (!force_bn && bn > 64 && N <= bn / 2) continue;  // do not waste more than half a tile on padding
-    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
-    const int max_sp = (out_mode == PPB_OUT_F32_ACCUM) ? 16 : 1;
-    for (int sp = 1; sp <= max_sp; ++sp) {
-      if (force_splits && sp != force_splits) continue;
-      const int kbs = (num_kb + sp - 1) / sp;
-      if (sp > 1 && kbs < 4) break;
-      if ((long long)(sp - 1) * kbs >= num_kb) continue;  // an empty split
-      const long long work = tiles * sp;
-      const long long waves = (work + sms - 1) / sms;
-      const double t_tile = kbs * (4.0 * bn / 2.0) + 600.0 + bn * 3.0;  // main loop + fill/drain + epilogue tail
-      const double cost = waves * t_tile;
-      if (cost < best) {
-        best = cost;
-        best_bn = bn;
-        best_sp = sp;
-      }
+  int best_sp = 1;
+  for (int sp = 1; sp <= max_sp; ++sp) {
+    if (force_splits && sp != force_splits) continue;
+    const int kbs = (num_kb + sp - 1) / sp;
+    if (sp > 1 && kbs < 4) break;
+    if ((long long)(sp - 1) * kbs >= num_kb) continue;  // an empty split
+    const long long waves = (tiles * sp + sms - 1) / sms;
+    const double cost = waves * (kbs * 2.0 * bn + 3000.0);
+    if (cost < best) {
+      best = cost;
+      best_sp = sp;
     }
   }
-  *bn_out = best_bn;
+  *bn_out = bn;
   *splits_out = best_sp;
 }
 
@@ -482,8 +495,7 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.ld_aux = ld_aux;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
-  p.prev = nullptr;
-  p.ld_prev = 0;
+  p.tile_counters = nullptr;
   p.n_dst = 0;
   p.drop_thresh = dropout_thresh16(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
@@ -510,22 +522,29 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
 }
 
 
-extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float* prev, void* const* dst_ptrs, int n_dst,
-                                       int M, int N, int K, long long lda, long long ldb, long long ldc, float alpha,
-                                       int force_bn, int force_splits, void* stream_) {
+extern "C" long long ppb_gemm_allreduce_scratch_bytes(int M, int N) {
+  return (long long)((M + BM - 1) / BM) * ((N + 63) / 64) * 4 * sizeof(unsigned int) + 256;
+}
+
+extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accum, void* const* dst_ptrs, int n_dst,
+                                       int M, int N, int K, long long lda, long long ldb, long long ldc, void* scratch,
+                                       long long scratch_bytes, int force_bn, int force_splits, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(M > 0 && N > 0 && K > 0, "ppb_gemm_allreduce_bf16: empty problem");
   PPB_REQUIRE(n_dst >= 1 && n_dst <= 8, "ppb_gemm_allreduce_bf16: 1..8 destination replicas supported (got %d)", n_dst);
   PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldc % 4) == 0, "ppb_gemm_allreduce_bf16: misaligned leading dimension");
-  PPB_REQUIRE(prev != nullptr && (reinterpret_cast<uintptr_t>(prev) % 16) == 0, "ppb_gemm_allreduce_bf16: prev must be 16-byte aligned");
+  PPB_REQUIRE(accum != nullptr && (reinterpret_cast<uintptr_t>(accum) % 16) == 0, "ppb_gemm_allreduce_bf16: accum must be 16-byte aligned");
+  PPB_REQUIRE(scratch != nullptr && scratch_bytes >= ppb_gemm_allreduce_scratch_bytes(M, N),
+              "ppb_gemm_allreduce_bf16: scratch too small (%lld bytes, need %lld)", scratch_bytes,
+              ppb_gemm_allreduce_scratch_bytes(M, N));
   PPB_REQUIRE(force_bn == 0 || force_bn == 64 || force_bn == 128 || force_bn == 256, "ppb_gemm_allreduce_bf16: bad force_bn");
   int bn = 128, splits = 1;
   choose_config(M, N, K, PPB_OUT_F32_ACCUM, force_bn, force_splits, &bn, &splits);
-  if (!force_splits && splits > 4) splits = 4;  // every split crosses NVLink (n_dst - 1) times
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmC;
   DstMaps dst;
   bool ok = make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, BK) &&
-            make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK);
+            make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK) &&
+            make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, accum, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 4, 32, 32);
   for (int r = 0; ok && r < n_dst; ++r)
     ok = make_tmap_2d(&dst.m[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, dst_ptrs[r], (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 4, 32, 32);
   for (int r = n_dst; ok && r < 8; ++r) dst.m[r] = dst.m[0];
@@ -539,7 +558,7 @@ extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float
   p.splits = splits;
   p.kb_per_split = (((K + BK - 1) / BK) + splits - 1) / splits;
   p.epi = PPB_EPI_NONE;
-  p.alpha = alpha;
+  p.alpha = 1.f;
   p.bias = nullptr;
   p.aux = nullptr;
   p.ld_aux = 0;
@@ -547,16 +566,17 @@ extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float
   p.seed_off = nullptr;
   p.drop_thresh = 0;
   p.drop_scale = 1.f;
-  p.prev = prev;
-  p.ld_prev = ldc;
+  p.tile_counters = reinterpret_cast<unsigned int*>(scratch);
   p.n_dst = n_dst;
+  // the arrival counters must be zero on entry: the caller zero-fills the scratch once, the kernel resets every
+  // counter it used (no per-call memset launch)
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
   const int grid = (int)(total < sm_count() ? total : sm_count());
 #define PPB_LAUNCH_AR(BN_)                                                                                       \
   {                                                                                                              \
     auto kfn = gemm_tcgen05_allreduce_kernel<BN_>;                                                               \
     PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN_>::SMEM_BYTES)); \
-    kfn<<<grid, GEMM_THREADS, GemmCfg<BN_>::SMEM_BYTES, stream>>>(tmA, tmB, dst, p);                              \
+    kfn<<<grid, GEMM_THREADS, GemmCfg<BN_>::SMEM_BYTES, stream>>>(tmA, tmB, tmC, dst, p);                         \
   }
   if (bn == 256) PPB_LAUNCH_AR(256) else if (bn == 128) PPB_LAUNCH_AR(128) else PPB_LAUNCH_AR(64)
 #undef PPB_LAUNCH_AR

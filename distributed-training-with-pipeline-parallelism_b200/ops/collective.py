@@ -23,25 +23,37 @@ def _bind(lib) -> None:
     if getattr(lib, "_ppb_collective_bound", False):
         return
     P, I, L, F = c_void_p, c_int, c_longlong, c_float
-    lib.ppb_gemm_allreduce_bf16.argtypes = [P, P, P, P, I, I, I, I, L, L, L, F, I, I, P]
+    lib.ppb_gemm_allreduce_bf16.argtypes = [P, P, P, P, I, I, I, I, L, L, L, P, L, I, I, P]
+    lib.ppb_gemm_allreduce_scratch_bytes.argtypes = [I, I]
+    lib.ppb_gemm_allreduce_scratch_bytes.restype = L
     lib.ppb_gemm_allreduce_bf16.restype = I
     lib.ppb_push_add_f32.argtypes = [P, P, I, L, F, P]
     lib.ppb_push_add_f32.restype = I
     lib._ppb_collective_bound = True
 
 
-def gemm_allreduce(dy: torch.Tensor, x: torch.Tensor, prev: torch.Tensor, dst_ptrs: List[int], alpha: float,
+_ar_scratch: dict = {}
+
+
+def gemm_allreduce(dy: torch.Tensor, x: torch.Tensor, accum: torch.Tensor, dst_ptrs: List[int],
                    force_bn: int = 0, force_splits: int = 0) -> None:
-    """dst_r[out, in] += alpha * (prev + dy^T @ x) for every pointer in ``dst_ptrs`` (device pointers, possibly
-    peer-mapped).  dy [T, out], x [T, in] bf16; prev fp32 [out, in] with the same leading dimension as the dsts."""
+    """accum[out, in] += dy^T @ x, and every completed slab of accum is reduce-added into dst_r for every pointer in
+    ``dst_ptrs`` (device pointers, possibly peer-mapped) from inside the same kernel.  dy [T, out], x [T, in] bf16;
+    accum fp32 [out, in]; the dsts share its leading dimension."""
     lib = _lib.load(required=True)
     _bind(lib)
     T, Nout = dy.shape
     Nin = x.shape[1]
+    need = int(lib.ppb_gemm_allreduce_scratch_bytes(Nout, Nin))
+    key = (dy.device.index, torch.cuda.current_stream().cuda_stream)
+    scratch = _ar_scratch.get(key)
+    if scratch is None or scratch.numel() < need:
+        scratch = torch.zeros(max(need, 1 << 16), dtype=torch.uint8, device=dy.device)
+        _ar_scratch[key] = scratch
     arr = (c_void_p * len(dst_ptrs))(*dst_ptrs)
-    rc = lib.ppb_gemm_allreduce_bf16(dy.data_ptr(), x.data_ptr(), prev.data_ptr(), arr, len(dst_ptrs), Nout, Nin, T,
-                                     dy.stride(0), x.stride(0), prev.stride(0), float(alpha), force_bn, force_splits,
-                                     torch.cuda.current_stream().cuda_stream)
+    rc = lib.ppb_gemm_allreduce_bf16(dy.data_ptr(), x.data_ptr(), accum.data_ptr(), arr, len(dst_ptrs), Nout, Nin, T,
+                                     dy.stride(0), x.stride(0), accum.stride(0), scratch.data_ptr(), scratch.numel(),
+                                     force_bn, force_splits, torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "ppb_gemm_allreduce_bf16")
     _lib.count_launch()
 
@@ -69,12 +81,12 @@ class FusedGradAllReduce:
       replica has not finished consuming/zeroing for step k.
     """
 
-    def __init__(self, grad_arena: torch.Tensor, n_total: int, dp_group, alpha: float):
+    def __init__(self, grad_arena: torch.Tensor, n_total: int, dp_group, grad_scale: float):
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm_mem
         self.grad = grad_arena
         self.n_total = n_total
-        self.alpha = alpha
+        self.grad_scale = grad_scale   # 1/(m*dp): applied by the optimizer kernel, the pushes are unscaled sums
         self.group = dp_group
         dev = grad_arena.device
         n = max(grad_arena.numel(), 8)
@@ -102,7 +114,7 @@ class FusedGradAllReduce:
     def wgrad(self, dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor) -> None:
         off = self._offset(dw_accum)
         self.covered.append((off, dw_accum.numel()))
-        gemm_allreduce(dy, x, dw_accum, [p + 4 * off for p in self.base_ptrs], self.alpha)
+        gemm_allreduce(dy, x, dw_accum, [p + 4 * off for p in self.base_ptrs])
 
     def finish(self) -> None:
         """Push the gradients no GEMM produced (biases, norms, embedding) and synchronise the replicas."""
@@ -113,7 +125,7 @@ class FusedGradAllReduce:
                 lo, hi = pos, off
                 hi = min(self.n_total, (hi + 3) // 4 * 4)
                 if hi > lo:
-                    push_add(self.grad[lo:hi], [p + 4 * lo for p in self.base_ptrs], self.alpha)
+                    push_add(self.grad[lo:hi], [p + 4 * lo for p in self.base_ptrs], 1.0)
             pos = max(pos, off + n)
         self.hdl.barrier(channel=0)
 

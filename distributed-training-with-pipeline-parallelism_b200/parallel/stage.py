@@ -246,8 +246,8 @@ class PipelineStage:
         nd = self.n_decay
         coef = clip_coef
         grad = self.grad
-        if self.fused_ar is not None:   # already reduced over replicas and scaled by 1/(m*dp) in the GEMM epilogues
-            grad, grad_scale = self.fused_ar.final, 1.0
+        if self.fused_ar is not None:   # already summed over the replicas by the fused GEMM epilogues
+            grad = self.fused_ar.final
         for lo, hi, wd in ((0, nd, weight_decay), (nd, self.n_total, 0.0)):
             if hi <= lo:
                 continue

@@ -47,15 +47,18 @@ int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, lo
                   int force_splits, void* stream);
 
 /* ---- K10: last-micro-batch wgrad GEMM fused with the data-parallel gradient all-reduce ---------------------------
- * dst_r[M,N] += alpha * (prev[M,N] + A^T B) for every replica r in dst_ptrs (own buffer and peer-mapped symmetric
- * memory of the other replicas; host array of n_dst device pointers, all with leading dimension ldc).  A is stored
- * [K, lda], B is stored [K, ldb] (the wgrad form).  Every replica calls it on its own data; after a cross-replica
- * barrier all dst buffers hold alpha * sum_r(prev_r + A_r^T B_r).  ppb_push_add_f32 does the same for the small
- * non-GEMM gradients.  The reference has no data parallelism at all; the baseline this
- * replaces is cuBLAS wgrad + ncclAllReduce. */
-int ppb_gemm_allreduce_bf16(const void* A, const void* B, const float* prev, void* const* dst_ptrs, int n_dst, int M,
-                            int N, int K, long long lda, long long ldb, long long ldc, float alpha, int force_bn,
-                            int force_splits, void* stream);
+ * accum[M,N] += A^T B exactly like the wgrad form of ppb_gemm_bf16 (A stored [K, lda], B stored [K, ldb], split-K,
+ * TMA reduce-add); additionally, as soon as a 32-row slab of a tile is complete, the CTA that finished it last
+ * reduce-adds the slab into dst_r[M,N] for every replica r in dst_ptrs (host array of n_dst device pointers: the
+ * caller's own reduced-gradient buffer and the peer-mapped symmetric buffers of the other replicas, leading
+ * dimension ldc).  Every replica calls it on its own data; after a cross-replica barrier every dst holds
+ * sum_r accum_r.  `scratch` (ppb_gemm_allreduce_scratch_bytes, zero-filled once by the caller; the kernel re-zeroes what it used) holds the arrival counters.  ppb_push_add_f32 does
+ * the same for the small non-GEMM gradients.  The reference has no data parallelism at all (SURVEY.md section
+ * 2.5); the baseline this replaces is wgrad GEMM + ncclAllReduce. */
+long long ppb_gemm_allreduce_scratch_bytes(int M, int N);
+int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accum, void* const* dst_ptrs, int n_dst, int M, int N,
+                            int K, long long lda, long long ldb, long long ldc, void* scratch, long long scratch_bytes,
+                            int force_bn, int force_splits, void* stream);
 int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long long n, float scale, void* stream);
 
 /* ---- K5: fused residual-add + dropout + LayerNorm / RMSNorm ------------------------------------------------

@@ -241,12 +241,14 @@ def test_gemm_allreduce_push_single_gpu(M, N, K, n_dst, splits):
     dy = torch.randn(K, M, device=DEV, dtype=torch.bfloat16)
     x = torch.randn(K, N, device=DEV, dtype=torch.bfloat16)
     prev = torch.randn(M, N, device=DEV)
+    accum = prev.clone()
     dsts = [torch.full((M, N), float(i + 1), device=DEV) for i in range(n_dst)]
-    alpha = 0.125
-    gemm_allreduce(dy, x, prev, [d.data_ptr() for d in dsts], alpha, force_splits=splits)
-    want = alpha * (prev + dy.float().t() @ x.float())
-    for i, d in enumerate(dsts):
-        assert rel_err(d - (i + 1), want) < 5e-3
+    for rep in range(2):  # twice: the arrival counters must have reset themselves
+        gemm_allreduce(dy, x, accum, [d.data_ptr() for d in dsts], force_splits=splits)
+    prod = dy.float().t() @ x.float()
+    assert rel_err(accum, prev + 2 * prod) < 5e-3
+    for i, d in enumerate(dsts):   # push 1 saw prev + prod, push 2 saw prev + 2 prod
+        assert rel_err(d - (i + 1), 2 * prev + 3 * prod) < 5e-3
     src = torch.randn(4096, device=DEV)
     outs = [torch.ones(4096, device=DEV) for _ in range(n_dst)]
     push_add(src, [o.data_ptr() for o in outs], 0.5)
