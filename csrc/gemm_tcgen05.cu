@@ -40,6 +40,10 @@ struct GemmParams {
   // OUT == 3 (fused all-reduce): per-(tile, epilogue-warp) arrival counters + number of replicas to push to
   unsigned int* tile_counters;
   int n_dst;
+  // tensor-parallel fusions (0 = off): rows of A gathered from / rows of C scattered to `rows_per_rank`-row shards
+  int ag_rows_per_rank;   // K12: A tile rows [m0, m0+128) live in shard m0 / ag_rows_per_rank (maps in a_maps[])
+  int ag_rank;            //      own rank: its shard's tiles are scheduled first
+  int rs_rows_per_rank;   // K11: C slab rows go to owner (row / rs_rows_per_rank)'s buffer (maps in dst_maps[])
 };
 
 struct DstMaps {
@@ -60,7 +64,8 @@ struct GemmCfg {
 
 template <int BN, bool A_MN, bool B_MN, int OUT>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
-                                          const GemmParams& p, const CUtensorMap* dst_maps) {
+                                          const GemmParams& p, const CUtensorMap* dst_maps,
+                                          const CUtensorMap* a_maps = nullptr) {
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -101,6 +106,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 
   const int total_tiles = p.tiles_m * p.tiles_n * p.splits;
   const int num_kb_total = (p.K + BK - 1) / BK;
+  // all-gather fusion: rotate the row-block order so that every rank starts on its OWN shard (already local)
+  // and touches the peers' shards afterwards, spreading the NVLink reads over time
+  const int m_rot = p.ag_rows_per_rank ? (p.ag_rank * (p.ag_rows_per_rank / BM)) : 0;
+  auto m_block_of = [&](int mn) { return (mn % p.tiles_m + m_rot) % p.tiles_m; };
 
   if (warp == 4) {
     // ======================= TMA producer =======================
@@ -110,17 +119,25 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
         const int mn = t % (p.tiles_m * p.tiles_n);
         const int sp = t / (p.tiles_m * p.tiles_n);
-        const int m0 = (mn % p.tiles_m) * BM;
+        const int m0 = m_block_of(mn) * BM;
         const int n0 = (mn / p.tiles_m) * BN;
         const int kb0 = sp * p.kb_per_split;
         const int kb1 = min(num_kb_total, kb0 + p.kb_per_split);
+        // K12: the A rows of this tile come from the shard (possibly on a peer GPU) that owns them
+        const CUtensorMap* ta = &tmA;
+        int a_row = m0;
+        if (p.ag_rows_per_rank) {
+          const int owner = m0 / p.ag_rows_per_rank;
+          ta = a_maps + owner;
+          a_row = m0 - owner * p.ag_rows_per_rank;
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           mbar_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sb = sa + Cfg::A_BYTES;
           if (!A_MN) {
-            tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m0);  // box {64 k, 128 rows}
+            tma_load_2d(sa, ta, full_bar(stage), kb * BK, a_row);  // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int i = 0; i < BM / 64; ++i)  // box {64 m, 64 k}
@@ -190,7 +207,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     uint32_t push_phase = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int mn = t % (p.tiles_m * p.tiles_n);
-      const int m0 = (mn % p.tiles_m) * BM;
+      const int m0 = m_block_of(mn) * BM;
       const int n0 = (mn / p.tiles_m) * BN;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
@@ -294,7 +311,14 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         __syncwarp();
         if (lane == 0) {
           if constexpr (OUT == 2 || OUT == 3) {
-            tma_reduce_add_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+            if (p.rs_rows_per_rank) {
+              // K11: this 32-row slab belongs to one tensor-parallel rank; reduce-add it into THAT rank's buffer
+              const int srow = m0 + warp * 32;
+              const int owner = srow / p.rs_rows_per_rank;
+              if (srow < p.M) tma_reduce_add_2d(dst_maps + owner, my_epi + buf * EPI_BUF_BYTES, nc, srow - owner * p.rs_rows_per_rank);
+            } else {
+              tma_reduce_add_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
+            }
           } else {
             tma_store_2d(&tmC, my_epi + buf * EPI_BUF_BYTES, nc, m0 + warp * 32);
           }
@@ -377,6 +401,28 @@ gemm_tcgen05_allreduce_kernel(const __grid_constant__ CUtensorMap tmA, const __g
                               const __grid_constant__ CUtensorMap tmC, const __grid_constant__ DstMaps dst,
                               const GemmParams p) {
   gemm_body<BN, true, true, 3>(tmA, tmB, tmC, p, dst.m);
+}
+
+// K12: all-gather -> GEMM.  C[M,N] = epi(A_gathered[M,K] * op(B)^T) where the rows of A are sharded
+// over the tensor-parallel ranks (sequence-parallel activations in symmetric memory): the TMA producer reads every
+// A tile straight from the shard that owns it -- the local one first, then the peers' over NVLink -- so no gathered
+// copy of the activations is ever materialised and the transfer overlaps the tensor-core work tile by tile.
+template <int BN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_ag_kernel(const __grid_constant__ DstMaps amaps, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  gemm_body<BN, false, B_MN, 0>(amaps.m[0], tmB, tmC, p, nullptr, amaps.m);
+}
+
+// K11: GEMM -> reduce-scatter.  Every rank computes its partial product (its K-slice of a
+// row-parallel layer) and the epilogue reduce-adds each 32-row slab directly into the fp32 buffer of the rank that
+// owns those rows (own slabs through L2, the others over NVLink).  After a barrier each rank holds the reduced
+// [M/tp, N] block; no full-size partial output and no separate reduce-scatter kernel exist.
+template <int BN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_rs_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                       const __grid_constant__ DstMaps dst, const GemmParams p) {
+  gemm_body<BN, false, B_MN, 2>(tmA, tmB, dst.m[0], p, dst.m);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -497,6 +543,9 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.seed_off = seed_offset_ptr();
   p.tile_counters = nullptr;
   p.n_dst = 0;
+  p.ag_rows_per_rank = 0;
+  p.ag_rank = 0;
+  p.rs_rows_per_rank = 0;
   p.drop_thresh = dropout_thresh16(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
@@ -568,6 +617,9 @@ extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accu
   p.drop_scale = 1.f;
   p.tile_counters = reinterpret_cast<unsigned int*>(scratch);
   p.n_dst = n_dst;
+  p.ag_rows_per_rank = 0;
+  p.ag_rank = 0;
+  p.rs_rows_per_rank = 0;
   // the arrival counters must be zero on entry: the caller zero-fills the scratch once, the kernel resets every
   // counter it used (no per-call memset launch)
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
@@ -580,6 +632,118 @@ extern "C" int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accu
   }
   if (bn == 256) PPB_LAUNCH_AR(256) else if (bn == 128) PPB_LAUNCH_AR(128) else PPB_LAUNCH_AR(64)
 #undef PPB_LAUNCH_AR
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+
+namespace ppb {
+static void fill_plain_params(GemmParams& p, int M, int N, int K, int bn, int splits) {
+  p.M = M;
+  p.N = N;
+  p.K = K;
+  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_n = (N + bn - 1) / bn;
+  p.splits = splits;
+  p.kb_per_split = (((K + BK - 1) / BK) + splits - 1) / splits;
+  p.epi = PPB_EPI_NONE;
+  p.alpha = 1.f;
+  p.bias = nullptr;
+  p.aux = nullptr;
+  p.ld_aux = 0;
+  p.seed = 0;
+  p.seed_off = nullptr;
+  p.drop_thresh = 0;
+  p.drop_scale = 1.f;
+  p.tile_counters = nullptr;
+  p.n_dst = 0;
+  p.ag_rows_per_rank = 0;
+  p.ag_rank = 0;
+  p.rs_rows_per_rank = 0;
+}
+}  // namespace ppb
+
+extern "C" int ppb_gemm_allgather_bf16(void* const* a_shards, const void* B, void* C, int M, int N, int K, long long lda,
+                                       long long ldb, long long ldc, int tp, int rank, int b_mn_major, int epi,
+                                       const void* bias, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "ppb_gemm_allgather_bf16: bad tp/rank %d/%d", tp, rank);
+  PPB_REQUIRE(M > 0 && N > 0 && K > 0 && (M % tp) == 0 && ((M / tp) % BM) == 0,
+              "ppb_gemm_allgather_bf16: rows per rank (M/tp = %d) must be a multiple of %d", M / (tp ? tp : 1), BM);
+  PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldc % 8) == 0, "ppb_gemm_allgather_bf16: misaligned leading dimension");
+  PPB_REQUIRE(epi == PPB_EPI_NONE || epi == PPB_EPI_BIAS || epi == PPB_EPI_BIAS_RELU || epi == PPB_EPI_BIAS_GELU,
+              "ppb_gemm_allgather_bf16: unsupported epilogue %d", epi);
+  PPB_REQUIRE(epi == PPB_EPI_NONE || bias != nullptr, "ppb_gemm_allgather_bf16: epilogue needs a bias");
+  int bn, splits;
+  choose_config(M, N, K, PPB_OUT_BF16, 0, 0, &bn, &splits);
+  const int rows = M / tp;
+  DstMaps am;
+  CUtensorMap tmB, tmC;
+  bool ok = true;
+  for (int r = 0; ok && r < tp; ++r)
+    ok = make_tmap_2d(&am.m[r], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, a_shards[r], (uint64_t)K, (uint64_t)rows, (uint64_t)lda * 2, BK, BM);
+  for (int r = tp; ok && r < 8; ++r) am.m[r] = am.m[0];
+  ok = ok && (b_mn_major ? make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK)
+                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn));
+  ok = ok && make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 2, 64, 32);
+  if (!ok) return -3;
+  GemmParams p;
+  fill_plain_params(p, M, N, K, bn, 1);
+  p.epi = epi;
+  p.bias = reinterpret_cast<const bf16*>(bias);
+  p.ag_rows_per_rank = rows;
+  p.ag_rank = rank;
+  const long long total = (long long)p.tiles_m * p.tiles_n;
+  const int grid = (int)(total < sm_count() ? total : sm_count());
+#define PPB_LAUNCH_AG(BN_, BMN_)                                                                                 \
+  {                                                                                                              \
+    auto kfn = gemm_tcgen05_ag_kernel<BN_, BMN_>;                                                                \
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN_>::SMEM_BYTES)); \
+    kfn<<<grid, GEMM_THREADS, GemmCfg<BN_>::SMEM_BYTES, stream>>>(am, tmB, tmC, p);                               \
+  }
+  if (bn == 256) { if (b_mn_major) PPB_LAUNCH_AG(256, true) else PPB_LAUNCH_AG(256, false) }
+  else if (bn == 128) { if (b_mn_major) PPB_LAUNCH_AG(128, true) else PPB_LAUNCH_AG(128, false) }
+  else { if (b_mn_major) PPB_LAUNCH_AG(64, true) else PPB_LAUNCH_AG(64, false) }
+#undef PPB_LAUNCH_AG
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_gemm_reducescatter_bf16(const void* A, const void* B, void* const* dst_shards, int M, int N, int K,
+                                           long long lda, long long ldb, long long ldc, int tp, int b_mn_major,
+                                           void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(tp >= 1 && tp <= 8, "ppb_gemm_reducescatter_bf16: bad tp %d", tp);
+  PPB_REQUIRE(M > 0 && N > 0 && K > 0 && (M % tp) == 0 && ((M / tp) % 32) == 0,
+              "ppb_gemm_reducescatter_bf16: rows per rank (M/tp) must be a multiple of 32");
+  PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldc % 4) == 0, "ppb_gemm_reducescatter_bf16: misaligned leading dimension");
+  int bn, splits;
+  choose_config(M, N, K, PPB_OUT_F32, 0, 0, &bn, &splits);
+  const int rows = M / tp;
+  CUtensorMap tmA, tmB;
+  DstMaps dm;
+  bool ok = make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, BM);
+  ok = ok && (b_mn_major ? make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK)
+                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn));
+  for (int r = 0; ok && r < tp; ++r)
+    ok = make_tmap_2d(&dm.m[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, dst_shards[r], (uint64_t)N, (uint64_t)rows, (uint64_t)ldc * 4, 32, 32);
+  for (int r = tp; ok && r < 8; ++r) dm.m[r] = dm.m[0];
+  if (!ok) return -3;
+  GemmParams p;
+  fill_plain_params(p, M, N, K, bn, 1);
+  p.rs_rows_per_rank = rows;
+  const long long total = (long long)p.tiles_m * p.tiles_n;
+  const int grid = (int)(total < sm_count() ? total : sm_count());
+#define PPB_LAUNCH_RS(BN_, BMN_)                                                                                 \
+  {                                                                                                              \
+    auto kfn = gemm_tcgen05_rs_kernel<BN_, BMN_>;                                                                \
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<BN_>::SMEM_BYTES)); \
+    kfn<<<grid, GEMM_THREADS, GemmCfg<BN_>::SMEM_BYTES, stream>>>(tmA, tmB, dm, p);                               \
+  }
+  if (bn == 256) { if (b_mn_major) PPB_LAUNCH_RS(256, true) else PPB_LAUNCH_RS(256, false) }
+  else if (bn == 128) { if (b_mn_major) PPB_LAUNCH_RS(128, true) else PPB_LAUNCH_RS(128, false) }
+  else { if (b_mn_major) PPB_LAUNCH_RS(64, true) else PPB_LAUNCH_RS(64, false) }
+#undef PPB_LAUNCH_RS
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -131,3 +131,102 @@ class FusedGradAllReduce:
 
     def after_optimizer(self) -> None:
         self.hdl.barrier(channel=1)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# tensor-parallel fusions (K11 / K12)
+# ------------------------------------------------------------------------------------------------------------
+def _bind_tp(lib) -> None:
+    if getattr(lib, "_ppb_tp_bound", False):
+        return
+    P, I, L = c_void_p, c_int, c_longlong
+    lib.ppb_gemm_allgather_bf16.argtypes = [P, P, P, I, I, I, L, L, L, I, I, I, I, P, P]
+    lib.ppb_gemm_allgather_bf16.restype = I
+    lib.ppb_gemm_reducescatter_bf16.argtypes = [P, P, P, I, I, I, L, L, L, I, I, P]
+    lib.ppb_gemm_reducescatter_bf16.restype = I
+    lib._ppb_tp_bound = True
+
+
+_EPI = {None: 0, "bias": 1, "relu": 2, "gelu": 3}
+
+
+def allgather_linear(a_shard_ptrs: List[int], rows_per_rank: int, K: int, lda: int, w: torch.Tensor, rank: int,
+                     bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+                     out: Optional[torch.Tensor] = None, w_mn_major: bool = False) -> torch.Tensor:
+    """K12: y[M, N] = act(concat_r(A_r)[M, K] @ w^T + bias) with A_r = the [rows_per_rank, K] bf16 shard at device
+    pointer ``a_shard_ptrs[r]`` (own buffer or a peer's symmetric buffer).  w [N, K] (or [K, N] if w_mn_major)."""
+    lib = _lib.load(required=True)
+    _bind_tp(lib)
+    tp = len(a_shard_ptrs)
+    M = rows_per_rank * tp
+    N = w.shape[1] if w_mn_major else w.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=w.device)
+    epi = 0 if bias is None else _EPI["bias" if act is None else act]
+    arr = (c_void_p * tp)(*a_shard_ptrs)
+    rc = lib.ppb_gemm_allgather_bf16(arr, w.data_ptr(), out.data_ptr(), M, N, K, lda, w.stride(0), out.stride(0), tp, rank,
+                                     int(w_mn_major), epi, _lib.ptr(bias), torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "ppb_gemm_allgather_bf16")
+    _lib.count_launch()
+    return out
+
+
+def linear_reducescatter(x: torch.Tensor, w: torch.Tensor, dst_shard_ptrs: List[int], ld_dst: int,
+                         w_mn_major: bool = False) -> None:
+    """K11: for every owner o, dst_o[M/tp, N] (fp32) += rows of (x[M, K] @ w^T) owned by o.  The caller zeroes the
+    destination buffers beforehand and synchronises the ranks afterwards."""
+    lib = _lib.load(required=True)
+    _bind_tp(lib)
+    tp = len(dst_shard_ptrs)
+    M, K = x.shape
+    N = w.shape[1] if w_mn_major else w.shape[0]
+    arr = (c_void_p * tp)(*dst_shard_ptrs)
+    rc = lib.ppb_gemm_reducescatter_bf16(x.data_ptr(), w.data_ptr(), arr, M, N, K, x.stride(0), w.stride(0), ld_dst, tp,
+                                         int(w_mn_major), torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "ppb_gemm_reducescatter_bf16")
+    _lib.count_launch()
+
+
+class SymmetricBuffer:
+    """A tensor in symmetric memory + the table of its peer-mapped addresses on every rank of ``group``."""
+
+    def __init__(self, shape, dtype, device, group):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.tensor = symm_mem.empty(*shape, dtype=dtype, device=device)
+        self.tensor.zero_()
+        self.hdl = symm_mem.rendezvous(self.tensor, group)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.rank, self.world = self.hdl.rank, self.hdl.world_size
+
+    def barrier(self, channel: int = 0) -> None:
+        self.hdl.barrier(channel=channel)
+
+
+class TensorParallelMLP:
+    """Megatron-style tensor + sequence parallel feed-forward block built from the two fused kernels:
+
+        x_shard [T/tp, d]  --(K12 all-gather -> GEMM, bias+act epilogue)-->  h [T, f/tp]
+        h                  --(K11 GEMM -> reduce-scatter)----------------->  y_shard [T/tp, d] (fp32 sums)
+
+    ``w1`` is the [f/tp, d] row slice of linear1 and ``w2`` the [d, f/tp] column slice of linear2 owned by this
+    rank.  Activations stay sharded on the sequence dimension between the blocks."""
+
+    def __init__(self, w1: torch.Tensor, b1: torch.Tensor, w2: torch.Tensor, T: int, group, act: str = "relu"):
+        dev = w1.device
+        self.w1, self.b1, self.w2, self.act = w1, b1, w2, act
+        self.d = w1.shape[1]
+        import torch.distributed as dist
+        self.tp = dist.get_world_size(group)
+        self.rows = T // self.tp
+        self.x_sym = SymmetricBuffer((self.rows, self.d), torch.bfloat16, dev, group)
+        self.y_sym = SymmetricBuffer((self.rows, self.d), torch.float32, dev, group)
+        self.rank = self.x_sym.rank
+
+    def forward(self, x_shard: torch.Tensor) -> torch.Tensor:
+        self.x_sym.tensor.copy_(x_shard)
+        self.y_sym.tensor.zero_()
+        self.x_sym.barrier(0)                       # every rank's input shard and zeroed output are in place
+        h = allgather_linear(self.x_sym.ptrs, self.rows, self.d, self.d, self.w1, self.rank, self.b1, self.act)
+        linear_reducescatter(h, self.w2, self.y_sym.ptrs, self.d)
+        self.y_sym.barrier(1)                       # all partial sums have landed
+        return self.y_sym.tensor

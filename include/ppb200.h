@@ -59,6 +59,20 @@ long long ppb_gemm_allreduce_scratch_bytes(int M, int N);
 int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accum, void* const* dst_ptrs, int n_dst, int M, int N,
                             int K, long long lda, long long ldb, long long ldc, void* scratch, long long scratch_bytes,
                             int force_bn, int force_splits, void* stream);
+/* ---- K12: all-gather -> GEMM (column-parallel layer under tensor parallelism, sequence-sharded input) ------------
+ * C[M,N] = epi(A[M,K] * op(B)^T) where A is the concatenation of `tp` row shards a_shards[r] ([M/tp, lda], local or
+ * peer-mapped symmetric memory); the TMA producer reads each tile from the shard that owns it, own shard first.
+ * M/tp must be a multiple of 128.  Baseline replaced: ncclAllGather + GEMM (torch _fused_all_gather_matmul). */
+int ppb_gemm_allgather_bf16(void* const* a_shards, const void* B, void* C, int M, int N, int K, long long lda,
+                            long long ldb, long long ldc, int tp, int rank, int b_mn_major, int epi, const void* bias,
+                            void* stream);
+/* ---- K11: GEMM -> reduce-scatter (row-parallel layer under tensor parallelism) -----------------------------------
+ * dst_shards[o][M/tp, N] (fp32, zeroed by the caller) += rows [o*M/tp, (o+1)*M/tp) of A[M,K] * op(B)^T, for every
+ * owner o: each 32-row slab of the partial product is TMA-reduce-added into its owner's buffer (local or over
+ * NVLink).  After a cross-rank barrier dst_shards[rank] holds the reduced block.  Baseline replaced: GEMM +
+ * ncclReduceScatter (torch _fused_matmul_reduce_scatter). */
+int ppb_gemm_reducescatter_bf16(const void* A, const void* B, void* const* dst_shards, int M, int N, int K,
+                                long long lda, long long ldb, long long ldc, int tp, int b_mn_major, void* stream);
 int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long long n, float scale, void* stream);
 
 /* ---- K5: fused residual-add + dropout + LayerNorm / RMSNorm ------------------------------------------------

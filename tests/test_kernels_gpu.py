@@ -254,3 +254,34 @@ def test_gemm_allreduce_push_single_gpu(M, N, K, n_dst, splits):
     push_add(src, [o.data_ptr() for o in outs], 0.5)
     for o in outs:
         assert rel_err(o, 1 + 0.5 * src) < 1e-6
+
+
+@pytest.mark.parametrize("tp,rows,N,K,act", [(2, 256, 512, 256, None), (4, 128, 2048, 1024, "relu"), (2, 512, 200, 136, "gelu")])
+def test_allgather_gemm_single_gpu(tp, rows, N, K, act):
+    """K12 numerics with the tp shards living in separate buffers of one GPU."""
+    from ppb200.ops.collective import allgather_linear
+    torch.manual_seed(13)
+    shards = [torch.randn(rows, K, device=DEV, dtype=torch.bfloat16) for _ in range(tp)]
+    w = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.05
+    b = torch.randn(N, device=DEV, dtype=torch.bfloat16)
+    for rank in range(tp):
+        y = allgather_linear([s.data_ptr() for s in shards], rows, K, K, w, rank, b, act)
+        ref = R.linear_fwd(torch.cat(shards), w, b, act)
+        assert rel_err(y, ref) < 1e-2
+
+
+@pytest.mark.parametrize("tp,M,N,K", [(2, 512, 768, 256), (4, 1024, 1024, 512), (2, 192, 200, 136)])
+def test_gemm_reducescatter_single_gpu(tp, M, N, K):
+    """K11 numerics: tp 'ranks' with different K-slices push into per-owner buffers on one GPU."""
+    from ppb200.ops.collective import linear_reducescatter
+    torch.manual_seed(14)
+    rows = M // tp
+    dsts = [torch.zeros(rows, N, device=DEV) for _ in range(tp)]
+    total = torch.zeros(M, N, device=DEV)
+    for r in range(tp):
+        x = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+        w = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.05
+        linear_reducescatter(x, w, [d.data_ptr() for d in dsts], N)
+        total += x.float() @ w.float().t()
+    got = torch.cat(dsts)
+    assert rel_err(got, total) < 5e-3

@@ -37,3 +37,10 @@ def test_pipeline_pp2_loss_matches_single_gpu():
     res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
     assert abs(res["loss_pp2"] - res["loss_pp1"]) < 2e-2 * abs(res["loss_pp1"]), res
     assert res["loss_after"] < res["loss_pp2"], res
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_tensor_parallel_mlp_fused_kernels():
+    out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_tp_check.py")])
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert res["max_rel_err"] < 2e-2, res
