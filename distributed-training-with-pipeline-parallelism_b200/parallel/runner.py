@@ -34,7 +34,8 @@ class PipelineSchedule:
     def __init__(self, stages: Union[PipelineStage, Sequence[PipelineStage]], n_microbatches: int, loss_fn=None, *,
                  schedule: Optional[str] = None, pp_group=None, pp_group_bwd=None, dp_group=None,
                  optimizer: Optional[dict] = None,
-                 scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None):
+                 scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None,
+                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2):
         self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
         if not self.stages:
             raise ValueError("need at least one stage")
@@ -87,6 +88,14 @@ class PipelineSchedule:
         if self.dp_size > 1 and optimizer is not None and self.cuda:
             self.fused_dp = all([st.enable_fused_dp(self.m) for st in self.stages if st.n_total > 0])
         self._b_seen: Dict[int, int] = {}
+        # CUDA graphs: one forward + one backward graph per (stage, in-flight slot); eager for the first steps
+        import os
+        want = (os.environ.get("PPB_CUDA_GRAPHS", "1") != "0") if cuda_graphs is None else cuda_graphs
+        self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None)
+        self.graph_warmup_steps = graph_warmup_steps
+        if self.use_graphs:
+            for st in self.stages:
+                st.enable_graphs(self._max_inflight(st.stage_index))
 
     # ---- helpers ------------------------------------------------------------------------------------------------
     def _global_rank(self, pp_rank: int) -> int:
@@ -96,6 +105,18 @@ class PipelineSchedule:
 
     def _rank_of_stage(self, stage: int) -> int:
         return stage % self.pp_size
+
+    def _max_inflight(self, stage: int) -> int:
+        live = peak = 0
+        for a in self.order:
+            if a.stage != stage:
+                continue
+            if a.type == T.F:
+                live += 1
+                peak = max(peak, live)
+            elif a.type == T.B:
+                live -= 1
+        return max(1, peak)
 
     def _sync_shape(self, x: Optional[torch.Tensor]) -> Tuple[int, int]:
         """One-time (B, S) agreement: the rank that owns stage 0 knows it from its input.  Replaces torch's
@@ -160,6 +181,8 @@ class PipelineSchedule:
         send_works: List[Any] = []
         keep_alive: List[torch.Tensor] = []
         allreduce_works: Dict[int, Any] = {}
+        slot_sends: Dict[Tuple[int, str, int], Any] = {}
+        graphs_on = self.use_graphs and self.steps_done >= self.graph_warmup_steps and all(st.training for st in self.stages)
         b_count: Dict[int, int] = {}
         timeline: List[Tuple[Action, Any, Any]] = []
         rec = self.record_timeline
@@ -205,8 +228,11 @@ class PipelineSchedule:
                         grp = self.pp_group_bwd
                     t = t.view(sizes[a.mb], S, -1)
                     dst = self._global_rank(self._rank_of_stage(dst_stage))
-                    send_works.append(dist.isend(t, dst=dst, group=grp))
+                    w = dist.isend(t, dst=dst, group=grp)
+                    send_works.append(w)
                     keep_alive.append(t)
+                    if graphs_on:
+                        slot_sends[(a.stage, "F" if typ == T.SEND_F else "B", a.mb % self.local[a.stage].nslots)] = w
                 elif typ == T.F:
                     st = self.local[a.stage]
                     if a.stage == 0:
@@ -215,7 +241,13 @@ class PipelineSchedule:
                         inp = self._take_input(recv_state, local_in, a.stage, "F", a.mb, compute)
                     tgt = y_chunks[a.mb] if (a.stage == last_stage and y_chunks is not None) else None
                     t0 = tick()
-                    out = st.forward_one_chunk(a.mb, inp, tgt, 1.0, None if self.fused_loss else self.loss_fn)
+                    if graphs_on:
+                        prev = slot_sends.pop((a.stage, "F", a.mb % st.nslots), None)
+                        if prev is not None:
+                            prev.wait()   # the slot's static output buffer is free again
+                        out = st.forward_graphed(a.mb, inp, tgt)
+                    else:
+                        out = st.forward_one_chunk(a.mb, inp, tgt, 1.0, None if self.fused_loss else self.loss_fn)
                     timeline.append((a, t0, tick()))
                     if a.stage != last_stage:
                         if self._rank_of_stage(a.stage + 1) == self.pp_rank:
@@ -229,7 +261,17 @@ class PipelineSchedule:
                         dout = self._take_input(recv_state, local_in, a.stage, "B", a.mb, compute)
                     t0 = tick()
                     b_count[a.stage] = b_count.get(a.stage, 0) + 1
-                    din = st.backward_one_chunk(a.mb, dout, last=(b_count[a.stage] == self.m))
+                    is_last_b = b_count[a.stage] == self.m
+                    if graphs_on:
+                        prev = slot_sends.pop((a.stage, "B", a.mb % st.nslots), None)
+                        if prev is not None:
+                            prev.wait()
+                        if is_last_b and st.fused_ar is not None:
+                            din = st.backward_eager_on_slot(a.mb, dout, last=True)
+                        else:
+                            din = st.backward_graphed(a.mb, dout)
+                    else:
+                        din = st.backward_one_chunk(a.mb, dout, last=is_last_b)
                     timeline.append((a, t0, tick()))
                     if a.stage != 0:
                         if self._rank_of_stage(a.stage - 1) == self.pp_rank:

@@ -48,6 +48,8 @@ class PipelineStage:
         self.step_count = 0
         self.training = True
         self.fused_ar = None
+        self.nslots = 0
+        self.graphs = None
         self.has_params = any(True for _ in submodule.parameters())
 
     # ---- memory layout --------------------------------------------------------------------------------------
@@ -223,6 +225,85 @@ class PipelineStage:
                 return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
         finally:
             self.sink.fused_ar = None
+
+    # ---- CUDA graphs ----------------------------------------------------------------------------------------------
+    def enable_graphs(self, nslots: int) -> None:
+        """Capture forward / backward of one micro-batch per in-flight slot into CUDA graphs (launch-bound inner
+        loops: ~45 / ~100 launches per 3-layer stage).  Micro-batch ``mb`` uses slot ``mb % nslots``; the
+        activation stash of a slot lives in the graphs' private memory pool."""
+        self.nslots = int(nslots)
+        self.graphs: Dict[int, dict] = {}
+        self.graph_pool = torch.cuda.graph_pool_handle()
+
+    def _set_mb_seed(self, mb: int) -> None:
+        # micro-batch-varying part of the dropout seed lives in device memory, so graph replays get fresh masks
+        self.seed_offset.fill_((self.step_count * 0x632BE5AB + (mb + 1) * 0x9E3779B1) & 0x7FFFFFFFFFFFFFFF)
+
+    def forward_graphed(self, mb: int, inp: torch.Tensor, target: Optional[torch.Tensor] = None) -> torch.Tensor:
+        from ..ops import _lib as L
+        slot = mb % self.nslots
+        g = self.graphs.get(slot)
+        self._set_mb_seed(mb)
+        if g is None:
+            g = {"in": inp.clone(), "tgt": None if target is None else target.clone(), "F": torch.cuda.CUDAGraph(),
+                 "B": None, "dout": None, "din": None, "sends": {}}
+            b, S = inp.shape[0], inp.shape[1]
+            ctx = Ctx(self.args, b, S, self.base_seed, slot, self.training, 0)
+            st: dict = {}
+            n0 = L.launches()
+            with torch.cuda.graph(g["F"], pool=self.graph_pool):
+                with torch.no_grad():
+                    out = stage_forward(self.submod, g["in"], ctx, st)
+                    loss = None
+                    if self.is_last and g["tgt"] is not None and self.submod.output is not None:
+                        loss = stage_loss(out, g["tgt"], 1.0, st)
+            g.update(out=out, loss=loss, stash=st, ctx=ctx, nF=L.launches() - n0, shape=(b, S))
+            self.graphs[slot] = g
+        else:
+            g["in"].copy_(inp)
+            if target is not None:
+                g["tgt"].copy_(target)
+            L.count_launch(g["nF"])
+        g["F"].replay()
+        if g["loss"] is not None:
+            self.losses[mb] = g["loss"].clone()
+        self.stash[mb] = g["stash"]
+        self.ctxs[mb] = g["ctx"]
+        return g["out"]
+
+    def backward_graphed(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        from ..ops import _lib as L
+        slot = mb % self.nslots
+        g = self.graphs[slot]
+        self._set_mb_seed(mb)
+        self.stash.pop(mb, None)
+        self.ctxs.pop(mb, None)
+        if g["B"] is None:
+            g["dout"] = None if dout is None else dout.clone()
+            g["B"] = torch.cuda.CUDAGraph()
+            st, ctx = g["stash"], g["ctx"]
+            n0 = L.launches()
+            with torch.cuda.graph(g["B"], pool=self.graph_pool):
+                with torch.no_grad():
+                    douts = [st["dlogits"]] if g["dout"] is None else [g["dout"]]
+                    g["din"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+            g["nB"] = L.launches() - n0
+        else:
+            if dout is not None:
+                g["dout"].copy_(dout.reshape(g["dout"].shape))
+            L.count_launch(g["nB"])
+        g["B"].replay()
+        return g["din"]
+
+    def backward_eager_on_slot(self, mb: int, dout: Optional[torch.Tensor], last: bool) -> Optional[torch.Tensor]:
+        """Eager backward over a graph slot's stash (used for the step's last micro-batch when the fused DP
+        all-reduce rides on its weight-gradient GEMMs, which is a different launch sequence)."""
+        slot = mb % self.nslots
+        g = self.graphs[slot]
+        self._set_mb_seed(mb)
+        self.stash[mb] = g["stash"]
+        self.ctxs[mb] = g["ctx"]
+        return self.backward_one_chunk(mb, dout, last=last)
 
     # ---- gradient reduction + optimizer ---------------------------------------------------------------------------
     def all_reduce_grads(self, async_op: bool = False):
