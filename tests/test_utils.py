@@ -1,0 +1,204 @@
+"""CPU unit tests: partitioner, mesh layout, analysis formulas on the reference's published table, checkpoint
+shards, config/CLI, trace/bubble helpers, dropout reference, launcher error contract."""
+import json
+import os
+import re
+
+import pytest
+import torch
+
+from ppb200.models import ModelArgs, Transformer, preset
+from ppb200.ops import reference as R
+from ppb200.parallel import partition as Pn
+from ppb200.parallel.mesh import coords_of, group_ranks, rank_of
+from ppb200.utils import analysis, checkpoint, trace
+from ppb200.utils.config import RunConfig
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---- partitioner (helper:60-94) -------------------------------------------------------------------------------
+def test_reference_ranges_remainder_goes_to_last_stage():
+    assert Pn.reference_ranges(12, 4) == [(0, 3), (3, 6), (6, 9), (9, 12)]
+    assert Pn.reference_ranges(10, 4) == [(0, 2), (2, 4), (4, 6), (6, 10)]        # helper:74-75
+    assert Pn.reference_ranges(4, 8)[-1] == (0, 4) and Pn.reference_ranges(4, 8)[0] == (0, 0)  # quirk 8
+
+
+def test_balanced_ranges_cover_all_layers_and_relieve_the_head_stage():
+    a = preset("ref-gpt2-medium")
+    for P in (1, 2, 3, 4, 6, 8):
+        rg = Pn.balanced_ranges(24, P, a, 1024)
+        assert rg[0][0] == 0 and rg[-1][1] == 24
+        assert all(rg[i][1] == rg[i + 1][0] for i in range(P - 1))
+        assert all(e > s for s, e in rg)
+        assert (rg[-1][1] - rg[-1][0]) <= max(e - s for s, e in rg)   # the head stage never has the most layers
+
+
+def test_prune_and_direct_build_give_the_same_stage_keys():
+    args = ModelArgs(dim=32, n_layers=5, n_heads=4, vocab_size=50, ffn_dim=64)
+    full_keys = set(Transformer(args).state_dict())
+    union = set()
+    for s in range(3):
+        pruned = Pn.prune_to_stage(Transformer(args), s, 3)
+        built = Pn.build_stage_model(args, s, 3, device=torch.device("cpu"), seed=0)
+        assert set(pruned.state_dict()) == set(built.state_dict())
+        assert all(p.device.type == "cpu" for p in built.parameters())
+        assert not (union & set(pruned.state_dict()))
+        union |= set(pruned.state_dict())
+    assert union == full_keys
+    # global layer indices are preserved
+    assert any(k.startswith("layers.4.") for k in Pn.prune_to_stage(Transformer(args), 2, 3).state_dict())
+
+
+def test_interleaved_fallback_rule_matches_helper():
+    # helper:181-185: two chunks per rank iff n_layers % (2 * world) == 0
+    for n_layers, world, want in [(4, 2, 2), (8, 4, 2), (4, 4, 1), (12, 4, 1), (12, 2, 2)]:
+        v = 2 if n_layers % (world * 2) == 0 else 1
+        assert v == want
+
+
+# ---- mesh ---------------------------------------------------------------------------------------------------------
+def test_mesh_rank_layout_roundtrip():
+    dp, pp, tp = 2, 4, 2
+    seen = set()
+    for d in range(dp):
+        for p in range(pp):
+            for t in range(tp):
+                r = rank_of(d, p, t, pp, tp)
+                assert coords_of(r, pp, tp) == (d, p, t)
+                seen.add(r)
+    assert seen == set(range(16))
+    ppg, dpg, tpg = group_ranks(dp, pp, tp)
+    assert len(ppg) == dp * tp and all(len(g) == pp for g in ppg)
+    assert len(dpg) == pp * tp and all(len(g) == dp for g in dpg)
+    assert tpg[0] == [0, 1]
+    assert sorted(r for g in ppg for r in g) == list(range(16))
+
+
+# ---- analysis on the reference's published numbers ---------------------------------------
+def _published_df():
+    import pandas as pd
+    rows = []
+    for line in open(os.path.join(ROOT, "BASELINE.md")):
+        m = re.match(r"^\|\s*(\d+)\s*\|\s*(\d+)\s*\|\s*(\d+)\s*\|\s*(GPipe|1F1B|Interleaved1F1B)\s*\|\s*(\d)\s*\|\s*([\d.]+)\s*\|", line)
+        if m:
+            rows.append({"n_layers": int(m.group(1)), "n_heads": int(m.group(2)), "num_processes": int(m.group(3)),
+                         "schedule": m.group(4), "throughput": float(m.group(6))})
+    return pd.DataFrame(rows[:54])  # section 2 of BASELINE.md (later sections re-quote a few rows)
+
+
+def test_speedup_and_efficiency_reproduce_the_notebook_table():
+    df = _published_df()
+    assert len(df) == 54
+    sp = analysis.compute_speedup_and_efficiency(df)
+    assert len(sp) == 36
+    row = sp[(sp.n_layers == 4) & (sp.n_heads == 4) & (sp.num_processes == 2) & (sp.schedule == "1F1B")].iloc[0]
+    assert abs(row.speedup - 1.0265) < 1e-3 and abs(row.efficiency - 51.32) < 0.05      # nb:802
+    row = sp[(sp.n_layers == 8) & (sp.n_heads == 4) & (sp.num_processes == 4) & (sp.schedule == "Interleaved1F1B")].iloc[0]
+    assert abs(row.speedup - 1.1247) < 1e-3 and abs(row.efficiency - 28.12) < 0.05      # nb:817
+    assert abs(sp.speedup.max() - 1.171) < 2e-3 and abs(sp.speedup.min() - 0.913) < 2e-3
+    ratio = analysis.scaling_ratio(df)
+    assert len(ratio) == 27 and abs(ratio.ratio_4_over_2.mean() - 1.114) < 5e-3
+    piv = analysis.throughput_pivot(df)
+    assert piv.shape == (9, 6)
+
+
+def test_plots_render_headless(tmp_path):
+    df = _published_df()
+    sp = analysis.compute_speedup_and_efficiency(df)
+    pa = analysis.plot_speedup_and_efficiency(sp, str(tmp_path / "a.svg"))
+    pb = analysis.plot_throughput_grid(df, str(tmp_path / "b.svg"))
+    assert os.path.getsize(pa) > 1000 and os.path.getsize(pb) > 1000
+    env = analysis.environment_report()
+    assert "torch" in env and "cuda_available" in env
+
+
+# ---- checkpoint shards ----------------------------------------------------------------------------------------------
+def test_checkpoint_shards_merge_to_full_state_dict_and_reshard(tmp_path):
+    from ppb200.api import manual_model_split
+    args = ModelArgs(dim=32, n_layers=4, n_heads=4, vocab_size=50, ffn_dim=64, dropout=0.0)
+    torch.manual_seed(0)
+    full = Transformer(args)
+    want = {k: v.clone() for k, v in full.state_dict().items()}
+    import copy
+    stages = [manual_model_split(copy.deepcopy(full), s, 2, torch.device("cpu")).materialize() for s in range(2)]
+    for st in stages:
+        st.exp_avg.fill_(0.5)
+        st.step_count = 7
+        checkpoint.save_stage(st, str(tmp_path))
+    merged = checkpoint.merge_shards(str(tmp_path))
+    assert set(merged) == set(want)
+    assert all(torch.equal(merged[k], want[k]) for k in want)
+    # the merged dict loads into the unmodified reference layout and into a different stage count
+    Transformer(args).load_state_dict(merged)
+    st4 = manual_model_split(Transformer(args), 3, 4, torch.device("cpu")).materialize()
+    step = checkpoint.load_stage(st4, str(tmp_path))
+    assert step == 7
+    for k, v in st4.state_dict().items():
+        assert torch.equal(v, want[k])
+    assert float(st4.exp_avg[: st4.n_total].max()) == 0.5
+
+
+# ---- config ---------------------------------------------------------------------------------------------------------
+def test_run_config_cli_and_presets():
+    cfg = RunConfig.from_args(["--model", "ref-gpt2-medium", "--schedule", "Interleaved1F1B", "--pp", "8",
+                               "--virtual-stages", "2", "--n-microbatches", "32", "--optimizer", "false"])
+    assert cfg.pp == 8 and cfg.virtual_stages == 2 and cfg.n_microbatches == 32 and cfg.optimizer is False
+    a = cfg.model_args()
+    assert (a.dim, a.n_layers, a.n_heads, a.vocab_size, a.ffn_dim) == (1024, 24, 16, 50257, 2048)
+    assert cfg.optimizer_dict() is None
+    assert RunConfig().optimizer_dict()["lr"] == 1e-4
+    d = ModelArgs()
+    assert (d.dim, d.n_layers, d.n_heads, d.vocab_size) == (768, 8, 8, 10000)      # helper:23-28
+    assert d.params_per_layer() == 7_877_888 and d.num_params() == 78_394_640 + 0  # SURVEY.md 2.3 (8 layers: 78.4 M)
+    with pytest.raises(ValueError):
+        ModelArgs(dim=100, n_heads=8)
+
+
+# ---- trace helpers ----------------------------------------------------------------------------------------------------
+def test_bubble_from_events_and_chrome_trace(tmp_path):
+    evs = [{"name": "0F0", "ph": "X", "pid": 0, "tid": 0, "ts": 0.0, "dur": 10.0},
+           {"name": "0B0", "ph": "X", "pid": 0, "tid": 0, "ts": 30.0, "dur": 20.0},
+           {"name": "1F0", "ph": "X", "pid": 1, "tid": 1, "ts": 10.0, "dur": 10.0},
+           {"name": "1B0", "ph": "X", "pid": 1, "tid": 1, "ts": 20.0, "dur": 10.0}]
+    b = trace.bubble_from_events(evs)
+    assert abs(b["rank0"] - 0.4) < 1e-9 and abs(b["rank1"] - 0.6) < 1e-9 and b["max"] == b["rank1"]
+    trace.write_chrome_trace(evs, str(tmp_path / "t.json"))
+    assert len(json.load(open(tmp_path / "t.json"))["traceEvents"]) == 4
+
+
+# ---- dropout reference ------------------------------------------------------------------------------------------------
+def test_dropout_reference_rate_and_determinism():
+    x = torch.ones(200_000)
+    y = R.dropout(x, 0.1, seed=42)
+    kept = (y != 0).float().mean().item()
+    assert abs(kept - 0.9) < 5e-3
+    assert torch.equal(y, R.dropout(x, 0.1, seed=42))
+    assert not torch.equal(y, R.dropout(x, 0.1, seed=43))
+    assert abs(y.mean().item() - 1.0) < 1e-2
+    # masks are addressed by flat index: a shifted window reproduces the same decisions
+    m_all = R.dropout_keep_mask(7, 0, 1000, 0.3)
+    assert torch.equal(m_all[100:300], R.dropout_keep_mask(7, 100, 200, 0.3))
+    assert torch.equal(R.dropout_keep_mask(7, 2**33 + 10, 64, 0.3), R.dropout_keep_mask(7, 2**33 + 10, 64, 0.3))
+
+
+# ---- launcher error contract (helper:231-235, nb:328-331) ---------------------------------------------------------------
+def _boom(rank, world, q, master_port=None):
+    if rank == 1:
+        q.put({"error": "boom"})
+    else:
+        import time
+        time.sleep(30)
+
+
+def _silent(rank, world, q, master_port=None):
+    return
+
+
+def test_launcher_reports_errors_and_kills_stragglers():
+    from ppb200.parallel.launch import launch_workers
+    import time
+    t0 = time.time()
+    res = launch_workers(_boom, 2, (), timeout=60)
+    assert res == {"error": "boom"} and time.time() - t0 < 25
+    assert launch_workers(_silent, 2, (), timeout=60) == {"error": "No results returned"}
