@@ -102,6 +102,8 @@ def run_ours(a, rank, local_rank, world):
     if world > 1:
         # no device_id: lazy communicator creation keeps P2P on per-peer communicators/streams (eager init would
         # serialise every send/recv with every other op of the group)
+        from ppb200.parallel.mesh import configure_nccl_for_pipeline
+        configure_nccl_for_pipeline()
         dist.init_process_group("nccl")
         mesh = init_mesh(dp_size=a.dp, pp_size=world // a.dp)
         pp_group, dp_group, pp_idx, dp_idx, P = mesh.pp_group, mesh.dp_group, mesh.pp_idx, mesh.dp_idx, mesh.pp_size

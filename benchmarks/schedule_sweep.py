@@ -31,6 +31,8 @@ a = ap.parse_args()
 rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
 dev = torch.device("cuda", local)
 torch.cuda.set_device(dev)
+from ppb200.parallel.mesh import configure_nccl_for_pipeline  # noqa: E402
+configure_nccl_for_pipeline()
 dist.init_process_group("nccl")
 mesh = init_mesh(dp_size=1, pp_size=world)
 margs = preset(a.model, dtype=torch.bfloat16)

@@ -2,6 +2,7 @@
 #include "host_common.h"
 
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -18,6 +19,11 @@ void set_error(const char* fmt, ...) {
 }
 const char* get_error() { return g_err; }
 
+static int g_reserved_sms = -1;
+
+// SMs the persistent kernels may occupy: the device's SM count minus a reserve left free for concurrently running
+// communication kernels (NCCL P2P CTAs that spin while a posted receive waits for its sender would otherwise push
+// one persistent CTA into a second wave).  The reserve comes from ppb_set_reserved_sms() or $PPB_RESERVED_SMS.
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;
@@ -27,7 +33,13 @@ int sm_count() {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
     cached[dev] = n;
   }
-  return cached[dev];
+  if (g_reserved_sms < 0) {
+    const char* e = getenv("PPB_RESERVED_SMS");
+    g_reserved_sms = e ? atoi(e) : 0;
+    if (g_reserved_sms < 0) g_reserved_sms = 0;
+  }
+  const int n = cached[dev] - g_reserved_sms;
+  return n > 8 ? n : 8;
 }
 
 static const unsigned long long* g_seed_off[64] = {nullptr};
@@ -87,6 +99,10 @@ bool make_tmap(CUtensorMap* out, CUtensorMapDataType dtype, int rank, const void
 
 extern "C" const char* ppb_last_error() { return ppb::get_error(); }
 extern "C" int ppb_version() { return 100; }
+extern "C" int ppb_set_reserved_sms(int n) {
+  ppb::g_reserved_sms = n < 0 ? 0 : n;
+  return 0;
+}
 extern "C" int ppb_set_dropout_offset_ptr(const unsigned long long* p) {
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {

@@ -114,6 +114,9 @@ def worker_process(rank, world_size, n_layers, n_heads, schedule_type, batch_siz
             dev = torch.device("cuda", rank % torch.cuda.device_count())
         else:
             dev = torch.device("cpu")
+        if backend == "nccl":
+            from .parallel.mesh import configure_nccl_for_pipeline
+            configure_nccl_for_pipeline()
         dist.init_process_group(backend=backend, rank=rank, world_size=world_size)
 
         # virtual-stage rule of helper:181-185 (silent fallback to one chunk per rank)

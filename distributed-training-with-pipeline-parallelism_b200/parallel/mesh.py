@@ -40,6 +40,17 @@ class Mesh:
         return "x".join(parts)
 
 
+def configure_nccl_for_pipeline() -> None:
+    """Call BEFORE ``init_process_group('nccl')``.  Stage-to-stage transfers are 2-32 MiB NCCL send/recv pairs that
+    overlap with compute; a posted receive spins on its SMs until the sender arrives, and with NCCL's default P2P
+    channel count those CTAs displace CTAs of the persistent tcgen05 GEMMs (measured on 4x B200, 1F1B: middle-rank
+    backward 5.6 ms -> 4.2 ms, step 303 -> 270 ms with <= 2 channels and 4 SMs left free).  User-set values win."""
+    import os
+    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", "2")
+    os.environ.setdefault("NCCL_MIN_P2P_NCHANNELS", "1")
+    os.environ.setdefault("PPB_RESERVED_SMS", "4")
+
+
 def rank_of(dp: int, pp: int, tp: int, pp_size: int, tp_size: int) -> int:
     return (dp * pp_size + pp) * tp_size + tp
 

@@ -24,6 +24,8 @@ int ppb_version(void);
 /* Optional device pointer to a 64-bit value that every dropout-using kernel adds to its seed at run time (per
  * device; NULL disables).  Lets CUDA graphs replay with fresh masks. */
 int ppb_set_dropout_offset_ptr(const unsigned long long* p);
+/* Leave `n` SMs free of persistent-kernel CTAs (for concurrently running NCCL P2P kernels); also $PPB_RESERVED_SMS. */
+int ppb_set_reserved_sms(int n);
 
 /* ---- K1/K2/K3: tcgen05 GEMM ------------------------------------------------------------------------------
  * C[M,N] (=|+=) epilogue(alpha * op(A)[M,K] * op(B)[N,K]^T)
