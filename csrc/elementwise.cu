@@ -129,6 +129,64 @@ __global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float* __restr
     y[i] = __float2bfloat16(x[i]);
 }
 
+// Residual branch without a norm (pre-LN blocks): z = resid + dropout(a); one pass, mask from (seed, flat index).
+__global__ void __launch_bounds__(256) add_dropout_fwd_kernel(const bf16* __restrict__ resid, const bf16* __restrict__ a,
+                                                              bf16* __restrict__ z, long long n8, unsigned long long seed,
+                                                              const unsigned long long* __restrict__ seed_off,
+                                                              unsigned int thresh, float scale) {
+  const unsigned long long seed_eff = seed + ((thresh && seed_off) ? *seed_off : 0ull);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 r4 = reinterpret_cast<const uint4*>(resid)[i];
+    const uint4 a4 = reinterpret_cast<const uint4*>(a)[i];
+    const uint32_t rw[4] = {r4.x, r4.y, r4.z, r4.w}, aw[4] = {a4.x, a4.y, a4.z, a4.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 r2 = unpack_bf16(rw[q]);
+      float2 a2 = unpack_bf16(aw[q]);
+      if (thresh) {
+        const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
+        a2.x = ((h & 0xFFFFu) >= thresh) ? a2.x * scale : 0.f;
+        a2.y = ((h >> 16) >= thresh) ? a2.y * scale : 0.f;
+      }
+      o[q] = pack_bf16(r2.x + a2.x, r2.y + a2.y);
+    }
+    reinterpret_cast<uint4*>(z)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// Backward of the above with gradient fan-in: dz = dy0 (+ dy1 + dy2); da = dropout'(dz).
+__global__ void __launch_bounds__(256) sum_dropout_bwd_kernel(const bf16* __restrict__ dy0, const bf16* __restrict__ dy1,
+                                                              const bf16* __restrict__ dy2, bf16* __restrict__ dz,
+                                                              bf16* __restrict__ da, long long n8, unsigned long long seed,
+                                                              const unsigned long long* __restrict__ seed_off,
+                                                              unsigned int thresh, float scale) {
+  const unsigned long long seed_eff = seed + ((thresh && seed_off) ? *seed_off : 0ull);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    const uint4 x = reinterpret_cast<const uint4*>(dy0)[i];
+    uint4 y = make_uint4(0, 0, 0, 0), w = make_uint4(0, 0, 0, 0);
+    if (dy1) y = reinterpret_cast<const uint4*>(dy1)[i];
+    if (dy2) w = reinterpret_cast<const uint4*>(dy2)[i];
+    const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, yw[4] = {y.x, y.y, y.z, y.w}, ww[4] = {w.x, w.y, w.z, w.w};
+    uint32_t oz[4], oa[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = unpack_bf16(xw[q]), g = unpack_bf16(yw[q]), h2 = unpack_bf16(ww[q]);
+      const float sx = f.x + g.x + h2.x, sy = f.y + g.y + h2.y;
+      oz[q] = pack_bf16(sx, sy);
+      float ax = sx, ay = sy;
+      if (thresh) {
+        const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
+        ax = ((h & 0xFFFFu) >= thresh) ? sx * scale : 0.f;
+        ay = ((h >> 16) >= thresh) ? sy * scale : 0.f;
+      }
+      oa[q] = pack_bf16(ax, ay);
+    }
+    reinterpret_cast<uint4*>(dz)[i] = make_uint4(oz[0], oz[1], oz[2], oz[3]);
+    if (da) reinterpret_cast<uint4*>(da)[i] = make_uint4(oa[0], oa[1], oa[2], oa[3]);
+  }
+}
+
 // dst_r[i] += src[i] * scale for every replica r (own + peers over NVLink): the all-reduce of the small, non-GEMM
 // gradients (biases, norm gains, embedding rows) in the same push style as the fused wgrad kernel.
 struct PushPtrs {
@@ -224,6 +282,30 @@ extern "C" int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_d
   PushPtrs d;
   for (int r = 0; r < 8; ++r) d.p[r] = reinterpret_cast<float*>(dst_ptrs[r < n_dst ? r : 0]);
   push_add_kernel<<<ew_grid(n / 4), 256, 0, stream>>>(src, d, n_dst, n / 4, scale);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+
+extern "C" int ppb_add_dropout_fwd(const void* resid, const void* a, void* z, long long n, float dropout_p,
+                                   unsigned long long seed, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_add_dropout_fwd: element count must be a multiple of 8");
+  const unsigned int th = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
+  add_dropout_fwd_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)resid, (const bf16*)a, (bf16*)z, n / 8, seed,
+                                                             seed_offset_ptr(), th, dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ppb_sum_dropout_bwd(const void* dy0, const void* dy1, const void* dy2, void* dz, void* da, long long n,
+                                   float dropout_p, unsigned long long seed, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_sum_dropout_bwd: element count must be a multiple of 8");
+  const unsigned int th = (da && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
+  sum_dropout_bwd_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)dy0, (const bf16*)dy1, (const bf16*)dy2, (bf16*)dz,
+                                                             (bf16*)da, n / 8, seed, seed_offset_ptr(), th,
+                                                             dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f);
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }

@@ -77,8 +77,6 @@ class _Norm(nn.Module):
 class DecoderLayer(nn.Module):
     def __init__(self, args: ModelArgs):
         super().__init__()
-        if args.norm_first:
-            raise NotImplementedError("pre-LN (GPT) block: explicit program not implemented yet; use the reference block")
         d, dt, rms = args.dim, args.dtype, args.norm == "rmsnorm"
         self.self_attn = _Attn(d, dt)
         if args.cross_attn:
@@ -132,8 +130,65 @@ class Ctx:
         return (site_seed(self.base_seed, layer_id, self.mb, site) + self.step_offset) & _MASK64
 
 
+def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Pre-LN (GPT-style) block:  x += drop(attn(LN1(x)));  x += drop(ffn(LN3(x)))   -- causal self-attention only."""
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
+    qkv = F.linear_fwd(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    o1, lse1 = F.attention_fwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], ctx.B, H, a.causal, None, p,
+                               ctx.seed(layer_id, SITE_ATTN1))
+    a1 = F.linear_fwd(o1, L.self_attn.out_proj.weight, L.self_attn.out_proj.bias)
+    # residual add + dropout fused with the NEXT norm: z3 is the updated residual stream, y3 = LN3(z3)
+    z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, p,
+                                                  ctx.seed(layer_id, SITE_RES1), rms)
+    if a.activation == "relu":
+        h = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
+        st["h"] = h
+    else:
+        hpre = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias)
+        h = F.gelu_fwd(hpre)
+        st.update(hpre=hpre, h=h)
+    a3 = F.linear_fwd(h, L.linear2.weight, L.linear2.bias)
+    x_out = F.add_dropout_fwd(z3, a3, p, ctx.seed(layer_id, SITE_RES3))
+    st.update(x_in=x_in, y1=y1, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1, z3=z3, y3=y3, mean3=mean3, rstd3=rstd3)
+    return x_out
+
+
+def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], ctx: Ctx, st: dict,
+                      G: "GradSink") -> List[torch.Tensor]:
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms = a.norm == "rmsnorm"
+    ar = getattr(G, "fused_ar", None)
+    g, da3 = F.sum_dropout_bwd(dys, p, ctx.seed(layer_id, SITE_RES3))          # d x_out, and through the FFN dropout
+    F.linear_wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias), ar=ar)
+    if a.activation == "relu":
+        dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
+    else:
+        dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
+    F.linear_wgrad(dh, st["y3"], G(L.linear1.weight), G(L.linear1.bias), ar=ar)
+    dy3 = F.linear_dgrad(dh, L.linear1.weight)
+    dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
+                           0.0, 0, rms, need_da=False)
+    total, da1 = F.sum_dropout_bwd([g, dz3_ln], p, ctx.seed(layer_id, SITE_RES1))  # d z3 = residual + through LN3
+    F.linear_wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias), ar=ar)
+    do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
+    qkv = st["qkv"]
+    dqkv = torch.empty_like(qkv)
+    F.attention_bwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], st["o1"], do1, st["lse1"], ctx.B, H, a.causal, None, p,
+                    ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
+    F.linear_wgrad(dqkv, st["y1"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias), ar=ar)
+    dy1 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
+    dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
+                          0.0, 0, rms, need_da=False)
+    return [total, dx_ln]
+
+
 def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
-    """Post-LN decoder layer forward on [T, d] tokens.  Fills the stash ``st`` and returns x3."""
+    """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
+    ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
+    if ctx.args.norm_first:
+        return _prenorm_forward(L, layer_id, x0, ctx, st)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     st["x0"] = x0
@@ -175,6 +230,8 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
                    G: GradSink) -> List[torch.Tensor]:
     """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. x3 (summed on load by the norm
     kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. x0."""
+    if ctx.args.norm_first:
+        return _prenorm_backward(L, layer_id, dys, ctx, st, G)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms = a.norm == "rmsnorm"
     x0 = st["x0"]

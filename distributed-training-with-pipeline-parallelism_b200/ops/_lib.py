@@ -41,6 +41,8 @@ def _declare(lib) -> None:
         "ppb_colsum_accum": [P, L, P, I, I, P],
         "ppb_add_n_bf16": [P, P, P, P, L, P],
         "ppb_gelu_fwd": [P, P, L, P],
+        "ppb_add_dropout_fwd": [P, P, P, L, F, U, P],
+        "ppb_sum_dropout_bwd": [P, P, P, P, P, L, F, U, P],
         "ppb_cast_f32_to_bf16": [P, P, L, P],
         "ppb_attn_fwd": [P, P, P, P, P, I, I, I, I, I, L, L, L, L, I, I, I, F, F, U, P],
         "ppb_attn_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, L, L, L, L, I, I, I, F, F, U, P],

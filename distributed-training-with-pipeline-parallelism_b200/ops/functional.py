@@ -350,6 +350,37 @@ def add_n(ts: Sequence[Optional[torch.Tensor]], out: Optional[torch.Tensor] = No
     return out
 
 
+def add_dropout_fwd(resid: torch.Tensor, a: torch.Tensor, dropout_p: float = 0.0, seed: int = 0) -> torch.Tensor:
+    """z = resid + dropout(a) (no norm; the residual branch of pre-LN blocks)."""
+    if not _is_cuda(resid):
+        return (resid.float() + (ref.dropout(a.float(), dropout_p, seed) if dropout_p > 0 else a.float())).to(resid.dtype)
+    lib = _lib_required()
+    z = torch.empty_like(resid)
+    _lib.check(lib.ppb_add_dropout_fwd(resid.data_ptr(), a.data_ptr(), z.data_ptr(), z.numel(), float(dropout_p),
+                                       int(seed) & (2**64 - 1), _stream()), "ppb_add_dropout_fwd")
+    _lib.count_launch()
+    return z
+
+
+def sum_dropout_bwd(dys: Sequence[Optional[torch.Tensor]], dropout_p: float = 0.0, seed: int = 0, need_da: bool = True):
+    """dz = sum(dys) (up to three); da = dropout'(dz).  Returns (dz, da) -- da is dz itself without dropout."""
+    dys = [d for d in dys if d is not None]
+    if not _is_cuda(dys[0]):
+        dz = ref.add_n(dys)
+        da = ref.dropout(dz.float(), dropout_p, seed).to(dz.dtype) if (need_da and dropout_p > 0) else dz
+        return dz, da
+    lib = _lib_required()
+    if len(dys) == 1 and not (need_da and dropout_p > 0):
+        return dys[0], dys[0]
+    dz = torch.empty_like(dys[0])
+    da = torch.empty_like(dys[0]) if (need_da and dropout_p > 0) else None
+    dys = dys + [None] * (3 - len(dys))
+    _lib.check(lib.ppb_sum_dropout_bwd(dys[0].data_ptr(), _lib.ptr(dys[1]), _lib.ptr(dys[2]), dz.data_ptr(), _lib.ptr(da),
+                                       dz.numel(), float(dropout_p), int(seed) & (2**64 - 1), _stream()), "ppb_sum_dropout_bwd")
+    _lib.count_launch()
+    return dz, (da if da is not None else dz)
+
+
 def gelu_fwd(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     if not _is_cuda(x):
         y = torch.nn.functional.gelu(x.float()).to(x.dtype)

@@ -125,6 +125,12 @@ int ppb_embedding_bwd(const long long* idx, const void* dy0, const void* dy1, co
 int ppb_colsum_accum(const void* dy, long long ld, float* db, int T, int N, void* stream);
 int ppb_add_n_bf16(const void* a, const void* b, const void* c, void* out, long long n, void* stream);
 int ppb_gelu_fwd(const void* x, void* y, long long n, void* stream);
+/* residual branch without a norm (pre-LN / GPT blocks): z = resid + dropout(a), and its backward with gradient
+ * fan-in: dz = dy0(+dy1+dy2), da = dropout'(dz) (da may be NULL).  Replaces aten.add + dropout of pre-LN layers. */
+int ppb_add_dropout_fwd(const void* resid, const void* a, void* z, long long n, float dropout_p, unsigned long long seed,
+                        void* stream);
+int ppb_sum_dropout_bwd(const void* dy0, const void* dy1, const void* dy2, void* dz, void* da, long long n,
+                        float dropout_p, unsigned long long seed, void* stream);
 int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 
 #ifdef __cplusplus

@@ -93,3 +93,51 @@ def test_dropout_is_deterministic_and_active():
     m.eval()
     d1, d2 = m(x), m(x)
     assert torch.equal(d1, d2)
+
+
+@pytest.mark.parametrize("act", ["gelu", "relu"])
+def test_prenorm_gpt_block_matches_torch_encoder_layer(act):
+    """The pre-LN (GPT-style, causal, no cross-attention) block against nn.TransformerEncoderLayer(norm_first=True)."""
+    torch.manual_seed(3)
+    d, H, f, V, S = 64, 4, 128, 97, 16
+    args = ModelArgs(dim=d, n_layers=2, n_heads=H, vocab_size=V, ffn_dim=f, dropout=0.0, causal=True, cross_attn=False,
+                     activation=act, norm_first=True)
+    m = Transformer(args)
+    layers = [torch.nn.TransformerEncoderLayer(d, H, dim_feedforward=f, dropout=0.0, activation=act, batch_first=True,
+                                               norm_first=True) for _ in range(2)]
+    for i, tl in enumerate(layers):
+        ml = m.layers[str(i)]
+        tl.self_attn.in_proj_weight.data.copy_(ml.self_attn.in_proj_weight.data)
+        tl.self_attn.in_proj_bias.data.copy_(ml.self_attn.in_proj_bias.data)
+        tl.self_attn.out_proj.weight.data.copy_(ml.self_attn.out_proj.weight.data)
+        tl.self_attn.out_proj.bias.data.copy_(ml.self_attn.out_proj.bias.data)
+        tl.linear1.weight.data.copy_(ml.linear1.weight.data)
+        tl.linear1.bias.data.copy_(ml.linear1.bias.data)
+        tl.linear2.weight.data.copy_(ml.linear2.weight.data)
+        tl.linear2.bias.data.copy_(ml.linear2.bias.data)
+        ml.norm1.weight.data.uniform_(0.5, 1.5)
+        ml.norm3.weight.data.uniform_(0.5, 1.5)
+        tl.norm1.weight.data.copy_(ml.norm1.weight.data)
+        tl.norm2.weight.data.copy_(ml.norm3.weight.data)
+    x = torch.randint(0, V, (2, S))
+    y = torch.randint(0, V, (2, S))
+    mask = torch.nn.Transformer.generate_square_subsequent_mask(S)
+    h = torch.nn.functional.embedding(x, m.tok_embeddings.weight)
+    for tl in layers:
+        h = tl(h, src_mask=mask, is_causal=True)
+    h = torch.nn.functional.layer_norm(h, (d,), m.norm.weight, m.norm.bias)
+    want = torch.nn.functional.linear(h, m.output.weight, m.output.bias)
+    got = m(x)
+    assert torch.allclose(want, got, atol=3e-5, rtol=1e-4), (want - got).abs().max()
+    ce = torch.nn.CrossEntropyLoss()
+    ce(got.reshape(-1, V), y.reshape(-1)).backward()
+    gm = {n: p.grad.clone() for n, p in m.named_parameters()}
+    m.zero_grad()
+    ce(want.reshape(-1, V), y.reshape(-1)).backward()   # same parameters feed the torch graph for embedding/norm/head
+    assert torch.allclose(gm["output.weight"], m.output.weight.grad, atol=3e-5, rtol=1e-3)
+    assert torch.allclose(gm["tok_embeddings.weight"], m.tok_embeddings.weight.grad, atol=3e-5, rtol=1e-3)
+    for i, tl in enumerate(layers):
+        for mine, theirs in [(f"layers.{i}.self_attn.in_proj_weight", tl.self_attn.in_proj_weight),
+                             (f"layers.{i}.linear1.weight", tl.linear1.weight), (f"layers.{i}.linear2.bias", tl.linear2.bias),
+                             (f"layers.{i}.norm1.weight", tl.norm1.weight), (f"layers.{i}.norm3.bias", tl.norm2.bias)]:
+            assert torch.allclose(gm[mine], theirs.grad, atol=3e-5, rtol=1e-3), mine

@@ -88,3 +88,21 @@ def test_cuda_graph_path_matches_eager():
     assert max(abs(a - b) for a, b in zip(res[False][0], res[True][0])) < 1e-4, (res[False][0], res[True][0])
     rel = ((res[False][1] - res[True][1]).norm() / res[False][1].norm()).item()
     assert rel < 1e-5, rel
+
+
+@pytest.mark.parametrize("act,dropout", [("gelu", 0.0), ("relu", 0.1)])
+def test_prenorm_gpt_block_cuda_matches_cpu(act, dropout):
+    torch.manual_seed(4)
+    args = ModelArgs(dim=512, n_layers=2, n_heads=8, vocab_size=1000, ffn_dim=1024, dropout=dropout, causal=True,
+                     cross_attn=False, activation=act, norm_first=True)
+    full = Transformer(args)
+    x = torch.randint(0, 1000, (8, 128))
+    y = torch.randint(0, 1000, (8, 128))
+    st_c, loss_c = _run("cpu", full, x, y, 4)
+    st_g, loss_g = _run("cuda", full, x, y, 4)
+    assert abs(loss_c[0] - loss_g[0]) < 3e-2 * abs(loss_c[0]), (loss_c, loss_g)
+    gc, gg = st_c.grad_views(), st_g.grad_views()
+    for n in gc:
+        a, b = gc[n].float(), gg[n].float().cpu()
+        rel = ((a - b).norm() / (a.norm() + 1e-6)).item()
+        assert rel < 0.12, (n, rel)
