@@ -234,8 +234,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const uint32_t dst_row = stg_smem + chunk * Cfg::CHUNK + row * 128;
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((q ^ (row & 7)) << 4)), "r"(r[4 * q]),
-                       "r"(r[4 * q + 1]), "r"(r[4 * q + 2]), "r"(r[4 * q + 3])
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((q ^ (row & 7)) << 4)),
+                       "r"(__float_as_uint(__uint_as_float(r[4 * q]) * p.scale)),
+                       "r"(__float_as_uint(__uint_as_float(r[4 * q + 1]) * p.scale)),
+                       "r"(__float_as_uint(__uint_as_float(r[4 * q + 2]) * p.scale)),
+                       "r"(__float_as_uint(__uint_as_float(r[4 * q + 3]) * p.scale))
                        : "memory");
         }
       }
@@ -293,17 +296,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const bool nw = dstr.nowrap(16);
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            const uint32_t hsh = nw ? dstr.bits_nowrap(i >> 1) : dstr.bits(i >> 1);
-            const float k0 = ((hsh & 0xFFFFu) >= p.drop_thresh) ? p.drop_scale : 0.f;
-            const float k1 = ((hsh >> 16) >= p.drop_thresh) ? p.drop_scale : 0.f;
-            dsv[i] = pv[i] * (dsv[i] * k0 - dlt) * p.scale;
-            dsv[i + 1] = pv[i + 1] * (dsv[i + 1] * k1 - dlt) * p.scale;
+            const DropPair hsh = nw ? dstr.bits_nowrap(i >> 1) : dstr.bits(i >> 1);
+            const float k0 = (hsh.a >= p.drop_thresh) ? p.drop_scale : 0.f;
+            const float k1 = (hsh.b >= p.drop_thresh) ? p.drop_scale : 0.f;
+            dsv[i] = pv[i] * fmaf(dsv[i], k0, -dlt);        // softmax scale is applied when dQ / dK leave TMEM
+            dsv[i + 1] = pv[i + 1] * fmaf(dsv[i + 1], k1, -dlt);
             pv[i] *= k0;
             pv[i + 1] *= k1;
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) dsv[i] = pv[i] * (dsv[i] - dlt) * p.scale;
+          for (int i = 0; i < 32; ++i) dsv[i] = pv[i] * (dsv[i] - dlt);
         }
         const uint32_t prow = pd_smem + hf * Cfg::CHUNK + row * 128;
         const uint32_t drow = ds_smem + hf * Cfg::CHUNK + row * 128;
@@ -334,7 +337,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tc_fence_after();
     if (warp == 0 && lane == 0) tma_wait_group_read<0>();
     named_bar_sync(1, 256);
-    auto stage_out = [&](uint32_t tcol, int ncols, uint32_t dst_base) {
+    auto stage_out = [&](uint32_t tcol, int ncols, uint32_t dst_base, float sc) {
       // this thread owns columns [hf*ncols/2, (hf+1)*ncols/2) of its kv row
       const int per = ncols / 2;
 #pragma unroll
@@ -347,16 +350,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const int col = hf * per + c * 32 + g * 8;
           const uint32_t dst = dst_base + (col >> 6) * Cfg::CHUNK + row * 128 + (((uint32_t)((col & 63) >> 3) ^ (row & 7)) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst),
-                       "r"(pack_bf16(__uint_as_float(r[8 * g]), __uint_as_float(r[8 * g + 1]))),
-                       "r"(pack_bf16(__uint_as_float(r[8 * g + 2]), __uint_as_float(r[8 * g + 3]))),
-                       "r"(pack_bf16(__uint_as_float(r[8 * g + 4]), __uint_as_float(r[8 * g + 5]))),
-                       "r"(pack_bf16(__uint_as_float(r[8 * g + 6]), __uint_as_float(r[8 * g + 7])))
+                       "r"(pack_bf16(__uint_as_float(r[8 * g]) * sc, __uint_as_float(r[8 * g + 1]) * sc)),
+                       "r"(pack_bf16(__uint_as_float(r[8 * g + 2]) * sc, __uint_as_float(r[8 * g + 3]) * sc)),
+                       "r"(pack_bf16(__uint_as_float(r[8 * g + 4]) * sc, __uint_as_float(r[8 * g + 5]) * sc)),
+                       "r"(pack_bf16(__uint_as_float(r[8 * g + 6]) * sc, __uint_as_float(r[8 * g + 7]) * sc))
                        : "memory");
         }
       }
     };
-    stage_out(Cfg::DV_COL, DV, pd_smem);
-    stage_out(Cfg::DK_COL, DQK, ds_smem);
+    stage_out(Cfg::DV_COL, DV, pd_smem, 1.f);
+    stage_out(Cfg::DK_COL, DQK, ds_smem, p.scale);
     fence_proxy_async_smem();
     named_bar_sync(1, 256);
     if (warp == 0 && lane == 0) {
@@ -497,7 +500,7 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   p.sl2 = scale * 1.4426950408889634f;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
-  p.drop_thresh = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
+  p.drop_thresh = dropout_p > 0.f ? dropout_thr32(dropout_p) : 0u;
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;
   p.delta = delta;

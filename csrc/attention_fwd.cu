@@ -282,16 +282,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           if (ds.nowrap(16)) {
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
-              const uint32_t hsh = ds.bits_nowrap(i >> 1);
-              pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
-              pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
+              const DropPair hsh = ds.bits_nowrap(i >> 1);
+              pr[i] = (hsh.a >= p.drop_thresh) ? pr[i] : 0.f;
+              pr[i + 1] = (hsh.b >= p.drop_thresh) ? pr[i + 1] : 0.f;
             }
           } else {
 #pragma unroll
             for (int i = 0; i < 32; i += 2) {
-              const uint32_t hsh = ds.bits(i >> 1);
-              pr[i] = ((hsh & 0xFFFFu) >= p.drop_thresh) ? pr[i] : 0.f;
-              pr[i + 1] = ((hsh >> 16) >= p.drop_thresh) ? pr[i + 1] : 0.f;
+              const DropPair hsh = ds.bits(i >> 1);
+              pr[i] = (hsh.a >= p.drop_thresh) ? pr[i] : 0.f;
+              pr[i + 1] = (hsh.b >= p.drop_thresh) ? pr[i + 1] : 0.f;
             }
           }
         }
@@ -405,7 +405,7 @@ extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o
   p.sl2 = scale * 1.4426950408889634f;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
-  p.drop_thresh = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
+  p.drop_thresh = dropout_p > 0.f ? dropout_thr32(dropout_p) : 0u;
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;
   const bool two = Sq > 128;

@@ -258,8 +258,7 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// Counter-based dropout RNG.  One 32-bit hash per PAIR of elements (16 random bits each); the keep
-// decision for element e is  bits16(e) >= thresh16  with thresh16 = round(p * 65536).  Stateless:
+// Counter-based dropout RNG.  Stateless:
 // forward and backward regenerate identical masks from (seed, element index), nothing is stored.
 // The python reference in ops/reference.py implements the same integer function bit-for-bit.
 // ---------------------------------------------------------------------------------------------
@@ -271,14 +270,28 @@ __host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   x ^= x >> 16;
   return x;
 }
-// hash for the pair index (element index / 2); idx may exceed 2^32 elements -> fold the high word in
-__host__ __device__ __forceinline__ uint32_t dropout_pair_bits(uint64_t seed, uint64_t pair_idx) {
+// One hash per PAIR of elements.  The pair index is folded with the seed (the high word goes through a full mix32,
+// which callers hoist out of inner loops), scrambled with a multiply-xorshift round, and two different odd
+// multipliers produce one 32-bit word per element; element e of the pair is kept iff its word >= thr32, where
+// thr32 = round(p * 65536) << 16 (the decision only looks at the top 16 bits, i.e. a 2^-16 resolution of p).
+struct DropPair {
+  uint32_t a, b;  // word for the even / odd element of the pair
+};
+__host__ __device__ __forceinline__ DropPair drop_pair_from(uint32_t x) {
+  x *= 0x9E3779B1U;
+  x ^= x >> 15;
+  DropPair r;
+  r.a = x * 0x85EBCA77U;
+  r.b = x * 0xC2B2AE3DU;
+  return r;
+}
+__host__ __device__ __forceinline__ DropPair dropout_pair_bits(uint64_t seed, uint64_t pair_idx) {
   uint32_t lo = uint32_t(pair_idx), hi = uint32_t(pair_idx >> 32);
   uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
-  return mix32((lo ^ k0) + mix32(hi ^ k1 ^ 0x9e3779b9U));
+  return drop_pair_from((lo ^ k0) + mix32(hi ^ k1 ^ 0x9e3779b9U));
 }
-// Fast path for runs of consecutive pair indices: the (expensive) mixing of the high word is hoisted out of the
-// inner loop.  bits(i) == dropout_pair_bits(seed, pair0 + i) for every i < 2^32, including across a low-word wrap.
+// Fast path for runs of consecutive pair indices: the mixing of the high word is hoisted out of the inner loop.
+// bits(i) == dropout_pair_bits(seed, pair0 + i) for every i < 2^32, including across a low-word wrap.
 struct DropoutStream {
   uint32_t k0, lo0, inner, inner_next;
   __device__ __forceinline__ DropoutStream(uint64_t seed, uint64_t pair0) {
@@ -288,24 +301,24 @@ struct DropoutStream {
     inner = mix32(hi ^ k1 ^ 0x9e3779b9U);
     inner_next = mix32((hi + 1u) ^ k1 ^ 0x9e3779b9U);
   }
-  __device__ __forceinline__ uint32_t bits(uint32_t i) const {
+  __device__ __forceinline__ DropPair bits(uint32_t i) const {
     const uint32_t lo = lo0 + i;
-    return mix32((lo ^ k0) + (lo < lo0 ? inner_next : inner));
+    return drop_pair_from((lo ^ k0) + (lo < lo0 ? inner_next : inner));
   }
   // true when indices [0, n) stay inside one value of the high word, so bits_nowrap() may be used
   __device__ __forceinline__ bool nowrap(uint32_t n) const { return lo0 + (n - 1u) >= lo0; }
-  __device__ __forceinline__ uint32_t bits_nowrap(uint32_t i) const { return mix32(((lo0 + i) ^ k0) + inner); }
+  __device__ __forceinline__ DropPair bits_nowrap(uint32_t i) const { return drop_pair_from(((lo0 + i) ^ k0) + inner); }
 };
 
 __host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
   float t = p * 65536.0f + 0.5f;
   return t <= 0.f ? 0u : (t >= 65535.f ? 65535u : uint32_t(t));
 }
+__host__ __device__ __forceinline__ uint32_t dropout_thr32(float p) { return dropout_thresh16(p) << 16; }
 // keep flag of element idx (idx even/odd selects low/high half of the pair hash)
-__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, uint32_t thresh16) {
-  uint32_t h = dropout_pair_bits(seed, idx >> 1);
-  uint32_t b = (idx & 1) ? (h >> 16) : (h & 0xFFFFu);
-  return b >= thresh16;
+__host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, uint32_t thr32) {
+  const DropPair h = dropout_pair_bits(seed, idx >> 1);
+  return ((idx & 1) ? h.b : h.a) >= thr32;
 }
 
 }  // namespace ppb

@@ -145,9 +145,9 @@ __global__ void __launch_bounds__(256) add_dropout_fwd_kernel(const bf16* __rest
       const float2 r2 = unpack_bf16(rw[q]);
       float2 a2 = unpack_bf16(aw[q]);
       if (thresh) {
-        const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
-        a2.x = ((h & 0xFFFFu) >= thresh) ? a2.x * scale : 0.f;
-        a2.y = ((h >> 16) >= thresh) ? a2.y * scale : 0.f;
+        const DropPair h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
+        a2.x = (h.a >= thresh) ? a2.x * scale : 0.f;
+        a2.y = (h.b >= thresh) ? a2.y * scale : 0.f;
       }
       o[q] = pack_bf16(r2.x + a2.x, r2.y + a2.y);
     }
@@ -176,9 +176,9 @@ __global__ void __launch_bounds__(256) sum_dropout_bwd_kernel(const bf16* __rest
       oz[q] = pack_bf16(sx, sy);
       float ax = sx, ay = sy;
       if (thresh) {
-        const uint32_t h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
-        ax = ((h & 0xFFFFu) >= thresh) ? sx * scale : 0.f;
-        ay = ((h >> 16) >= thresh) ? sy * scale : 0.f;
+        const DropPair h = dropout_pair_bits(seed_eff, (unsigned long long)i * 4 + q);
+        ax = (h.a >= thresh) ? sx * scale : 0.f;
+        ay = (h.b >= thresh) ? sy * scale : 0.f;
       }
       oa[q] = pack_bf16(ax, ay);
     }
@@ -291,7 +291,7 @@ extern "C" int ppb_add_dropout_fwd(const void* resid, const void* a, void* z, lo
                                    unsigned long long seed, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_add_dropout_fwd: element count must be a multiple of 8");
-  const unsigned int th = dropout_p > 0.f ? dropout_thresh16(dropout_p) : 0u;
+  const unsigned int th = dropout_p > 0.f ? dropout_thr32(dropout_p) : 0u;
   add_dropout_fwd_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)resid, (const bf16*)a, (bf16*)z, n / 8, seed,
                                                              seed_offset_ptr(), th, dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f);
   PPB_CUDA_OK(cudaGetLastError());
@@ -302,7 +302,7 @@ extern "C" int ppb_sum_dropout_bwd(const void* dy0, const void* dy1, const void*
                                    float dropout_p, unsigned long long seed, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(n > 0 && (n % 8) == 0, "ppb_sum_dropout_bwd: element count must be a multiple of 8");
-  const unsigned int th = (da && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
+  const unsigned int th = (da && dropout_p > 0.f) ? dropout_thr32(dropout_p) : 0u;
   sum_dropout_bwd_kernel<<<ew_grid(n / 8), 256, 0, stream>>>((const bf16*)dy0, (const bf16*)dy1, (const bf16*)dy2, (bf16*)dz,
                                                              (bf16*)da, n / 8, seed, seed_offset_ptr(), th,
                                                              dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f);

@@ -247,9 +247,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             const DropoutStream ds(seed_eff, ((unsigned long long)row * (unsigned long long)p.N + nc) >> 1);
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 2) {
-              const uint32_t h = ds.bits(j >> 1);
-              v[j] = ((h & 0xFFFFu) >= p.drop_thresh) ? v[j] * p.drop_scale : 0.f;
-              v[j + 1] = ((h >> 16) >= p.drop_thresh) ? v[j + 1] * p.drop_scale : 0.f;
+              const DropPair h = ds.bits(j >> 1);
+              v[j] = (h.a >= p.drop_thresh) ? v[j] * p.drop_scale : 0.f;
+              v[j + 1] = (h.b >= p.drop_thresh) ? v[j + 1] * p.drop_scale : 0.f;
             }
           }
         } else if (p.epi == PPB_EPI_MASK_POS || p.epi == PPB_EPI_GELU_BWD) {
@@ -546,7 +546,7 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.ag_rows_per_rank = 0;
   p.ag_rank = 0;
   p.rs_rows_per_rank = 0;
-  p.drop_thresh = dropout_thresh16(dropout_p);
+  p.drop_thresh = dropout_thr32(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
   const int grid = (int)(total < sm_count() ? total : sm_count());

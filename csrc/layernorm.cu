@@ -65,9 +65,9 @@ __global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p)
           const float2 r2 = unpack_bf16(rw[q]);
           float2 a2 = unpack_bf16(aw[q]);
           if (p.thresh) {
-            const uint32_t h = dstr.bits(c * 4 + q);
-            a2.x = ((h & 0xFFFFu) >= p.thresh) ? a2.x * p.scale : 0.f;
-            a2.y = ((h >> 16) >= p.thresh) ? a2.y * p.scale : 0.f;
+            const DropPair h = dstr.bits(c * 4 + q);
+            a2.x = (h.a >= p.thresh) ? a2.x * p.scale : 0.f;
+            a2.y = (h.b >= p.thresh) ? a2.y * p.scale : 0.f;
           }
           zw[q] = pack_bf16(r2.x + a2.x, r2.y + a2.y);
           const float2 z2 = unpack_bf16(zw[q]);  // statistics are taken on the bf16-rounded z
@@ -209,9 +209,9 @@ __global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p)
           if (p.da) {
             float ax = gx, ay = gy;
             if (p.thresh) {
-              const uint32_t h = dstr.bits(c * 4 + q);
-              ax = ((h & 0xFFFFu) >= p.thresh) ? gx * p.scale : 0.f;
-              ay = ((h >> 16) >= p.thresh) ? gy * p.scale : 0.f;
+              const DropPair h = dstr.bits(c * 4 + q);
+              ax = (h.a >= p.thresh) ? gx * p.scale : 0.f;
+              ay = (h.b >= p.thresh) ? gy * p.scale : 0.f;
             }
             ao[q] = pack_bf16(ax, ay);
           }
@@ -305,7 +305,7 @@ extern "C" int ppb_add_dropout_norm_fwd(const void* resid, const void* a, const 
   p.eps = eps;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
-  p.thresh = (a && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
+  p.thresh = (a && dropout_p > 0.f) ? dropout_thr32(dropout_p) : 0u;
   p.scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.rms = rms;
   const int grid = ln_grid(T);
@@ -366,7 +366,7 @@ static void fill_ln_bwd_params(LnBwdParams& p, const void* dy0, const void* dy1,
   p.d = d;
   p.seed = seed;
   p.seed_off = seed_offset_ptr();
-  p.thresh = (da && dropout_p > 0.f) ? dropout_thresh16(dropout_p) : 0u;
+  p.thresh = (da && dropout_p > 0.f) ? dropout_thr32(dropout_p) : 0u;
   p.scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.rms = rms;
 }

@@ -30,16 +30,20 @@ def dropout_thresh16(p: float) -> int:
 
 
 def dropout_keep_mask(seed: int, start: int, numel: int, p: float, device=None) -> torch.Tensor:
-    """keep[i] for flat element indices start .. start+numel-1 (bool)."""
+    """keep[i] for flat element indices start .. start+numel-1 (bool); bit-identical to ppb::dropout_keep."""
     thresh = dropout_thresh16(p)
     idx = torch.arange(start, start + numel, dtype=torch.int64, device=device)
     pair = idx >> 1
     lo, hi = pair & _M32, (pair >> 32) & _M32
     k0, k1 = seed & _M32, (seed >> 32) & _M32
     inner = _mix32(hi ^ ((k1 ^ 0x9E3779B9) & _M32))
-    h = _mix32(((lo ^ k0) + inner) & _M32)
-    bits = torch.where((idx & 1) == 1, h >> 16, h & 0xFFFF)
-    return bits >= thresh
+    x = ((lo ^ k0) + inner) & _M32
+    x = (x * 0x9E3779B1) & _M32
+    x = x ^ (x >> 15)
+    a = (x * 0x85EBCA77) & _M32
+    b = (x * 0xC2B2AE3D) & _M32
+    word = torch.where((idx & 1) == 1, b, a)
+    return (word >> 16) >= thresh
 
 
 def dropout(x: torch.Tensor, p: float, seed: int, index_offset: int = 0) -> torch.Tensor:
