@@ -440,13 +440,19 @@ static int launch_attn_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const C
   return 0;
 }
 
+int attn_bwd_generic(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse,
+                     void* dq, void* dk, void* dv, void* scratch, int B, int H, int Sq, int Skv, int dh, long long ldq,
+                     long long ldk, long long ldv, long long ldo, int causal, float scale, float dropout_p,
+                     unsigned long long seed, cudaStream_t stream);
+
 }  // namespace ppb
 
 using namespace ppb;
 
-extern "C" long long ppb_attn_bwd_scratch_bytes(int B, int H, int Sq, int dh) {
-  const long long delta = ((long long)B * H * Sq * 4 + 255) / 256 * 256;
-  return delta + (long long)B * Sq * H * dh * 4 + 256;
+// `S` = max(Sq, Skv).  tcgen05 path: delta + fp32 dQ accumulator; generic path (dh > 128): fp32 dK and dV accumulators.
+extern "C" long long ppb_attn_bwd_scratch_bytes(int B, int H, int S, int dh) {
+  const long long delta = ((long long)B * H * S * 4 + 255) / 256 * 256;
+  return delta + (long long)B * S * H * dh * 4 * (dh > 128 ? 2 : 1) + 256;
 }
 
 extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO,
@@ -459,11 +465,14 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   (void)reserved1;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(B > 0 && H > 0 && Sq > 0 && Skv > 0, "ppb_attn_bwd: empty problem");
-  PPB_REQUIRE(dh % 8 == 0 && dh >= 8 && dh <= 128, "ppb_attn_bwd: head dim must be a multiple of 8 in [8, 128] (got %d)", dh);
+  PPB_REQUIRE(dh % 8 == 0 && dh >= 8 && dh <= 256, "ppb_attn_bwd: head dim must be a multiple of 8 in [8, 256] (got %d)", dh);
   PPB_REQUIRE((ldq % 8) == 0 && (ldk % 8) == 0 && (ldv % 8) == 0 && (ldo % 8) == 0, "ppb_attn_bwd: row strides must be multiples of 8");
   PPB_REQUIRE(!causal || Skv >= Sq, "ppb_attn_bwd: causal attention needs Skv >= Sq");
   PPB_REQUIRE(dropout_p <= 0.f || (Skv % 2) == 0, "ppb_attn_bwd: dropout needs an even Skv");
   PPB_REQUIRE(scratch != nullptr && (reinterpret_cast<uintptr_t>(scratch) % 256) == 0, "ppb_attn_bwd: scratch must be 256-byte aligned");
+  if (dh > 128)
+    return attn_bwd_generic(q, k, v, o, dO, lse, dq, dk, dv, scratch, B, H, Sq, Skv, dh, ldq, ldk, ldv, ldo, causal, scale,
+                            dropout_p, seed, stream);
   float* delta = reinterpret_cast<float*>(scratch);
   const long long delta_bytes = ((long long)B * H * Sq * 4 + 255) / 256 * 256;
   float* dq_acc = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + delta_bytes);

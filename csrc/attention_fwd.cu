@@ -375,6 +375,10 @@ static int launch_attn_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const C
   return 0;
 }
 
+int attn_fwd_generic(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Skv,
+                     int dh, long long ldq, long long ldk, long long ldv, long long ldo, int causal, float scale,
+                     float dropout_p, unsigned long long seed, cudaStream_t stream);
+
 }  // namespace ppb
 
 using namespace ppb;
@@ -387,10 +391,12 @@ extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o
   (void)reserved1;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(B > 0 && H > 0 && Sq > 0 && Skv > 0, "ppb_attn_fwd: empty problem");
-  PPB_REQUIRE(dh % 8 == 0 && dh >= 8 && dh <= 128, "ppb_attn_fwd: head dim must be a multiple of 8 in [8, 128] (got %d)", dh);
+  PPB_REQUIRE(dh % 8 == 0 && dh >= 8 && dh <= 256, "ppb_attn_fwd: head dim must be a multiple of 8 in [8, 256] (got %d)", dh);
   PPB_REQUIRE((ldq % 8) == 0 && (ldk % 8) == 0 && (ldv % 8) == 0 && (ldo % 8) == 0, "ppb_attn_fwd: row strides must be multiples of 8");
   PPB_REQUIRE(!causal || Skv >= Sq, "ppb_attn_fwd: causal attention needs Skv >= Sq");
   PPB_REQUIRE(dropout_p <= 0.f || (Skv % 2) == 0, "ppb_attn_fwd: dropout needs an even Skv");
+  if (dh > 128)  // CUDA-core fallback (attention_generic.cu); the tcgen05 path covers head dims up to 128
+    return attn_fwd_generic(q, k, v, o, lse, B, H, Sq, Skv, dh, ldq, ldk, ldv, ldo, causal, scale, dropout_p, seed, stream);
   CUtensorMap tq, tk, tv, to;
   if (!make_head_tmap(&tq, q, dh, H, Sq, B, ldq, 128) || !make_head_tmap(&tk, k, dh, H, Skv, B, ldk, 128) ||
       !make_head_tmap(&tv, v, dh, H, Skv, B, ldv, 128) || !make_head_tmap(&to, o, dh, H, Sq, B, ldo, 128))

@@ -466,7 +466,7 @@ def attention_bwd(q, k, v, o, do, lse, B: int, H: int, causal: bool = False, sca
         dq, dk, dv = out
     if dq.stride(0) != q.stride(0) or dk.stride(0) != k.stride(0) or dv.stride(0) != v.stride(0) or do.stride(0) != o.stride(0):
         raise ValueError("attention_bwd: gradient buffers must share the row stride of their forward tensors")
-    scratch = _attn_scratch(q.device, B, H, Sq, dh)
+    scratch = _attn_scratch(q.device, B, H, max(Sq, Skv), dh)
     rc = lib.ppb_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), do.data_ptr(), lse.data_ptr(),
                           dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), scratch.data_ptr(), 0, B, H, Sq, Skv, dh,
                           q.stride(0), k.stride(0), v.stride(0), o.stride(0), int(causal), 0, 0, float(scale),

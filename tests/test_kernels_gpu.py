@@ -197,6 +197,9 @@ ATTN_CASES = [
     (2, 3, 200, 200, 64, False, 0.0),
     (2, 3, 136, 328, 64, False, 0.0),
     (1, 4, 128, 128, 32, False, 0.0),
+    (2, 4, 128, 128, 192, False, 0.1),   # the reference sweep's 4-head case (CUDA-core fallback path)
+    (1, 2, 96, 160, 192, False, 0.0),
+    (1, 2, 128, 128, 256, True, 0.0),
 ]
 
 

@@ -25,7 +25,7 @@ def _run(dev, full, x, y, m, dropout_seed=3, steps=1, opt=None):
     return st, hist
 
 
-@pytest.mark.parametrize("heads,dropout", [(6, 0.0), (8, 0.1), (12, 0.1)])
+@pytest.mark.parametrize("heads,dropout", [(4, 0.1), (6, 0.0), (8, 0.1), (12, 0.1)])
 def test_cuda_matches_cpu_reference(heads, dropout):
     torch.manual_seed(0)
     args = ModelArgs(dim=768, n_layers=2, n_heads=heads, vocab_size=1000, dropout=dropout)
