@@ -177,6 +177,7 @@ def run_ours(a, rank, local_rank, world):
     clocks = sampler.stop() if sampler is not None else None
     meas = sched.measured()
     bubble = max_over_ranks(meas.get("bubble_fraction", 0.0), dev)
+    bubble_min = -max_over_ranks(-meas.get("bubble_fraction", 0.0), dev)   # idle fraction of the busiest (critical) rank
     loss_val = None
     if last and losses:
         loss_val = float(torch.stack([l.reshape(()) for l in losses]).mean().item())
@@ -213,7 +214,8 @@ def run_ours(a, rank, local_rank, world):
                        "global_batch": a.global_batch, "seq_len": S, "n_microbatches": a.microbatches, "schedule": a.schedule,
                        "parallelism": par, "partition": a.partition, "optimizer": "fused AdamW (in timed region)",
                        "l2": "inputs >> L2: >2 GB of weights+activations touched per step per GPU, no explicit flush"},
-            "bubble_fraction_measured_max": bubble, "bubble_fraction_theory": sched.theory_bubble,
+            "bubble_fraction_measured_max": bubble, "bubble_fraction_critical_rank": bubble_min,
+            "bubble_fraction_theory": sched.theory_bubble,
             "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
             "model_tflops_per_gpu": margs.flops_per_token(S) * tokens / (ms_step / 1e3) / 1e12 / world,
             "per_rank": per_rank,
