@@ -275,6 +275,114 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __res
   }
 }
 
+// ---- wide rows (2048 < d <= 8192, e.g. Llama-width models): nothing is cached in registers --------------------
+// Kernel A: one warp per row, two sweeps over the row (the second one hits L2): dz / da only.
+__global__ void __launch_bounds__(LN_THREADS) ln_bwd_wide_rows_kernel(const LnBwdParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nchunks = p.d >> 3;
+  const float inv_d = 1.f / float(p.d);
+  const unsigned long long seed_eff = p.seed + ((p.thresh && p.seed_off) ? *p.seed_off : 0ull);
+  for (int row = blockIdx.x * LN_WARPS + warp; row < p.T; row += gridDim.x * LN_WARPS) {
+    const long long rbase = (long long)row * p.d;
+    const float mean = p.rms ? 0.f : p.mean[row];
+    const float rstd = p.rstd[row];
+    float c1 = 0.f, c2 = 0.f;
+    for (int c = lane; c < nchunks; c += 32) {
+      const bf16* z8 = p.z + rbase + c * 8;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float dy = __bfloat162float(p.dy0[rbase + c * 8 + j]);
+        if (p.dy1) dy += __bfloat162float(p.dy1[rbase + c * 8 + j]);
+        if (p.dy2) dy += __bfloat162float(p.dy2[rbase + c * 8 + j]);
+        const float g = dy * __bfloat162float(p.gamma[c * 8 + j]);
+        const float xh = (__bfloat162float(z8[j]) - mean) * rstd;
+        c1 += g;
+        c2 += g * xh;
+      }
+    }
+    c1 = p.rms ? 0.f : warp_sum(c1) * inv_d;
+    c2 = warp_sum(c2) * inv_d;
+    const DropoutStream dstr(seed_eff, (unsigned long long)rbase >> 1);
+    for (int c = lane; c < nchunks; c += 32) {
+      uint32_t zo[4], ao[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        float gx[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const long long i = rbase + c * 8 + 2 * q + e;
+          float dy = __bfloat162float(p.dy0[i]);
+          if (p.dy1) dy += __bfloat162float(p.dy1[i]);
+          if (p.dy2) dy += __bfloat162float(p.dy2[i]);
+          const float g = dy * __bfloat162float(p.gamma[c * 8 + 2 * q + e]);
+          const float xh = (__bfloat162float(p.z[i]) - mean) * rstd;
+          gx[e] = rstd * (g - c1 - xh * c2);
+        }
+        zo[q] = pack_bf16(gx[0], gx[1]);
+        float ax = gx[0], ay = gx[1];
+        if (p.da && p.thresh) {
+          const DropPair h = dstr.bits(c * 4 + q);
+          ax = (h.a >= p.thresh) ? gx[0] * p.scale : 0.f;
+          ay = (h.b >= p.thresh) ? gx[1] * p.scale : 0.f;
+        }
+        ao[q] = pack_bf16(ax, ay);
+      }
+      *reinterpret_cast<uint4*>(p.dz + rbase + c * 8) = make_uint4(zo[0], zo[1], zo[2], zo[3]);
+      if (p.da) *reinterpret_cast<uint4*>(p.da + rbase + c * 8) = make_uint4(ao[0], ao[1], ao[2], ao[3]);
+    }
+  }
+}
+
+// Kernel B: dgamma[c] += sum_t dy*xhat, dbeta[c] += sum_t dy.  Thread = (column pair, row lane); fp32 atomics.
+__global__ void __launch_bounds__(256) ln_bwd_wide_cols_kernel(const LnBwdParams p, int rows_per_cta) {
+  __shared__ float2 rg[8][32], rb[8][32];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cx) * 2;
+  const int r0 = blockIdx.y * rows_per_cta, r1 = min(p.T, r0 + rows_per_cta);
+  float2 ag = make_float2(0.f, 0.f), ab = make_float2(0.f, 0.f);
+  if (col < p.d) {
+    for (int r = r0 + ry; r < r1; r += 8) {
+      const long long i = (long long)r * p.d + col;
+      float2 dy = unpack_bf16(*reinterpret_cast<const uint32_t*>(p.dy0 + i));
+      if (p.dy1) {
+        const float2 e = unpack_bf16(*reinterpret_cast<const uint32_t*>(p.dy1 + i));
+        dy.x += e.x;
+        dy.y += e.y;
+      }
+      if (p.dy2) {
+        const float2 e = unpack_bf16(*reinterpret_cast<const uint32_t*>(p.dy2 + i));
+        dy.x += e.x;
+        dy.y += e.y;
+      }
+      const float2 z2 = unpack_bf16(*reinterpret_cast<const uint32_t*>(p.z + i));
+      const float mean = p.rms ? 0.f : p.mean[r], rstd = p.rstd[r];
+      ag.x += dy.x * (z2.x - mean) * rstd;
+      ag.y += dy.y * (z2.y - mean) * rstd;
+      ab.x += dy.x;
+      ab.y += dy.y;
+    }
+  }
+  rg[ry][cx] = ag;
+  rb[ry][cx] = ab;
+  __syncthreads();
+  if (ry == 0 && col < p.d) {
+    float2 sg = rg[0][cx], sb = rb[0][cx];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) {
+      sg.x += rg[i][cx].x;
+      sg.y += rg[i][cx].y;
+      sb.x += rb[i][cx].x;
+      sb.y += rb[i][cx].y;
+    }
+    atomicAdd(p.dgamma + col, sg.x);
+    atomicAdd(p.dgamma + col + 1, sg.y);
+    if (p.dbeta) {
+      atomicAdd(p.dbeta + col, sb.x);
+      atomicAdd(p.dbeta + col + 1, sb.y);
+    }
+  }
+}
+
 static int ln_grid(int T) {
   const int want = (T + LN_WARPS - 1) / LN_WARPS;
   const int cap = sm_count() * 2;
@@ -377,7 +485,20 @@ extern "C" int ppb_norm_bwd(const void* dy0, const void* dy1, const void* dy2, c
                             void* scratch, long long scratch_bytes, int T, int d, float dropout_p,
                             unsigned long long seed, int rms, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-  PPB_REQUIRE(T > 0 && d > 0 && (d % 8) == 0 && d <= 2048, "ppb_norm_bwd: need d %% 8 == 0 and d <= 2048 (got %d)", d);
+  PPB_REQUIRE(T > 0 && d > 0 && (d % 8) == 0 && d <= 8192, "ppb_norm_bwd: need d %% 8 == 0 and d <= 8192 (got %d)", d);
+  if (d > 2048) {  // wide rows: row pass + column pass, no scratch needed
+    LnBwdParams pw;
+    fill_ln_bwd_params(pw, dy0, dy1, dy2, z, mean, rstd, gamma, dz, da, dgamma, dbeta, nullptr, T, d, dropout_p, seed, rms);
+    ln_bwd_wide_rows_kernel<<<ln_grid(T), LN_THREADS, 0, stream>>>(pw);
+    const int col_blocks = (d + 63) / 64;
+    int slabs = (sm_count() * 4 + col_blocks - 1) / col_blocks;
+    if (slabs > (T + 63) / 64) slabs = (T + 63) / 64;
+    if (slabs < 1) slabs = 1;
+    const int rows_per = (T + slabs - 1) / slabs;
+    ln_bwd_wide_cols_kernel<<<dim3(col_blocks, (T + rows_per - 1) / rows_per), 256, 0, stream>>>(pw, rows_per);
+    PPB_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
   PPB_REQUIRE(scratch != nullptr && scratch_bytes >= ppb_norm_bwd_scratch_bytes(T, d),
               "ppb_norm_bwd: scratch too small (%lld bytes, need %lld); it must also be zero-initialised once",
               scratch_bytes, ppb_norm_bwd_scratch_bytes(T, d));

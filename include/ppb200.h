@@ -81,6 +81,7 @@ int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long lo
  * fwd: z = resid + dropout(a); y = norm(z)*gamma(+beta).  Either of resid / a may be NULL; z, mean may be NULL.
  * bwd: dy = dy0(+dy1+dy2); dz = norm'(dy); da = dropout'(dz) (da may be NULL); dgamma/dbeta are fp32 accum.
  * `scratch` needs ppb_norm_bwd_scratch_bytes() bytes, zero-filled once; concurrent launches must not share it.
+ * d <= 2048 keeps each row in registers; 2048 < d <= 8192 takes a row-pass + column-pass route (no scratch use).
  * Replaces aten.add + bernoulli_/div_/mul + native_layer_norm(_backward) -- torch transformer.py:1144-1153. */
 int ppb_add_dropout_norm_fwd(const void* resid, const void* a, const void* gamma, const void* beta, void* z, void* y,
                              float* mean, float* rstd, int T, int d, float eps, float dropout_p,

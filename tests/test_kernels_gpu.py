@@ -97,7 +97,7 @@ def test_wgrad_splitk(M, N, K, splits):
     assert rel_err(dw, 1 + dy.float().t() @ x.float()) < 5e-3
 
 
-@pytest.mark.parametrize("T,d", [(1024, 768), (4096, 1024), (333, 1600), (64, 256)])
+@pytest.mark.parametrize("T,d", [(1024, 768), (4096, 1024), (333, 1600), (64, 256), (512, 4096)])
 @pytest.mark.parametrize("p", [0.0, 0.1])
 @pytest.mark.parametrize("rms", [False, True])
 def test_add_dropout_norm(T, d, p, rms):
