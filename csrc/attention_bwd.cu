@@ -156,23 +156,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       constexpr uint32_t id_dv = make_idesc_bf16(128, DV, 1, 1);
       constexpr uint32_t id_dk = make_idesc_bf16(128, DQK, 1, 1);
       constexpr uint32_t id_dq = make_idesc_bf16(128, DQK, 0, 1);
-      mbar_wait(kv_full, 0);
-      for (int it = 0; it < n_it; ++it) {
+      auto issue_sdp = [&](int it) {   // S = Q K^T and dP = dO V^T of query tile `it`
         const int st = it % STAGES;
         const uint32_t qa = q_smem + st * Cfg::Q_BYTES;
         const uint32_t da = do_smem + st * Cfg::DO_BYTES;
-        mbar_wait(qdo_full(st), (it / STAGES) & 1);
-        mbar_wait(sdp_empty, (it & 1) ^ 1);                     // compute warps have consumed S/dP of tile it-1
-        if (Cfg::ALIAS_DQ) mbar_wait(dq_empty, (it & 1) ^ 1);   // dQ(it-1) shares the dP columns
-        tc_fence_after();
-        // S = Q K^T
 #pragma unroll
         for (int kk = 0; kk < DQK / 16; ++kk) {
           const uint32_t o = (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32;
           umma_f16_ss(tmem_base + Cfg::S_COL, make_smem_desc_sw128(qa + o, 16, 1024),
                       make_smem_desc_sw128(k_smem + o, 16, 1024), id_s, kk > 0 ? 1u : 0u);
         }
-        // dP = dO V^T
 #pragma unroll
         for (int kk = 0; kk < DV / 16; ++kk) {
           const uint32_t o = (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32;
@@ -180,30 +173,62 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                       make_smem_desc_sw128(v_smem + o, 16, 1024), id_s, kk > 0 ? 1u : 0u);
         }
         umma_commit(sdp_full);
-        mbar_wait(pds_full, it & 1);
-        if (!Cfg::ALIAS_DQ) mbar_wait(dq_empty, (it & 1) ^ 1);
-        tc_fence_after();
+      };
+      auto issue_grads = [&](int it) {  // dV += P^T dO, dK += dS^T Q, dQ = dS K of query tile `it`
+        const int st = it % STAGES;
+        const uint32_t qa = q_smem + st * Cfg::Q_BYTES;
+        const uint32_t da = do_smem + st * Cfg::DO_BYTES;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // K = 128 query rows
-          // dV += P^T dO      A: P tile MN-major (M = kv), B: dO tile MN-major (N = dv)
+        for (int kk = 0; kk < 8; ++kk) {  // K = 128 query rows; A: P tile MN-major (M = kv), B: dO tile MN-major (N = dv)
           umma_f16_ss(tmem_base + Cfg::DV_COL, make_smem_desc_sw128(pd_smem + kk * 2048, Cfg::CHUNK, 1024),
                       make_smem_desc_sw128(da + kk * 2048, Cfg::CHUNK, 1024), id_dv, (it > 0 || kk > 0) ? 1u : 0u);
         }
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          // dK += dS^T Q      A: dS tile MN-major, B: Q tile MN-major (N = dqk)
+        for (int kk = 0; kk < 8; ++kk) {  // A: dS tile MN-major, B: Q tile MN-major (N = dqk)
           umma_f16_ss(tmem_base + Cfg::DK_COL, make_smem_desc_sw128(ds_smem + kk * 2048, Cfg::CHUNK, 1024),
                       make_smem_desc_sw128(qa + kk * 2048, Cfg::CHUNK, 1024), id_dk, (it > 0 || kk > 0) ? 1u : 0u);
         }
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // K = 128 kv rows
-          // dQ = dS K         A: dS tile K-major (M = q), B: K tile MN-major (N = dqk)
+        for (int kk = 0; kk < 8; ++kk) {  // K = 128 kv rows; A: dS tile K-major (M = q), B: K tile MN-major (N = dqk)
           umma_f16_ss(tmem_base + Cfg::DQ_COL,
                       make_smem_desc_sw128(ds_smem + (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32, 16, 1024),
                       make_smem_desc_sw128(k_smem + kk * 2048, Cfg::CHUNK, 1024), id_dq, kk > 0 ? 1u : 0u);
         }
         umma_commit(dq_full);
         umma_commit(qdo_empty(st));
+      };
+      mbar_wait(kv_full, 0);
+      if constexpr (Cfg::ALIAS_DQ || STAGES < 2) {
+        // dQ shares the dP columns (wide heads): strictly alternate  [S,dP](it) -> compute -> [dV,dK,dQ](it)
+        for (int it = 0; it < n_it; ++it) {
+          mbar_wait(qdo_full(it % STAGES), (it / STAGES) & 1);
+          mbar_wait(sdp_empty, (it & 1) ^ 1);   // compute warps have consumed S/dP of tile it-1
+          mbar_wait(dq_empty, (it & 1) ^ 1);    // dQ(it-1) has left the columns it shares with dP
+          tc_fence_after();
+          issue_sdp(it);
+          mbar_wait(pds_full, it & 1);
+          tc_fence_after();
+          issue_grads(it);
+        }
+      } else {
+        // Software pipeline: the compute warps release S/dP as soon as they hold them in registers, so
+        // [S,dP](it+1) is issued while tile `it` is still in its exp/dropout phase, and [dV,dK,dQ](it) runs while
+        // the warps already work on tile it+1.  The tensor pipe never waits for the softmax math and vice versa.
+        mbar_wait(qdo_full(0), 0);
+        tc_fence_after();
+        issue_sdp(0);
+        for (int it = 0; it < n_it; ++it) {
+          if (it + 1 < n_it) {
+            mbar_wait(qdo_full((it + 1) % STAGES), ((it + 1) / STAGES) & 1);
+            mbar_wait(sdp_empty, it & 1);       // S/dP of tile `it` are in the compute warps' registers
+            tc_fence_after();
+            issue_sdp(it + 1);
+          }
+          mbar_wait(pds_full, it & 1);          // P / dS tiles of tile `it` are in shared memory
+          mbar_wait(dq_empty, (it & 1) ^ 1);    // dQ(it-1) drained from TMEM
+          tc_fence_after();
+          issue_grads(it);
+        }
       }
       umma_commit(fin_full);
     }
@@ -264,31 +289,38 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float lse2 = p.lse[lidx] * LOG2E;
       const float dlt = p.delta[lidx];
       const int causal_lim = q_idx + off;
-      if (it > 0) drain_dq(it - 1);
+      constexpr bool PIPELINED = !(Cfg::ALIAS_DQ || STAGES < 2);   // must match the MMA issuer's ordering
+      if (!PIPELINED && it > 0) drain_dq(it - 1);
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
       const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * p.Sq + (unsigned long long)min(q_idx, p.Sq - 1)) *
                                           (unsigned long long)p.Skv;
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {  // 2 x 32 columns of this thread's half
-        uint32_t rs[32], rd[32];
-        tmem_ld_x32(t_s + c * 32, rs);
-        tmem_ld_x32(t_dp + c * 32, rd);
-        tmem_ld_wait();
-        float pv[32], dsv[32];
+      // this thread's 64 columns of S and dP, pulled into registers in one go
+      uint32_t rs[64], rd[64];
+      tmem_ld_x32(t_s, rs);
+      tmem_ld_x32(t_s + 32, rs + 32);
+      tmem_ld_x32(t_dp, rd);
+      tmem_ld_x32(t_dp + 32, rd + 32);
+      tmem_ld_wait();
+      if (PIPELINED) {   // S/dP may be overwritten by the next tile's GEMMs while we do the math below
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(sdp_empty);
+      }
+      float* pv = reinterpret_cast<float*>(rs);    // P (then dropped-out P) in place of S
+      float* dsv = reinterpret_cast<float*>(rd);   // dS in place of dP
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
         const int kvb = kv0 + hf * 64 + c * 32;
         const bool need_mask = !row_ok || (kvb + 32 > p.Skv) || (p.causal && (kvb + 31 > causal_lim));
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          pv[i] = ex2f(fmaf(__uint_as_float(rs[i]), p.sl2, -lse2));
-          dsv[i] = __uint_as_float(rd[i]);
-        }
+        for (int i = 0; i < 32; ++i) pv[c * 32 + i] = ex2f(fmaf(pv[c * 32 + i], p.sl2, -lse2));
         if (need_mask) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
             const int kv = kvb + i;
             const bool ok = row_ok && (kv < p.Skv) && (!p.causal || kv <= causal_lim);
-            pv[i] = ok ? pv[i] : 0.f;
+            pv[c * 32 + i] = ok ? pv[c * 32 + i] : 0.f;
           }
         }
         if (p.drop_thresh) {
@@ -299,35 +331,39 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const DropPair hsh = nw ? dstr.bits_nowrap(i >> 1) : dstr.bits(i >> 1);
             const float k0 = (hsh.a >= p.drop_thresh) ? p.drop_scale : 0.f;
             const float k1 = (hsh.b >= p.drop_thresh) ? p.drop_scale : 0.f;
-            dsv[i] = pv[i] * fmaf(dsv[i], k0, -dlt);        // softmax scale is applied when dQ / dK leave TMEM
-            dsv[i + 1] = pv[i + 1] * fmaf(dsv[i + 1], k1, -dlt);
-            pv[i] *= k0;
-            pv[i + 1] *= k1;
+            const int e = c * 32 + i;
+            dsv[e] = pv[e] * fmaf(dsv[e], k0, -dlt);        // softmax scale is applied when dQ / dK leave TMEM
+            dsv[e + 1] = pv[e + 1] * fmaf(dsv[e + 1], k1, -dlt);
+            pv[e] *= k0;
+            pv[e + 1] *= k1;
           }
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) dsv[i] = pv[i] * (dsv[i] - dlt);
+          for (int i = 0; i < 32; ++i) dsv[c * 32 + i] = pv[c * 32 + i] * (dsv[c * 32 + i] - dlt);
         }
-        const uint32_t prow = pd_smem + hf * Cfg::CHUNK + row * 128;
-        const uint32_t drow = ds_smem + hf * Cfg::CHUNK + row * 128;
+      }
+      // the previous tile's [dV,dK,dQ] GEMMs must have finished reading the P/dS tiles before they are rewritten;
+      // waiting for them (and draining dQ) only now keeps that latency off the critical path
+      if (PIPELINED && it > 0) drain_dq(it - 1);
+      const uint32_t prow = pd_smem + hf * Cfg::CHUNK + row * 128;
+      const uint32_t drow = ds_smem + hf * Cfg::CHUNK + row * 128;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const uint32_t sw = (((uint32_t)(c * 4 + q)) ^ (row & 7)) << 4;
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + sw), "r"(pack_bf16(pv[8 * q], pv[8 * q + 1])),
-                       "r"(pack_bf16(pv[8 * q + 2], pv[8 * q + 3])), "r"(pack_bf16(pv[8 * q + 4], pv[8 * q + 5])),
-                       "r"(pack_bf16(pv[8 * q + 6], pv[8 * q + 7]))
-                       : "memory");
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + sw), "r"(pack_bf16(dsv[8 * q], dsv[8 * q + 1])),
-                       "r"(pack_bf16(dsv[8 * q + 2], dsv[8 * q + 3])), "r"(pack_bf16(dsv[8 * q + 4], dsv[8 * q + 5])),
-                       "r"(pack_bf16(dsv[8 * q + 6], dsv[8 * q + 7]))
-                       : "memory");
-        }
+      for (int q = 0; q < 8; ++q) {
+        const uint32_t sw = (((uint32_t)q) ^ (row & 7)) << 4;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + sw), "r"(pack_bf16(pv[8 * q], pv[8 * q + 1])),
+                     "r"(pack_bf16(pv[8 * q + 2], pv[8 * q + 3])), "r"(pack_bf16(pv[8 * q + 4], pv[8 * q + 5])),
+                     "r"(pack_bf16(pv[8 * q + 6], pv[8 * q + 7]))
+                     : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + sw), "r"(pack_bf16(dsv[8 * q], dsv[8 * q + 1])),
+                     "r"(pack_bf16(dsv[8 * q + 2], dsv[8 * q + 3])), "r"(pack_bf16(dsv[8 * q + 4], dsv[8 * q + 5])),
+                     "r"(pack_bf16(dsv[8 * q + 6], dsv[8 * q + 7]))
+                     : "memory");
       }
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
-        mbar_arrive(sdp_empty);
+        if (!PIPELINED) mbar_arrive(sdp_empty);
         mbar_arrive(pds_full);
       }
     }
