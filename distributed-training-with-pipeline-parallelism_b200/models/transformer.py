@@ -105,6 +105,28 @@ class GradSink:
     def __init__(self):
         self._g: Dict[int, torch.Tensor] = {}
         self.fused_ar = None   # ops.collective.FusedGradAllReduce while the stage's LAST backward runs
+        self.deferred: Optional[list] = None   # a list while an input-gradient-only pass (IR action I) runs
+
+    def wgrad(self, dy: torch.Tensor, x: torch.Tensor, gw: torch.Tensor, gb: Optional[torch.Tensor]) -> None:
+        """gw += dy^T x, gb += colsum(dy): now (action B) or recorded for the matching W action (torch's
+        stage_backward_input / stage_backward_weight split, _backward.py:165/:283)."""
+        if self.deferred is not None:
+            self.deferred.append(("linear", dy, x, gw, gb))
+        else:
+            F.linear_wgrad(dy, x, gw, gb, ar=self.fused_ar)
+
+    def embedding_wgrad(self, tokens: torch.Tensor, dys: Sequence[torch.Tensor], gw: torch.Tensor) -> None:
+        if self.deferred is not None:
+            self.deferred.append(("embedding", tokens, list(dys), gw, None))
+        else:
+            F.embedding_bwd(tokens, dys, gw)
+
+    def run_deferred(self, items: list) -> None:
+        for kind, a, b, gw, gb in items:
+            if kind == "linear":
+                F.linear_wgrad(a, b, gw, gb, ar=self.fused_ar)
+            else:
+                F.embedding_bwd(a, b, gw)
 
     def bind(self, param: torch.Tensor, grad: torch.Tensor) -> None:
         self._g[id(param)] = grad
@@ -159,25 +181,24 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
                       G: "GradSink") -> List[torch.Tensor]:
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms = a.norm == "rmsnorm"
-    ar = getattr(G, "fused_ar", None)
     g, da3 = F.sum_dropout_bwd(dys, p, ctx.seed(layer_id, SITE_RES3))          # d x_out, and through the FFN dropout
-    F.linear_wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias), ar=ar)
+    G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
     if a.activation == "relu":
         dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
     else:
         dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
-    F.linear_wgrad(dh, st["y3"], G(L.linear1.weight), G(L.linear1.bias), ar=ar)
+    G.wgrad(dh, st["y3"], G(L.linear1.weight), G(L.linear1.bias))
     dy3 = F.linear_dgrad(dh, L.linear1.weight)
     dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
                            0.0, 0, rms, need_da=False)
     total, da1 = F.sum_dropout_bwd([g, dz3_ln], p, ctx.seed(layer_id, SITE_RES1))  # d z3 = residual + through LN3
-    F.linear_wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias), ar=ar)
+    G.wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias))
     do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
     qkv = st["qkv"]
     dqkv = torch.empty_like(qkv)
     F.attention_bwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], st["o1"], do1, st["lse1"], ctx.B, H, a.causal, None, p,
                     ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
-    F.linear_wgrad(dqkv, st["y1"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias), ar=ar)
+    G.wgrad(dqkv, st["y1"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
     dy1 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
     dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
                           0.0, 0, rms, need_da=False)
@@ -239,12 +260,12 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
     dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
                           ctx.seed(layer_id, SITE_RES3), rms)
     x2 = st["x2"] if a.cross_attn else st["x1"]
-    F.linear_wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias), ar=getattr(G, 'fused_ar', None))
+    G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
     if a.activation == "relu":
         dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
     else:
         dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
-    F.linear_wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias), ar=getattr(G, 'fused_ar', None))
+    G.wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias))
     dx2 = F.linear_dgrad(dh, L.linear1.weight)
     dys1 = [dz3, dx2]
     dx0_extra = None
@@ -254,28 +275,28 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
         gW, gb = G(W), G(L.multihead_attn.in_proj_bias)
         dz2, da2 = F.norm_bwd(dys1, st["z2"], st["mean2"], st["rstd2"], L.norm2.weight, G(L.norm2.weight),
                               G(L.norm2.bias), p, ctx.seed(layer_id, SITE_RES2), rms)
-        F.linear_wgrad(da2, st["o2"], G(L.multihead_attn.out_proj.weight), G(L.multihead_attn.out_proj.bias), ar=getattr(G, 'fused_ar', None))
+        G.wgrad(da2, st["o2"], G(L.multihead_attn.out_proj.weight), G(L.multihead_attn.out_proj.bias))
         do2 = F.linear_dgrad(da2, L.multihead_attn.out_proj.weight)
         kv2 = st["kv2"]
         dq2 = torch.empty_like(st["q2"])
         dkv2 = torch.empty_like(kv2)
         F.attention_bwd(st["q2"], kv2[:, :d], kv2[:, d:], st["o2"], do2, st["lse2"], ctx.B, H, False, None, p,
                         ctx.seed(layer_id, SITE_ATTN2), out=(dq2, dkv2[:, :d], dkv2[:, d:]))
-        F.linear_wgrad(dq2, st["x1"], gW[:d], gb[:d], ar=getattr(G, 'fused_ar', None))
-        F.linear_wgrad(dkv2, x0, gW[d:], gb[d:], ar=getattr(G, 'fused_ar', None))
+        G.wgrad(dq2, st["x1"], gW[:d], gb[:d])
+        G.wgrad(dkv2, x0, gW[d:], gb[d:])
         dx1 = F.linear_dgrad(dq2, W[:d])
         dx0_extra = F.linear_dgrad(dkv2, W[d:])
         dys1 = [dz2, dx1]
     # ---- self-attention ----
     dz1, da1 = F.norm_bwd(dys1, st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias), p,
                           ctx.seed(layer_id, SITE_RES1), rms)
-    F.linear_wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias), ar=getattr(G, 'fused_ar', None))
+    G.wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias))
     do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
     qkv = st["qkv"]
     dqkv = torch.empty_like(qkv)
     F.attention_bwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], st["o1"], do1, st["lse1"], ctx.B, H, a.causal, None, p,
                     ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
-    F.linear_wgrad(dqkv, x0, G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias), ar=getattr(G, 'fused_ar', None))
+    G.wgrad(dqkv, x0, G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
     dx0 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
     out = [dz1, dx0]
     if dx0_extra is not None:
@@ -333,7 +354,7 @@ def stage_backward(model: "Transformer", douts: Sequence[torch.Tensor], ctx: Ctx
     dys: List[torch.Tensor] = [d.reshape(-1, d.shape[-1]) for d in douts]
     if model.output is not None:
         dlog = dys[0]
-        F.linear_wgrad(dlog, st["head_in"], G(model.output.weight), G(model.output.bias), ar=getattr(G, 'fused_ar', None))
+        G.wgrad(dlog, st["head_in"], G(model.output.weight), G(model.output.bias))
         dys = [F.linear_dgrad(dlog, model.output.weight)]
     if model.norm is not None:
         dz, _ = F.norm_bwd(dys, st["norm_in"], st["norm_mean"], st["norm_rstd"], model.norm.weight, G(model.norm.weight),
@@ -342,7 +363,7 @@ def stage_backward(model: "Transformer", douts: Sequence[torch.Tensor], ctx: Ctx
     for name in reversed(list(model.layers.keys())):
         dys = layer_backward(model.layers[name], int(name), dys, ctx, st["layers"][name], G)
     if model.tok_embeddings is not None:
-        F.embedding_bwd(st["tokens"].reshape(-1), dys, G(model.tok_embeddings.weight))
+        G.embedding_wgrad(st["tokens"].reshape(-1), dys, G(model.tok_embeddings.weight))
         return None
     if not need_input_grad:
         return None

@@ -131,7 +131,9 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
     if ar is not None and ar.armed:
         ar.wgrad(dy, x, dw_accum)
     else:
-        gemm(dy, x, dw_accum, Nout, Nin, T, True, True, OUT_F32_ACCUM)
+        # split-K partials land with TMA reduce-add in arrival order: fp32-rounding-level run-to-run differences
+        # (which Adam can amplify for near-zero gradients); the deterministic mode keeps each output tile in one CTA
+        gemm(dy, x, dw_accum, Nout, Nin, T, True, True, OUT_F32_ACCUM, force_splits=1 if DETERMINISTIC else 0)
     if db_accum is not None:
         lib = _lib_required()
         _lib.check(lib.ppb_colsum_accum(dy.data_ptr(), dy.stride(0), db_accum.data_ptr(), T, Nout, _stream()),
@@ -143,12 +145,18 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
 # fused residual + dropout + norm
 # ------------------------------------------------------------------------------------------------------------
 _scratch: dict = {}
+import os as _os
+DETERMINISTIC = _os.environ.get("PPB_DETERMINISTIC", "0") == "1"   # bit-reproducible weight gradients (no split-K)
 
 
 def _norm_scratch(device: torch.device, d: int) -> torch.Tensor:
     lib = _lib_required()
     key = (device.index, torch.cuda.current_stream().cuda_stream, "norm")
     need = int(lib.ppb_norm_bwd_scratch_bytes(0, d))
+    if torch.cuda.is_current_stream_capturing():
+        # a capture gets its own scratch from the graph's private pool (static address, reusable by the rest of the
+        # capture once this call is over); a process-wide cache entry would tie graphs of unrelated pools together
+        return torch.empty(need, dtype=torch.uint8, device=device)
     buf = _scratch.get(key)
     if buf is None or buf.numel() < need:
         buf = torch.zeros(need, dtype=torch.uint8, device=device)  # zero-filled once; the kernel self-resets
@@ -434,6 +442,8 @@ def _attn_scratch(device: torch.device, B: int, H: int, Sq: int, dh: int) -> tor
     lib = _lib_required()
     need = int(lib.ppb_attn_bwd_scratch_bytes(B, H, Sq, dh))
     key = (device.index, torch.cuda.current_stream().cuda_stream, "attn")
+    if torch.cuda.is_current_stream_capturing():
+        return torch.empty(need, dtype=torch.uint8, device=device)
     buf = _scratch.get(key)
     if buf is None or buf.numel() < need:
         buf = torch.empty(need, dtype=torch.uint8, device=device)

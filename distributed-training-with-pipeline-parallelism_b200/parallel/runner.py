@@ -35,7 +35,7 @@ class PipelineSchedule:
                  schedule: Optional[str] = None, pp_group=None, pp_group_bwd=None, dp_group=None,
                  optimizer: Optional[dict] = None,
                  scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None,
-                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2):
+                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2, actions=None):
         self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
         if not self.stages:
             raise ValueError("need at least one stage")
@@ -69,8 +69,12 @@ class PipelineSchedule:
         self.local: Dict[int, PipelineStage] = {st.stage_index: st for st in self.stages}
         self.device = self.stages[0].device
         self.cuda = self.device.type == "cuda"
-        order = build_schedule(self.name, self.pp_size, self.m, n_virtual=self.n_virtual,
-                               dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None)
+        if actions is not None:
+            order = self._load_actions(actions, optimizer is not None)
+            self.name = "custom" if schedule is None else schedule
+        else:
+            order = build_schedule(self.name, self.pp_size, self.m, n_virtual=self.n_virtual,
+                                   dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None)
         self.full_order = order
         self.order: List[Action] = order[self.pp_rank]
         self.theory_bubble = theoretical_bubble(self.pp_size, self.m, self.n_virtual)
@@ -98,6 +102,34 @@ class PipelineSchedule:
                 st.enable_graphs(self._max_inflight(st.stage_index))
 
     # ---- helpers ------------------------------------------------------------------------------------------------
+    def _load_actions(self, actions, with_optimizer: bool):
+        """User-supplied schedule: {rank: [Action | str]}, the text of ``format_schedule`` / ``to_csv``, or a path to
+        such a file (torch _PipelineScheduleRuntime._load_actions / _load_csv, schedules.py:1976-2027).  Compute-only
+        lists (no SEND/RECV) are lowered here: reduce-grad, comms, optimizer; everything is validated before use."""
+        import os
+        from .schedule import generate as G
+        if isinstance(actions, str):
+            text = open(actions).read() if os.path.exists(actions) else actions
+            order = sched_ir.parse_schedule(text) if ":" in text else sched_ir.from_csv(text)
+        else:
+            order = {int(r): [a if isinstance(a, Action) else Action.from_str(a) for a in acts] for r, acts in actions.items()}
+        for r in range(self.pp_size):
+            order.setdefault(r, [])
+        comm = (T.SEND_F, T.SEND_B, T.RECV_F, T.RECV_B)
+        s2r = G.stage_to_rank_loop(self.pp_size)
+        if self.pp_size > 1 and not any(a.type in comm for acts in order.values() for a in acts):
+            if not any(a.type == T.REDUCE_GRAD for acts in order.values() for a in acts):
+                order = G.add_reduce_grad(order, self.m, also_allreduce=self.dp_size > 1)
+            order = G.add_send_recv(order, s2r, self.num_stages)
+        elif not any(a.type == T.REDUCE_GRAD for acts in order.values() for a in acts):
+            order = G.add_reduce_grad(order, self.m, also_allreduce=self.dp_size > 1)
+        if with_optimizer and not any(a.type == T.OPTIM for acts in order.values() for a in acts):
+            order = G.add_optimizer(order)
+        G.validate_schedule(order, self.num_stages, self.m, s2r)
+        from .schedule import simulate
+        simulate(order, self.num_stages)     # raises DeadlockError on an order that cannot complete
+        return order
+
     def _global_rank(self, pp_rank: int) -> int:
         if self.pp_group is None:
             return pp_rank
@@ -114,7 +146,7 @@ class PipelineSchedule:
             if a.type == T.F:
                 live += 1
                 peak = max(peak, live)
-            elif a.type == T.B:
+            elif a.type in (T.B, T.W):
                 live -= 1
         return max(1, peak)
 
@@ -278,6 +310,33 @@ class PipelineSchedule:
                             local_in[(a.stage - 1, "B", a.mb)] = din.view(sizes[a.mb], S, -1)
                         else:
                             bwd_out[(a.stage, a.mb)] = din
+                elif typ == T.I:
+                    st = self.local[a.stage]
+                    dout = None
+                    if a.stage != last_stage:
+                        dout = self._take_input(recv_state, local_in, a.stage, "B", a.mb, compute)
+                    t0 = tick()
+                    if graphs_on:
+                        prev = slot_sends.pop((a.stage, "B", a.mb % st.nslots), None)
+                        if prev is not None:
+                            prev.wait()
+                        din = st.backward_input_graphed(a.mb, dout)
+                    else:
+                        din = st.backward_input_one_chunk(a.mb, dout)
+                    timeline.append((a, t0, tick()))
+                    if a.stage != 0:
+                        if self._rank_of_stage(a.stage - 1) == self.pp_rank:
+                            local_in[(a.stage - 1, "B", a.mb)] = din.view(sizes[a.mb], S, -1)
+                        else:
+                            bwd_out[(a.stage, a.mb)] = din
+                elif typ == T.W:
+                    t0 = tick()
+                    b_count[a.stage] = b_count.get(a.stage, 0) + 1
+                    if graphs_on:
+                        self.local[a.stage].backward_weight_graphed(a.mb, last=b_count[a.stage] == self.m)
+                    else:
+                        self.local[a.stage].backward_weight_one_chunk(a.mb, last=b_count[a.stage] == self.m)
+                    timeline.append((a, t0, tick()))
                 elif typ == T.REDUCE_GRAD:
                     # micro-batch averaging: folded into the optimizer kernel; done explicitly when there is none
                     if self.optimizer is None and self.scale_grads and self.local[a.stage].n_total:
@@ -412,13 +471,20 @@ class Schedule1F1B(PipelineSchedule):
     schedule_name = "1F1B"
 
 
+class ScheduleZeroBubble1F1B(PipelineSchedule):
+    """1F1B with backward split into input-gradient (I) and weight-gradient (W) actions, the W's moved into idle
+    slots (ZB-H1 style).  An extension beyond the reference's three schedules; exercises the I/W half of the IR."""
+    schedule_name = "ZeroBubble1F1B"
+
+
 class ScheduleInterleaved1F1B(PipelineSchedule):
     """Virtual stages, depth-first interleaved 1F1B (torch ScheduleInterleaved1F1B, used at helper:220)."""
     schedule_name = "Interleaved1F1B"
 
 
 def make_schedule(name: str, stages, n_microbatches: int, loss_fn=None, **kw) -> PipelineSchedule:
-    cls = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B, "Interleaved1F1B": ScheduleInterleaved1F1B}.get(name)
+    cls = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B, "Interleaved1F1B": ScheduleInterleaved1F1B,
+           "ZeroBubble1F1B": ScheduleZeroBubble1F1B}.get(name)
     if cls is None:
         raise ValueError(f"unknown schedule {name!r}")
     if name != "Interleaved1F1B" and not isinstance(stages, PipelineStage):

@@ -17,7 +17,8 @@ from .ir import Action, ActionType as T
 
 Order = Dict[int, List[Action]]
 
-SCHEDULES = ("GPipe", "1F1B", "Interleaved1F1B")
+SCHEDULES = ("GPipe", "1F1B", "Interleaved1F1B")   # the reference's three (helper:215-219)
+EXTRA_SCHEDULES = ("ZeroBubble1F1B",)
 
 
 def stage_to_rank_loop(pp_size: int) -> Callable[[int], int]:
@@ -103,9 +104,89 @@ def interleaved_order(pp_size: int, n_virtual: int, n_microbatches: int) -> Orde
     return order
 
 
+def zero_bubble_order(pp_size: int, n_microbatches: int, max_in_flight: Optional[int] = None,
+                      max_deferred_w: Optional[int] = None) -> Order:
+    """ZB-H1-style schedule: 1F1B with every backward split into I (input gradient, on the critical path between
+    ranks) and W (weight gradient, local), the W's greedily moved into what would otherwise be idle slots.
+
+    Built by list-scheduling on a unit-cost clock (F = I = W = 1): each tick a rank runs, in priority order, a W when
+    ``max_deferred_w`` (default ``pp_size``) weight-gradient passes are already waiting, else a ready I, else a ready
+    F while fewer than ``max_in_flight`` (default ``pp_size - rank``, the 1F1B bound on full activation stashes, F
+    until I) micro-batches are live, else a pending W, else it idles.  A deferred W keeps the GEMM operands of its
+    micro-batch (layer inputs + output gradients) alive, so ``max_deferred_w`` is the memory knob.  Not one of the reference's
+    three schedules (helper:215-219); it exercises the I/W actions of the IR end to end (SURVEY.md section 2.2 T9/T13
+    "split I/W variants")."""
+    p, m = pp_size, n_microbatches
+    f_done: Dict[tuple, int] = {}    # (stage, mb) -> tick at which the result is available
+    i_done: Dict[tuple, int] = {}
+    nf = [0] * p
+    ni = [0] * p
+    nw = [0] * p
+    order: Order = {r: [] for r in range(p)}
+    t = 0
+    while any(nw[r] < m for r in range(p)):
+        picks = []
+        for r in range(p):
+            cap = max_in_flight if max_in_flight is not None else p - r
+            wcap = max_deferred_w if max_deferred_w is not None else p
+            k = ni[r]
+            i_ready = (k < m and f_done.get((r, k), 1 << 60) <= t and (r == p - 1 or i_done.get((r + 1, k), 1 << 60) <= t))
+            k2 = nf[r]
+            f_ready = (k2 < m and (r == 0 or f_done.get((r - 1, k2), 1 << 60) <= t) and nf[r] - ni[r] < cap)
+            if ni[r] - nw[r] >= wcap:
+                picks.append((r, T.W, nw[r]))
+            elif i_ready:
+                picks.append((r, T.I, k))
+            elif f_ready:
+                picks.append((r, T.F, k2))
+            elif nw[r] < ni[r]:
+                picks.append((r, T.W, nw[r]))
+        for r, typ, k in picks:
+            order[r].append(Action(r, typ, k))
+            if typ == T.F:
+                f_done[(r, k)] = t + 1
+                nf[r] += 1
+            elif typ == T.I:
+                i_done[(r, k)] = t + 1
+                ni[r] += 1
+            else:
+                nw[r] += 1
+        t += 1
+        if t > 8 * (m + p) + 64:
+            raise RuntimeError("zero_bubble_order did not converge")
+    return order
+
+
 # ------------------------------------------------------------------------------------------------------------
 # lowering passes
 # ------------------------------------------------------------------------------------------------------------
+def split_bw(order: Order) -> Order:
+    """Replace every full backward ``B`` by the adjacent pair ``I``, ``W``."""
+    return {r: [x for a in acts for x in ((Action(a.stage, T.I, a.mb), Action(a.stage, T.W, a.mb)) if a.type == T.B else (a,))]
+            for r, acts in order.items()}
+
+
+def merge_bw(order: Order) -> Order:
+    """Fuse an ``I`` immediately followed by the ``W`` of the same stage and micro-batch back into one ``B``
+    (torch _merge_bw, schedules.py:1204): the fused backward shares loads between dgrad and wgrad and skips the
+    deferral bookkeeping."""
+    out: Order = {}
+    for r, acts in order.items():
+        res: List[Action] = []
+        i = 0
+        while i < len(acts):
+            a = acts[i]
+            if (a.type == T.I and i + 1 < len(acts) and acts[i + 1].type == T.W and acts[i + 1].stage == a.stage
+                    and acts[i + 1].mb == a.mb):
+                res.append(Action(a.stage, T.B, a.mb))
+                i += 2
+            else:
+                res.append(a)
+                i += 1
+        out[r] = res
+    return out
+
+
 def add_reduce_grad(order: Order, n_microbatches: int, also_allreduce: bool = False) -> Order:
     """Insert ``{s}REDUCE_GRAD`` right after a stage's m-th backward (B or W) -- and, for data-parallel replicas,
     ``{s}ALLREDUCE`` right behind it, which is what lets the gradient all-reduce of the later stages hide inside
@@ -245,6 +326,9 @@ def validate_schedule(order: Order, num_stages: int, n_microbatches: int,
                 b_seen[(a.stage, a.mb)] = b_seen.get((a.stage, a.mb), 0) + 1
                 if Action(a.stage, T.F, a.mb) not in pos:
                     raise ValueError(f"rank {r}: {a} before its forward")
+            elif a.type == T.W:
+                if Action(a.stage, T.I, a.mb) not in pos:
+                    raise ValueError(f"rank {r}: {a} before its input-gradient pass")
             elif a.type in (T.SEND_F, T.SEND_B):
                 sends.add((a.type, a.stage, a.mb))
                 src = Action(a.stage, T.F if a.type == T.SEND_F else T.B, a.mb)
@@ -252,6 +336,9 @@ def validate_schedule(order: Order, num_stages: int, n_microbatches: int,
                     raise ValueError(f"rank {r}: {a} before the compute that produces it")
             elif a.type in (T.RECV_F, T.RECV_B):
                 recvs.add((a.type, a.stage, a.mb))
+        for a in pos:
+            if a.type == T.I and Action(a.stage, T.W, a.mb) not in pos:
+                raise ValueError(f"rank {r}: {a} has no weight-gradient pass")
         for a, i in pos.items():  # a consumer must come after its RECV
             if a.type == T.F and Action(a.stage, T.RECV_F, a.mb) in pos and pos[Action(a.stage, T.RECV_F, a.mb)] > i:
                 raise ValueError(f"rank {r}: {a} before its RECV_F")
@@ -290,8 +377,12 @@ def build_schedule(name: str, pp_size: int, n_microbatches: int, n_virtual: int 
         order = one_f_one_b_order(pp_size, n_microbatches)
     elif name == "Interleaved1F1B":
         order = interleaved_order(pp_size, n_virtual, n_microbatches)
+    elif name == "ZeroBubble1F1B":
+        if n_virtual != 1:
+            raise ValueError("ZeroBubble1F1B runs one stage per rank")
+        order = merge_bw(zero_bubble_order(pp_size, n_microbatches))
     else:
-        raise ValueError(f"unknown schedule {name!r}; expected one of {SCHEDULES}")
+        raise ValueError(f"unknown schedule {name!r}; expected one of {SCHEDULES + EXTRA_SCHEDULES}")
     num_stages = pp_size * n_virtual
     s2r = stage_to_rank_loop(pp_size)
     order = add_unshard_reshard(order)

@@ -48,6 +48,7 @@ class PipelineStage:
         self.step_count = 0
         self.training = True
         self.fused_ar = None
+        self.deferred_wgrads: Dict[int, list] = {}   # micro-batch -> weight-gradient work recorded by an I action
         self.nslots = 0
         self.graphs = None
         self.has_params = any(True for _ in submodule.parameters())
@@ -172,9 +173,15 @@ class PipelineStage:
         if self.device.type == "cuda" and self._materialized:
             self.seed_offset.fill_(self.step_count * 0x632BE5AB)
 
+    def _mb_offset(self, mb: int) -> int:
+        """Step- and micro-batch-varying part of every dropout seed (one scheme for CPU, eager CUDA and graph replays)."""
+        return (self.step_count * 0x632BE5AB + (mb + 1) * 0x9E3779B1) & 0x7FFFFFFFFFFFFFFF
+
     def _ctx(self, mb: int, batch: int, seq: int) -> Ctx:
-        off = 0 if self.device.type == "cuda" else self.step_count * 0x632BE5AB
-        return Ctx(self.args, batch, seq, self.base_seed, mb, self.training, off)
+        # on CUDA the offset lives in device memory (set right before the launches of a micro-batch), so the seeds
+        # baked into captured kernels are micro-batch independent; the CPU program adds the same number on the host
+        off = 0 if self.device.type == "cuda" else self._mb_offset(mb)
+        return Ctx(self.args, batch, seq, self.base_seed, 0, self.training, off)
 
     def forward_one_chunk(self, mb: int, inp: torch.Tensor, target: Optional[torch.Tensor] = None,
                           loss_scale: float = 1.0, loss_fn=None) -> torch.Tensor:
@@ -186,6 +193,8 @@ class PipelineStage:
         b, S = inp.shape[0], inp.shape[1]
         ctx = self._ctx(mb, b, S)
         st: dict = {}
+        if self.device.type == "cuda":
+            self._set_mb_seed(mb)
         with torch.no_grad():
             out = stage_forward(self.submod, inp, ctx, st)
             if self.is_last and target is not None and self.submod.output is not None:
@@ -220,9 +229,44 @@ class PipelineStage:
         if fused is not None:
             fused.begin_last_backward()   # this backward's weight-gradient GEMMs carry the DP all-reduce
             self.sink.fused_ar = fused
+        if self.device.type == "cuda":
+            self._set_mb_seed(mb)
         try:
             with torch.no_grad():
                 return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+        finally:
+            self.sink.fused_ar = None
+
+    def backward_input_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """IR action ``I``: the input-gradient chain only (dgrad GEMMs, attention backward, norm backward -- whose
+        gamma/beta gradients are by-products of the same kernel and land now).  Every weight-gradient GEMM and the
+        embedding scatter are recorded, with their operands kept alive, for the matching ``W`` action.  Counterpart
+        of torch's stage_backward_input (_backward.py:165, driven from stage.py:873); explicit here because the
+        stage program is explicit."""
+        if mb in self.deferred_wgrads:
+            raise RuntimeError(f"stage {self.stage_index}: I{mb} issued twice without W{mb}")
+        self.sink.deferred = []
+        try:
+            din = self.backward_one_chunk(mb, dout, last=False)
+        finally:
+            items, self.sink.deferred = self.sink.deferred, None
+        self.deferred_wgrads[mb] = items
+        return din
+
+    def backward_weight_one_chunk(self, mb: int, last: bool = False) -> None:
+        """IR action ``W``: run the weight-gradient work recorded by ``I`` of the same micro-batch (torch
+        stage_backward_weight, _backward.py:283).  ``last`` = this is the stage's final W of the step, whose GEMMs
+        carry the fused data-parallel all-reduce when that is enabled."""
+        items = self.deferred_wgrads.pop(mb, None)
+        if items is None:
+            raise RuntimeError(f"stage {self.stage_index}: W{mb} without a preceding I{mb}")
+        fused = self.fused_ar if (last and self.fused_ar is not None) else None
+        if fused is not None:
+            fused.begin_last_backward()
+            self.sink.fused_ar = fused
+        try:
+            with torch.no_grad():
+                self.sink.run_deferred(items)
         finally:
             self.sink.fused_ar = None
 
@@ -233,11 +277,10 @@ class PipelineStage:
         activation stash of a slot lives in the graphs' private memory pool."""
         self.nslots = int(nslots)
         self.graphs: Dict[int, dict] = {}
-        self.graph_pool = torch.cuda.graph_pool_handle()
 
     def _set_mb_seed(self, mb: int) -> None:
         # micro-batch-varying part of the dropout seed lives in device memory, so graph replays get fresh masks
-        self.seed_offset.fill_((self.step_count * 0x632BE5AB + (mb + 1) * 0x9E3779B1) & 0x7FFFFFFFFFFFFFFF)
+        self.seed_offset.fill_(self._mb_offset(mb))
 
     def forward_graphed(self, mb: int, inp: torch.Tensor, target: Optional[torch.Tensor] = None) -> torch.Tensor:
         from ..ops import _lib as L
@@ -246,12 +289,16 @@ class PipelineStage:
         self._set_mb_seed(mb)
         if g is None:
             g = {"in": inp.clone(), "tgt": None if target is None else target.clone(), "F": torch.cuda.CUDAGraph(),
-                 "B": None, "dout": None, "din": None, "sends": {}}
+                 "B": None, "dout": None, "din": None, "sends": {},
+                 # one private pool per slot: within a slot the replay order F -> B (or F -> I -> W) is the capture
+                 # order, so its graphs may share scratch; across slots live ranges interleave differently from the
+                 # capture order (slot 1's stash is live while slot 0's backward replays), so nothing is shared
+                 "pool": torch.cuda.graph_pool_handle()}
             b, S = inp.shape[0], inp.shape[1]
-            ctx = Ctx(self.args, b, S, self.base_seed, slot, self.training, 0)
+            ctx = Ctx(self.args, b, S, self.base_seed, 0, self.training, 0)   # micro-batch variation comes from the device-side offset only
             st: dict = {}
             n0 = L.launches()
-            with torch.cuda.graph(g["F"], pool=self.graph_pool):
+            with torch.cuda.graph(g["F"], pool=g["pool"]):
                 with torch.no_grad():
                     out = stage_forward(self.submod, g["in"], ctx, st)
                     loss = None
@@ -283,7 +330,7 @@ class PipelineStage:
             g["B"] = torch.cuda.CUDAGraph()
             st, ctx = g["stash"], g["ctx"]
             n0 = L.launches()
-            with torch.cuda.graph(g["B"], pool=self.graph_pool):
+            with torch.cuda.graph(g["B"], pool=g["pool"]):
                 with torch.no_grad():
                     douts = [st["dlogits"]] if g["dout"] is None else [g["dout"]]
                     g["din"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
@@ -294,6 +341,60 @@ class PipelineStage:
             L.count_launch(g["nB"])
         g["B"].replay()
         return g["din"]
+
+    def backward_input_graphed(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+        """Graph replay of IR action ``I`` on the slot of ``mb``: the deferred weight-gradient operands are static
+        tensors of the graph pool, so the matching ``W`` is a second graph over the same addresses."""
+        from ..ops import _lib as L
+        slot = mb % self.nslots
+        g = self.graphs[slot]
+        self._set_mb_seed(mb)
+        self.stash.pop(mb, None)
+        self.ctxs.pop(mb, None)
+        if g.get("I") is None:
+            g["dout"] = None if dout is None else dout.clone()
+            g["I"] = torch.cuda.CUDAGraph()
+            st, ctx = g["stash"], g["ctx"]
+            n0 = L.launches()
+            self.sink.deferred = []
+            try:
+                with torch.cuda.graph(g["I"], pool=g["pool"]):
+                    with torch.no_grad():
+                        douts = [st["dlogits"]] if g["dout"] is None else [g["dout"]]
+                        g["din"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+            finally:
+                g["wlist"], self.sink.deferred = self.sink.deferred, None
+            g["nI"] = L.launches() - n0
+            g["W"] = None
+        else:
+            if dout is not None:
+                g["dout"].copy_(dout.reshape(g["dout"].shape))
+            L.count_launch(g["nI"])
+        g["I"].replay()
+        return g["din"]
+
+    def backward_weight_graphed(self, mb: int, last: bool = False) -> None:
+        from ..ops import _lib as L
+        g = self.graphs[mb % self.nslots]
+        if last and self.fused_ar is not None:   # fused DP all-reduce epilogues: a different launch sequence, eager
+            self.fused_ar.begin_last_backward()
+            self.sink.fused_ar = self.fused_ar
+            try:
+                with torch.no_grad():
+                    self.sink.run_deferred(g["wlist"])
+            finally:
+                self.sink.fused_ar = None
+            return
+        if g.get("W") is None:
+            g["W"] = torch.cuda.CUDAGraph()
+            n0 = L.launches()
+            with torch.cuda.graph(g["W"], pool=g["pool"]):
+                with torch.no_grad():
+                    self.sink.run_deferred(g["wlist"])
+            g["nW"] = L.launches() - n0
+        else:
+            L.count_launch(g["nW"])
+        g["W"].replay()
 
     def backward_eager_on_slot(self, mb: int, dout: Optional[torch.Tensor], last: bool) -> Optional[torch.Tensor]:
         """Eager backward over a graph slot's stash (used for the step's last micro-batch when the fused DP

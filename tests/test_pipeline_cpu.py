@@ -16,6 +16,8 @@ pytestmark = pytest.mark.timeout(600)
     ("GPipe", 4, 4, 1, 8),
     ("1F1B", 4, 5, 1, 4),          # 5 layers on 4 stages: the last stage takes the remainder (helper:74-75)
     ("Interleaved1F1B", 4, 8, 2, 8),
+    ("ZeroBubble1F1B", 2, 4, 1, 4),       # backward split into I / W actions
+    ("ZeroBubble1F1B", 4, 4, 1, 8),
 ])
 def test_pipeline_matches_single_process(schedule, world, n_layers, v, m):
     res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), timeout=400)
@@ -54,3 +56,34 @@ def test_reference_api_run_one_experiment():
     assert res["tokens_processed"] == 16 * 16 * 2
     assert res["throughput"] > 0
     assert abs(res["bubble_theory"] - 3 / 11) < 1e-9
+
+
+def test_custom_action_lists_single_rank(tmp_path):
+    """User-supplied schedules (dict / text / CSV file; torch _load_actions/_load_csv): lowered, validated, executed;
+    an I/W order gives the same gradients as the fused-backward order."""
+    import copy
+    import torch
+    from ppb200.api import make_schedule, manual_model_split
+    from ppb200.models import ModelArgs, Transformer
+    from ppb200.parallel.schedule import ir
+    torch.manual_seed(0)
+    args = ModelArgs(dim=64, n_layers=2, n_heads=4, vocab_size=97, ffn_dim=128, dropout=0.1)
+    full = Transformer(args)
+    x, y = torch.randint(0, 97, (8, 16)), torch.randint(0, 97, (8, 16))
+    grads = {}
+    csv = tmp_path / "sched.csv"
+    csv.write_text("0F0,0F1,0I0,0I1,0W1,0W0,0F2,0F3,0I2,0W2,0I3,0W3\n")
+    for key, custom in [("B", None), ("dict", {0: "0F0 0I0 0F1 0I1 0W0 0F2 0I2 0W1 0F3 0I3 0W2 0W3".split()}),
+                        ("csv", str(csv)), ("text", "rank0: 0F0 0B0 0F1 0B1 0F2 0I2 0F3 0I3 0W2 0W3")]:
+        st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
+        sched = make_schedule("1F1B", st, 4, None, actions=custom)
+        losses = []
+        sched.step(x, target=y, losses=losses)
+        grads[key] = (st.grad[:st.n_total].clone(), torch.stack([l.reshape(()) for l in losses]))
+        assert not st.deferred_wgrads
+    for key in ("dict", "csv", "text"):
+        assert torch.allclose(grads[key][1], grads["B"][1], atol=1e-6)
+        assert (grads[key][0] - grads["B"][0]).norm() <= 1e-5 * grads["B"][0].norm(), key
+    with pytest.raises(ValueError):      # W without its I
+        make_schedule("1F1B", manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu")), 1, None, actions={0: ["0F0", "0W0"]})
+    assert ir.from_csv(csv.read_text())[0][2].type.value == "I"

@@ -7,6 +7,7 @@ from ppb200.parallel.schedule import (Action, ActionType, build_schedule, format
                                       theoretical_bubble, validate_schedule, gpipe_order, one_f_one_b_order,
                                       interleaved_order, add_reduce_grad, add_send_recv, stage_to_rank_loop)
 from ppb200.parallel.schedule import ir
+from ppb200.parallel.schedule import ActionType as T
 from ppb200.parallel.schedule.simulate import DeadlockError
 
 GOLDEN_RANK0 = ("0F0 0SEND_F0 4RECV_F0 0F1 0SEND_F1 4RECV_F1 0F2 0SEND_F2 4RECV_F2 0F3 0SEND_F3 4RECV_F3 "
@@ -155,3 +156,63 @@ def test_matches_torch_generator_when_available():
                 assert [str(a) for a in mine[r]] == theirs, (P, v, m, r)
         except (AttributeError, TypeError):
             pytest.skip("torch internals changed")
+
+
+# ---- split backward (I / W) ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("p,m", [(2, 4), (4, 4), (4, 8), (8, 16), (3, 7)])
+def test_zero_bubble_schedule_is_valid_and_beats_1f1b(p, m):
+    from ppb200.parallel.schedule import zero_bubble_order, merge_bw
+    raw = zero_bubble_order(p, m)
+    for r, acts in raw.items():
+        assert sum(a.type == T.F for a in acts) == m
+        assert sum(a.type == T.I for a in acts) == m
+        assert sum(a.type == T.W for a in acts) == m
+        live = peak = wait = wpeak = 0
+        for a in acts:   # the 1F1B bound on full activation stashes (F until I) is kept; deferred W's are capped at p
+            live += (a.type == T.F) - (a.type == T.I)
+            wait += (a.type == T.I) - (a.type == T.W)
+            peak, wpeak = max(peak, live), max(wpeak, wait)
+        assert peak <= p - r and wpeak <= p
+    order = build_schedule("ZeroBubble1F1B", p, m, with_optimizer=True)     # validates internally
+    zb = simulate(order, p, f_cost=1.0, b_cost=2.0)
+    ref = simulate(build_schedule("1F1B", p, m), p, f_cost=1.0, b_cost=2.0)
+    assert zb.makespan <= ref.makespan
+    if m >= p:
+        assert zb.makespan == 3 * m + (p - 1)        # ZB-H1: bubble (p-1)(F + I - W) with unit costs
+        assert ref.makespan == 3 * (m + p - 1)
+    # adjacent I,W pairs were fused back into B by merge_bw; nothing else changed
+    merged = merge_bw(raw)
+    for r in raw:
+        n_b = sum(a.type == T.B for a in merged[r])
+        assert sum(a.type == T.I for a in merged[r]) == m - n_b == sum(a.type == T.W for a in merged[r])
+
+
+def test_split_and_merge_bw_roundtrip():
+    from ppb200.parallel.schedule import split_bw, merge_bw, one_f_one_b_order
+    base = one_f_one_b_order(4, 8)
+    sp = split_bw(base)
+    assert all(a.type != T.B for acts in sp.values() for a in acts)
+    assert merge_bw(sp) == base
+
+
+def test_validator_rejects_w_before_i():
+    from ppb200.parallel.schedule import validate_schedule
+    bad = {0: [Action(0, T.F, 0), Action(0, T.W, 0), Action(0, T.I, 0)]}
+    with pytest.raises(ValueError):
+        validate_schedule(bad, 1, 1)
+    bad = {0: [Action(0, T.F, 0), Action(0, T.I, 0)]}
+    with pytest.raises(ValueError):
+        validate_schedule(bad, 1, 1)
+
+
+def test_concept_figures_and_ascii(tmp_path):
+    from ppb200.utils import diagram
+    paths = diagram.write_concept_figures(str(tmp_path))
+    assert len(paths) == 4
+    for p in paths:
+        txt = open(p).read()
+        assert txt.startswith("<svg") and txt.rstrip().endswith("</svg>")
+    tl, span, bub = diagram.timeline_of("1F1B", 4, 8)
+    art = diagram.ascii_timeline(tl, span)
+    assert art.count("\n") == 3 and art.splitlines()[3].startswith("rank3: ...0aa1")
+    assert abs(max(bub.values()) - 3 / 11) < 1e-9
