@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--microbatches", type=int, default=32)
     ap.add_argument("--virtual-stages", type=int, default=1)
     ap.add_argument("--dp", type=int, default=1)
+    ap.add_argument("--tp", type=int, default=1, help="intra-stage tensor parallel degree (pre-LN presets, dropout 0)")
     ap.add_argument("--partition", default="balanced", choices=["reference", "balanced"])
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
@@ -105,12 +106,13 @@ def run_ours(a, rank, local_rank, world):
         from ppb200.parallel.mesh import configure_nccl_for_pipeline
         configure_nccl_for_pipeline()
         dist.init_process_group("nccl")
-        mesh = init_mesh(dp_size=a.dp, pp_size=world // a.dp)
+        mesh = init_mesh(dp_size=a.dp, pp_size=world // (a.dp * a.tp), tp_size=a.tp)
         pp_group, dp_group, pp_idx, dp_idx, P = mesh.pp_group, mesh.dp_group, mesh.pp_idx, mesh.dp_idx, mesh.pp_size
         pp_group_bwd = mesh.pp_group_bwd
+        tp_group, tp_idx = mesh.tp_group, mesh.tp_idx
     else:
-        pp_group = dp_group = pp_group_bwd = None
-        pp_idx = dp_idx = 0
+        pp_group = dp_group = pp_group_bwd = tp_group = None
+        pp_idx = dp_idx = tp_idx = 0
         P = 1
     over = {"dtype": torch.bfloat16}
     if a.dropout is not None:
@@ -126,7 +128,10 @@ def run_ours(a, rank, local_rank, world):
     for i in range(v):
         sidx = pp_idx + P * i
         model = build_stage_model(margs, sidx, num_stages, rule=a.partition, seq_len=a.seq_len, device=dev, seed=1234)
-        st = PipelineStage(model, sidx, num_stages, dev, group=pp_group, dp_group=dp_group)
+        if a.tp > 1:
+            from ppb200.models.tp import shard_model_for_tp
+            shard_model_for_tp(model, tp_idx, a.tp)
+        st = PipelineStage(model, sidx, num_stages, dev, group=pp_group, dp_group=dp_group, tp_group=tp_group)
         st.base_seed = 1234
         stages.append(st)
     opt = {"lr": 1e-4, "betas": (0.9, 0.95), "weight_decay": 0.1}
@@ -187,7 +192,7 @@ def run_ours(a, rank, local_rank, world):
         ms_e2e = timed(step_e2e, a.steps)
         tokens = a.global_batch * S
         e2e = {"value": tokens * a.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / a.steps,
-               "h2d_bytes_per_step": int(a.dp * 2 * B * S * 8), "d2h_bytes_per_step": int(a.dp * 4)}
+               "h2d_bytes_per_step": int(a.dp * a.tp * 2 * B * S * 8), "d2h_bytes_per_step": int(a.dp * 4)}
     if a.trace:
         evs = gather_trace(sched)
         if rank == 0 and evs is not None:
@@ -204,13 +209,13 @@ def run_ours(a, rank, local_rank, world):
     if rank == 0:
         tokens = a.global_batch * S
         ms_step = ms_total / a.steps
-        par = f"pp{P}" + (f"xdp{a.dp}" if a.dp > 1 else "") + (f"xv{v}" if v > 1 else "")
+        par = f"pp{P}" + (f"xdp{a.dp}" if a.dp > 1 else "") + (f"xtp{a.tp}" if a.tp > 1 else "") + (f"xv{v}" if v > 1 else "")
         emit({
             "metric": "tokens/sec (1F1B pipeline training step, max over ranks)" if a.schedule == "1F1B" else f"tokens/sec ({a.schedule})",
             "value": tokens / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic random tokens, random-init weights", "impl": "ours",
-            "config": {"model": f"helper LM @ GPT-2 medium ({a.model}: dim {margs.dim}, {margs.n_layers} layers, {margs.n_heads} heads, vocab {margs.vocab_size}, ffn {margs.ffn_dim}, dropout {margs.dropout})",
+            "config": {"model": f"{'helper LM @ GPT-2 medium' if a.model == 'ref-gpt2-medium' else 'LM'} ({a.model}: dim {margs.dim}, {margs.n_layers} layers, {margs.n_heads} heads, vocab {margs.vocab_size}, ffn {margs.ffn_dim}, dropout {margs.dropout})",
                        "global_batch": a.global_batch, "seq_len": S, "n_microbatches": a.microbatches, "schedule": a.schedule,
                        "parallelism": par, "partition": a.partition, "optimizer": "fused AdamW (in timed region)",
                        "l2": "inputs >> L2: >2 GB of weights+activations touched per step per GPU, no explicit flush"},
@@ -345,7 +350,7 @@ def run_reference(a, rank, local_rank, world):
                 "value": B * S / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic random tokens, random-init weights", "impl": "reference",
-                "config": {"model": f"helper LM @ GPT-2 medium ({a.model}: {dims})", "global_batch": B, "seq_len": S,
+                "config": {"model": f"{'helper LM @ GPT-2 medium' if a.model == 'ref-gpt2-medium' else 'LM'} ({a.model}: {dims})", "global_batch": B, "seq_len": S,
                            "n_microbatches": a.microbatches, "schedule": a.schedule, "parallelism": f"pp{world}" + (f"xv{v}" if v > 1 else ""),
                            "partition": "reference (helper:70-75)", "optimizer": "torch.optim.AdamW(fused=True) after schedule.step (in timed region)",
                            "stack": "unmodified helper Transformer/manual_model_split + torch.distributed.pipelining + NCCL p2p + cuBLAS/SDPA, bf16 parameters"},

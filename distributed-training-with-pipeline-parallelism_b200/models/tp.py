@@ -1,0 +1,170 @@
+"""Intra-stage tensor parallelism (Megatron style, with sequence-parallel activations) for the pre-LN block.
+
+Not in the reference ("TP (intra-stage): no"); required by BASELINE.json config 4 ("4-stage
+1F1B x 2-way intra-stage TP, fused GEMM->reduce-scatter / all-gather->GEMM").  Layout per decoder layer, tp ranks:
+
+    residual stream, norms, residual adds ......... [T/tp, d] row shards (sequence parallel, every rank its own rows)
+    in_proj  (column-parallel, heads h0..h1) ....... qkv_local [T, 3d/tp] = all-gather(norm1(x)) @ Wqkv_local^T   (K12)
+    attention ..................................... local heads only, all T rows
+    out_proj (row-parallel) ....................... a1 [T/tp, d] = reduce-scatter(o_local @ Wo_local^T)          (K11)
+    linear1  (column-parallel) .................... h_local [T, f/tp] = act(all-gather(norm3(z)) @ W1_local^T)   (K12)
+    linear2  (row-parallel) ....................... a3 [T/tp, d] = reduce-scatter(h_local @ W2_local^T)          (K11)
+
+Backward mirrors it: the input gradient of a row-parallel layer is an all-gather -> GEMM, the input gradient of a
+column-parallel layer is a GEMM -> reduce-scatter, weight gradients are local GEMMs against the gathered rows.
+
+Sharded parameters keep the reference's key names; split dims (for checkpoint merge, ``merge_tp_shards``):
+    self_attn.in_proj_weight / in_proj_bias : dim 0, per head WITHIN each of q, k, v  (packed [3, H, dh, ...])
+    self_attn.out_proj.weight               : dim 1
+    linear1.weight / linear1.bias           : dim 0
+    linear2.weight                          : dim 1
+    everything else (norms, out_proj.bias, linear2.bias, embedding, head) is replicated; its gradient is computed
+    on the local token rows and summed over the tp group once per step (``PipelineStage.reduce_tp_grads``).
+
+Dropout must be 0 on this path (Llama-style models have none): the column shards would need per-rank mask streams.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as F
+
+SHARD_DIM = {"self_attn.in_proj_weight": "qkv0", "self_attn.in_proj_bias": "qkv0", "self_attn.out_proj.weight": 1,
+             "linear1.weight": 0, "linear1.bias": 0, "linear2.weight": 1}
+
+
+def _shard_key(name: str):
+    for suffix, dim in SHARD_DIM.items():
+        if name.endswith(suffix):
+            return dim
+    return None
+
+
+def shard_tensor(name: str, t: torch.Tensor, n_heads: int, tp_rank: int, tp_size: int) -> torch.Tensor:
+    dim = _shard_key(name)
+    if dim is None:
+        return t
+    if dim == "qkv0":
+        H = n_heads
+        v = t.reshape(3, H, t.shape[0] // (3 * H), *t.shape[1:])
+        h0, h1 = tp_rank * H // tp_size, (tp_rank + 1) * H // tp_size
+        return v[:, h0:h1].reshape(-1, *t.shape[1:]).contiguous()
+    n = t.shape[dim]
+    return t.narrow(dim, tp_rank * n // tp_size, n // tp_size).contiguous()
+
+
+def shard_model_for_tp(model, tp_rank: int, tp_size: int):
+    """Replace the shardable parameters of every layer of a (pruned) ``Transformer`` by this rank's slices, in place."""
+    a = model.args
+    if tp_size == 1:
+        return model
+    if not a.norm_first or a.cross_attn:
+        raise ValueError("tensor parallelism is implemented for the pre-LN block (norm_first=True, cross_attn=False)")
+    if a.dropout != 0.0:
+        raise ValueError("tensor parallelism needs dropout=0 (per-rank mask streams for column shards are not implemented)")
+    if a.n_heads % tp_size or a.ffn_dim % tp_size or (a.ffn_dim // tp_size) % 8 or (a.dim // tp_size) % 8:
+        raise ValueError(f"heads ({a.n_heads}) and ffn_dim ({a.ffn_dim}) must divide by tp={tp_size} into multiples of 8 columns")
+    for name, p in list(model.named_parameters()):
+        if _shard_key(name) is None:
+            p._tp_replicated = True
+            continue
+        mod = model
+        parts = name.split(".")
+        for part in parts[:-1]:
+            mod = getattr(mod, part) if not isinstance(mod, nn.ModuleDict) else mod[part]
+        new = nn.Parameter(shard_tensor(name, p.data, a.n_heads, tp_rank, tp_size), requires_grad=p.requires_grad)
+        new._tp_replicated = False
+        setattr(mod, parts[-1], new)
+    model.tp_rank, model.tp_size = tp_rank, tp_size
+    return model
+
+
+def merge_tp_shards(shards: Sequence[Dict[str, torch.Tensor]], n_heads: int) -> Dict[str, torch.Tensor]:
+    """Inverse of ``shard_tensor`` over whole state dicts: tp shards (same stage) -> the reference-layout state dict."""
+    tp = len(shards)
+    out: Dict[str, torch.Tensor] = {}
+    for name in shards[0]:
+        dim = _shard_key(name)
+        ts = [sd[name] for sd in shards]
+        if dim is None:
+            out[name] = ts[0].clone()
+        elif dim == "qkv0":
+            hl = n_heads // tp
+            vs = [t.reshape(3, hl, t.shape[0] // (3 * hl), *t.shape[1:]) for t in ts]
+            out[name] = torch.cat(vs, dim=1).reshape(-1, *ts[0].shape[1:]).contiguous()
+        else:
+            out[name] = torch.cat(ts, dim=dim).contiguous()
+    return out
+
+
+def _rs_finish(y32: torch.Tensor, bias, dtype) -> torch.Tensor:
+    """fp32 reduce-scatter result (+ replicated bias) -> activation dtype."""
+    if bias is not None:
+        return (y32 + bias.float()).to(dtype)
+    return y32.to(dtype)
+
+
+def _gelu_bwd(dh: torch.Tensor, hpre: torch.Tensor) -> torch.Tensor:
+    a = hpre.float()
+    cdf = 0.5 * (1.0 + torch.erf(a * 0.70710678118))
+    pdf = 0.3989422804 * torch.exp(-0.5 * a * a)
+    return (dh.float() * (cdf + a * pdf)).to(dh.dtype)
+
+
+def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> torch.Tensor:
+    """x_in: this rank's [T/tp, d] rows of the residual stream.  Returns the same rows of the layer output."""
+    a, tp = ctx.args, ctx.tp
+    dl, Hl = a.dim // tp.tp, a.n_heads // tp.tp
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
+    qkv, y1_full = tp.ag_linear(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, 0.0, 0)
+    a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x_in.dtype)
+    z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, 0.0, 0, rms)
+    if a.activation == "relu":
+        h, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias, "relu")
+    else:
+        hpre, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias)
+        h = F.gelu_fwd(hpre)
+        st["hpre"] = hpre
+    a3 = _rs_finish(tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x_in.dtype)
+    x_out = F.add_dropout_fwd(z3, a3, 0.0, 0)
+    st.update(x_in=x_in, y1_full=y1_full, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1, z3=z3, y3_full=y3_full,
+              mean3=mean3, rstd3=rstd3, h=h)
+    return x_out
+
+
+def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: dict, G) -> List[torch.Tensor]:
+    a, tp = ctx.args, ctx.tp
+    dl, Hl = a.dim // tp.tp, a.n_heads // tp.tp
+    rms = a.norm == "rmsnorm"
+    g, _ = F.sum_dropout_bwd(dys, 0.0, 0)                               # d x_out rows == d a3 rows
+    # linear2 (row-parallel):  d h_local = gather(g) @ W2_local ;  dW2_local += gather(g)^T h_local
+    dh, g_full = tp.ag_linear(g, L.linear2.weight, w_mn_major=True)
+    G.wgrad(g_full, st["h"], G(L.linear2.weight), None)
+    G.bias_grad(g, G(L.linear2.bias))
+    if a.activation == "relu":
+        dh = torch.where(st["h"] > 0, dh, torch.zeros_like(dh))
+    else:
+        dh = _gelu_bwd(dh, st["hpre"])
+    # linear1 (column-parallel):  dW1_local += dh^T gather(y3) ;  d y3 rows = reduce-scatter(dh @ W1_local)
+    G.wgrad(dh, st["y3_full"], G(L.linear1.weight), G(L.linear1.bias))
+    dy3 = tp.linear_rs(dh, L.linear1.weight, w_mn_major=True).to(g.dtype)
+    dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
+                           0.0, 0, rms, need_da=False)
+    total, _ = F.sum_dropout_bwd([g, dz3_ln], 0.0, 0)                  # d z3 rows == d a1 rows
+    do1, t_full = tp.ag_linear(total, L.self_attn.out_proj.weight, w_mn_major=True)
+    G.wgrad(t_full, st["o1"], G(L.self_attn.out_proj.weight), None)
+    G.bias_grad(total, G(L.self_attn.out_proj.bias))
+    qkv = st["qkv"]
+    dqkv = torch.empty_like(qkv)
+    F.attention_bwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], st["o1"], do1, st["lse1"], ctx.B, Hl, a.causal, None,
+                    0.0, 0, out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
+    G.wgrad(dqkv, st["y1_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
+    dy1 = tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True).to(g.dtype)
+    dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
+                          0.0, 0, rms, need_da=False)
+    return [total, dx_ln]

@@ -115,6 +115,13 @@ class GradSink:
         else:
             F.linear_wgrad(dy, x, gw, gb, ar=self.fused_ar)
 
+    def bias_grad(self, dy: torch.Tensor, gb: torch.Tensor) -> None:
+        """gb += colsum(dy) for a bias whose weight gradient is computed elsewhere (tensor-parallel row-parallel layers)."""
+        if self.deferred is not None:
+            self.deferred.append(("bias", dy, None, None, gb))
+        else:
+            F.colsum_accum(dy, gb)
+
     def embedding_wgrad(self, tokens: torch.Tensor, dys: Sequence[torch.Tensor], gw: torch.Tensor) -> None:
         if self.deferred is not None:
             self.deferred.append(("embedding", tokens, list(dys), gw, None))
@@ -125,6 +132,8 @@ class GradSink:
         for kind, a, b, gw, gb in items:
             if kind == "linear":
                 F.linear_wgrad(a, b, gw, gb, ar=self.fused_ar)
+            elif kind == "bias":
+                F.colsum_accum(a, gb)
             else:
                 F.embedding_bwd(a, b, gw)
 
@@ -147,6 +156,7 @@ class Ctx:
         self.base_seed, self.mb = base_seed, mb
         self.p = args.dropout if training else 0.0
         self.step_offset = step_offset  # CPU path only: on CUDA the offset lives in device memory
+        self.tp = None                  # ops.collective.TPComm when the stage is tensor-parallel (models/tp.py)
 
     def seed(self, layer_id: int, site: int) -> int:
         return (site_seed(self.base_seed, layer_id, self.mb, site) + self.step_offset) & _MASK64
@@ -208,6 +218,9 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
 def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
     """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
     ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
+    if ctx.tp is not None:
+        from .tp import tp_prenorm_forward
+        return tp_prenorm_forward(L, layer_id, x0, ctx, st)
     if ctx.args.norm_first:
         return _prenorm_forward(L, layer_id, x0, ctx, st)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
@@ -251,6 +264,9 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
                    G: GradSink) -> List[torch.Tensor]:
     """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. x3 (summed on load by the norm
     kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. x0."""
+    if ctx.tp is not None:
+        from .tp import tp_prenorm_backward
+        return tp_prenorm_backward(L, layer_id, dys, ctx, st, G)
     if ctx.args.norm_first:
         return _prenorm_backward(L, layer_id, dys, ctx, st, G)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
@@ -313,6 +329,8 @@ def stage_forward(model: "Transformer", inp: torch.Tensor, ctx: Ctx, st: dict) -
     row-padded buffer) when the model holds the LM head."""
     a = ctx.args
     if model.tok_embeddings is not None:
+        if ctx.tp is not None:   # sequence-parallel: this rank embeds its own rows of the flattened token stream
+            inp = inp.reshape(-1)[ctx.tp.rank * ctx.tp.rows:(ctx.tp.rank + 1) * ctx.tp.rows]
         st["tokens"] = inp
         h = F.embedding_fwd(inp.reshape(-1), model.tok_embeddings.weight)
     else:
@@ -335,11 +353,16 @@ def stage_forward(model: "Transformer", inp: torch.Tensor, ctx: Ctx, st: dict) -
     return h
 
 
-def stage_loss(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float, st: dict) -> torch.Tensor:
+def stage_loss(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float, st: dict, tp=None) -> torch.Tensor:
     """Mean token cross-entropy (helper:197-201) of one micro-batch; overwrites ``logits`` with its gradient
-    (scaled by ``grad_scale``, e.g. 1 for a plain mean).  Returns a 1-element fp32 tensor."""
+    (scaled by ``grad_scale``, e.g. 1 for a plain mean).  Returns a 1-element fp32 tensor.  With a tensor-parallel
+    communicator ``logits`` are this rank's rows: the mean is over ALL rows and the result is this rank's share."""
     T = logits.shape[0]
-    rows = F.xent_fwd_bwd(logits, targets.reshape(-1), grad_scale / T, True)
+    targets = targets.reshape(-1)
+    if tp is not None:
+        targets = targets[tp.rank * tp.rows:(tp.rank + 1) * tp.rows]
+        T = T * tp.tp
+    rows = F.xent_fwd_bwd(logits, targets, grad_scale / T, True)
     loss = torch.zeros(1, dtype=torch.float32, device=logits.device)
     F.reduce_sum(rows, loss, 1.0 / T)
     st["dlogits"] = logits

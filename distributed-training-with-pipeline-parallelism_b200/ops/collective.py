@@ -230,3 +230,81 @@ class TensorParallelMLP:
         linear_reducescatter(h, self.w2, self.y_sym.ptrs, self.d)
         self.y_sym.barrier(1)                       # all partial sums have landed
         return self.y_sym.tensor
+
+
+class TPComm:
+    """Tensor-parallel communicator of one pipeline stage: the two fused compute+collective ops every sharded
+    linear layer needs, with sequence-parallel activations ([T/tp, d] row shards) on both sides.
+
+        ag_linear : [T/tp, d] shard  --all-gather -> GEMM (K12)-->  [T, N_local]      (column-parallel weights)
+        linear_rs : [T, K_local]     --GEMM -> reduce-scatter (K11)-->  [T/tp, d] fp32 (row-parallel weights)
+
+    On CUDA the shards live in symmetric memory and the kernels read / reduce-add peer memory over NVLink; buffers
+    are double-buffered so ONE device-side barrier per op is enough (all shards written / all partial sums landed):
+    passing the barrier of op k+1 proves every rank finished op k, so the buffer of op k may be rewritten at k+2.
+    On CPU (gloo) the same interface runs all_gather / all_reduce + matmul, which is what the multi-process CPU tests
+    check the sharded layer program against.  Every AG input and every RS output of a transformer layer has d
+    columns, so two [T/tp, d] buffers per direction serve the whole stage."""
+
+    def __init__(self, group, rows: int, d: int, device: torch.device):
+        import torch.distributed as dist
+        self.group = group
+        self.tp = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.rows, self.d = int(rows), int(d)
+        self.device = torch.device(device)
+        self.cuda = self.device.type == "cuda"
+        if self.cuda:
+            self.x_sym = [SymmetricBuffer((self.rows, self.d), torch.bfloat16, self.device, group) for _ in range(2)]
+            self.y_sym = [SymmetricBuffer((self.rows, self.d), torch.float32, self.device, group) for _ in range(2)]
+            self.kx = self.ky = 0
+            self.x_sym[0].barrier(0)   # every rank's zeroed reduce-scatter buffers exist before the first push
+
+    # ---- all-gather -> GEMM -------------------------------------------------------------------------------------
+    def ag_linear(self, x_shard: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                  act: Optional[str] = None, w_mn_major: bool = False, need_full: bool = True):
+        """(act(gather(x_shard) @ op(w) + bias), gather(x_shard) or None).  w is [N, d] (or [d, N] when w_mn_major)."""
+        import torch.distributed as dist
+        if not self.cuda:
+            full = torch.empty((self.rows * self.tp, self.d), dtype=x_shard.dtype)
+            dist.all_gather_into_tensor(full, x_shard.contiguous(), group=self.group)
+            y = full @ (w if w_mn_major else w.t())
+            if bias is not None:
+                y = y + bias
+            if act == "relu":
+                y = torch.relu(y)
+            elif act == "gelu":
+                y = torch.nn.functional.gelu(y)
+            return y, (full if need_full else None)
+        buf = self.x_sym[self.kx]
+        self.kx ^= 1
+        buf.tensor.copy_(x_shard)
+        buf.barrier(0)
+        out = allgather_linear(buf.ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major)
+        full = None
+        if need_full:   # the weight-gradient GEMM of this layer wants the gathered rows as its own operand
+            full = torch.empty((self.rows * self.tp, self.d), dtype=torch.bfloat16, device=self.device)
+            for r in range(self.tp):
+                src = buf.tensor if r == self.rank else buf.hdl.get_buffer(r, (self.rows, self.d), torch.bfloat16)
+                full[r * self.rows:(r + 1) * self.rows].copy_(src)
+        return out, full
+
+    # ---- GEMM -> reduce-scatter ---------------------------------------------------------------------------------
+    def linear_rs(self, x: torch.Tensor, w: torch.Tensor, w_mn_major: bool = False) -> torch.Tensor:
+        """Rows of sum_over_ranks(x_r @ op(w_r)) owned by this rank, fp32 [T/tp, d].  The result is valid until the
+        second-next call (copy or convert it right away).  w is [d, K_local] (or [K_local, d] when w_mn_major)."""
+        import torch.distributed as dist
+        if not self.cuda:
+            y = (x @ (w if w_mn_major else w.t())).float()
+            dist.all_reduce(y, group=self.group)
+            return y[self.rank * self.rows:(self.rank + 1) * self.rows]
+        cur, other = self.y_sym[self.ky], self.y_sym[self.ky ^ 1]
+        self.ky ^= 1
+        other.tensor.zero_()   # consumed two calls ago; peers start adding to it only after the barrier below
+        linear_reducescatter(x, w, cur.ptrs, self.d, w_mn_major=w_mn_major)
+        cur.barrier(1)
+        return cur.tensor
+
+    def all_reduce(self, t: torch.Tensor) -> None:
+        import torch.distributed as dist
+        dist.all_reduce(t, group=self.group)

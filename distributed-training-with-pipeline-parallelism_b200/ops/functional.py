@@ -141,6 +141,18 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw_accum: torch.Tensor,
         _lib.count_launch()
 
 
+def colsum_accum(dy: torch.Tensor, db_accum: torch.Tensor) -> None:
+    """db_accum[out] += colsum(dy)  (bias gradient without its weight-gradient GEMM)."""
+    _check_2d(dy, "dy")
+    if not _is_cuda(dy):
+        db_accum.add_(dy.float().sum(0).to(db_accum.dtype))
+        return
+    lib = _lib_required()
+    _lib.check(lib.ppb_colsum_accum(dy.data_ptr(), dy.stride(0), db_accum.data_ptr(), dy.shape[0], dy.shape[1], _stream()),
+               "ppb_colsum_accum")
+    _lib.count_launch()
+
+
 # ------------------------------------------------------------------------------------------------------------
 # fused residual + dropout + norm
 # ------------------------------------------------------------------------------------------------------------

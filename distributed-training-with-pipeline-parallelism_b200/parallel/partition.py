@@ -36,13 +36,14 @@ def balanced_ranges(n_layers: int, num_stages: int, args: Optional[ModelArgs] = 
         layer_cost, head_cost = 1.0, 1.0
     else:
         # FLOPs per token weighted by the efficiency each part reaches on B200, calibrated on measured per-action
-        # times (profiles/: a decoder layer 1.3 ms, embedding+head+loss 1.05 ms per 4096-token micro-batch): the
-        # vocabulary-sized head GEMMs run near the tensor-core roofline (~0.9), the d x d / d x f GEMMs of a layer at
-        # ~0.35, attention (exp-bound softmax) at ~0.12; the cross-entropy pass is HBM-bound.
+        # times (profiles/bench_r1_n4_1f1b_v2.json: forward+backward of a decoder layer 1.00 ms, of embedding + final
+        # norm + head + loss 1.46 ms per 4096-token micro-batch): the vocabulary-sized head GEMMs run near the
+        # tensor-core roofline (~0.9), the d x d / d x f GEMMs of a layer at ~0.40, attention (exp-bound softmax) at
+        # ~0.20; the cross-entropy pass is HBM-bound (reads and rewrites the [tokens, V] logits).
         d, f, V = args.dim, args.ffn_dim, args.vocab_size
         blocks = 2 if args.cross_attn else 1
-        layer_cost = (blocks * 8 * d * d + 4 * d * f) / 0.35 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.12
-        head_cost = 2 * d * V / 0.9 + 40.0 * V
+        layer_cost = (blocks * 8 * d * d + 4 * d * f) / 0.40 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
+        head_cost = 2 * d * V / 0.9 + 650.0 * V
     # DP over (stage, first layer of the stage): minimise (most expensive stage, then sum of squared costs);
     # every stage gets at least one layer when there are enough layers.
     INF = (float("inf"), float("inf"))

@@ -60,6 +60,9 @@ class PipelineSchedule:
         else:
             self.pp_size, self.pp_rank, self.dp_size = 1, 0, 1
         self.n_virtual = len(self.stages)
+        self.tp_size = self.stages[0].tp_size
+        if any(st.tp_size != self.tp_size for st in self.stages):
+            raise ValueError("all stages of a rank must use the same tensor-parallel degree")
         self.num_stages = self.pp_size * self.n_virtual
         for st in self.stages:
             if st.num_stages != self.num_stages:
@@ -95,7 +98,7 @@ class PipelineSchedule:
         # CUDA graphs: one forward + one backward graph per (stage, in-flight slot); eager for the first steps
         import os
         want = (os.environ.get("PPB_CUDA_GRAPHS", "1") != "0") if cuda_graphs is None else cuda_graphs
-        self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None)
+        self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None and self.tp_size == 1)
         self.graph_warmup_steps = graph_warmup_steps
         if self.use_graphs:
             for st in self.stages:
@@ -178,9 +181,10 @@ class PipelineSchedule:
     def _ring_buf(self, stage: int, kind: str, mb: int, b: int, S: int) -> torch.Tensor:
         key = (stage, kind, mb)
         buf = self._ring.get(key)
-        if buf is None or buf.shape[0] != b:
+        if buf is None or buf.shape[0] != (b if self.tp_size == 1 else b * S // self.tp_size):
             st = self.local[stage]
-            buf = torch.empty((b, S, st.args.dim), dtype=st.dtype, device=self.device)
+            shape = (b, S, st.args.dim) if self.tp_size == 1 else (b * S // self.tp_size, st.args.dim)
+            buf = torch.empty(shape, dtype=st.dtype, device=self.device)
             self._ring[key] = buf
         return buf
 
@@ -196,6 +200,11 @@ class PipelineSchedule:
         y_chunks = list(torch.tensor_split(target, self.m, dim=0)) if (target is not None and last_stage in self.local) else None
         for st in self.stages:
             st.begin_step()
+            st.seq_len = S
+        tp = self.tp_size
+
+        def act_view(t, b):   # stage boundary tensors: [b, S, d], or this tp rank's [b*S/tp, d] rows
+            return t.view(b, S, -1) if tp == 1 else t.view(b * S // tp, -1)
 
         cuda = self.cuda
         compute = torch.cuda.current_stream(self.device) if cuda else None
@@ -258,7 +267,7 @@ class PipelineSchedule:
                         t = bwd_out.pop((a.stage, a.mb))
                         dst_stage = a.stage - 1
                         grp = self.pp_group_bwd
-                    t = t.view(sizes[a.mb], S, -1)
+                    t = act_view(t, sizes[a.mb])
                     dst = self._global_rank(self._rank_of_stage(dst_stage))
                     w = dist.isend(t, dst=dst, group=grp)
                     send_works.append(w)
@@ -283,7 +292,7 @@ class PipelineSchedule:
                     timeline.append((a, t0, tick()))
                     if a.stage != last_stage:
                         if self._rank_of_stage(a.stage + 1) == self.pp_rank:
-                            local_in[(a.stage + 1, "F", a.mb)] = out.view(sizes[a.mb], S, -1)
+                            local_in[(a.stage + 1, "F", a.mb)] = act_view(out, sizes[a.mb])
                         else:
                             fwd_out[(a.stage, a.mb)] = out
                 elif typ == T.B:
@@ -307,7 +316,7 @@ class PipelineSchedule:
                     timeline.append((a, t0, tick()))
                     if a.stage != 0:
                         if self._rank_of_stage(a.stage - 1) == self.pp_rank:
-                            local_in[(a.stage - 1, "B", a.mb)] = din.view(sizes[a.mb], S, -1)
+                            local_in[(a.stage - 1, "B", a.mb)] = act_view(din, sizes[a.mb])
                         else:
                             bwd_out[(a.stage, a.mb)] = din
                 elif typ == T.I:
@@ -326,7 +335,7 @@ class PipelineSchedule:
                     timeline.append((a, t0, tick()))
                     if a.stage != 0:
                         if self._rank_of_stage(a.stage - 1) == self.pp_rank:
-                            local_in[(a.stage - 1, "B", a.mb)] = din.view(sizes[a.mb], S, -1)
+                            local_in[(a.stage - 1, "B", a.mb)] = act_view(din, sizes[a.mb])
                         else:
                             bwd_out[(a.stage, a.mb)] = din
                 elif typ == T.W:
@@ -338,6 +347,7 @@ class PipelineSchedule:
                         self.local[a.stage].backward_weight_one_chunk(a.mb, last=b_count[a.stage] == self.m)
                     timeline.append((a, t0, tick()))
                 elif typ == T.REDUCE_GRAD:
+                    self.local[a.stage].reduce_tp_grads()
                     # micro-batch averaging: folded into the optimizer kernel; done explicitly when there is none
                     if self.optimizer is None and self.scale_grads and self.local[a.stage].n_total:
                         self.local[a.stage].grad.mul_(1.0 / self.m)

@@ -27,7 +27,7 @@ class PipelineStage:
     """A stage of the pipeline.  ``submod`` is a (possibly pruned) :class:`Transformer`."""
 
     def __init__(self, submodule: Transformer, stage_index: int, num_stages: int, device: torch.device,
-                 group=None, dp_group=None):
+                 group=None, dp_group=None, tp_group=None):
         if not (0 <= stage_index < num_stages):
             raise ValueError(f"stage_index {stage_index} out of range for {num_stages} stages")
         self.submod = submodule
@@ -36,6 +36,13 @@ class PipelineStage:
         self.device = torch.device(device)
         self.group = group
         self.dp_group = dp_group
+        # intra-stage tensor parallelism (models/tp.py): ``submodule`` must already hold this rank's shards
+        self.tp_group = tp_group
+        self.tp_size = int(getattr(submodule, "tp_size", 1))
+        self.tp = None            # ops.collective.TPComm, created on the first forward (needs the micro-batch geometry)
+        self.seq_len = None       # set by the runner: activations between tensor-parallel stages are [b*S/tp, d] rows
+        if self.tp_size > 1 and tp_group is None:
+            raise ValueError("a tensor-parallel sharded model needs its tp_group")
         self.is_first = stage_index == 0
         self.is_last = stage_index == num_stages - 1
         self.args = submodule.args
@@ -81,6 +88,7 @@ class PipelineStage:
         self.exp_avg_sq = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
         self.sink = GradSink()
         self.param_names = []
+        self.tp_replicated: List[tuple] = []   # (offset, numel) of parameters every tp rank holds in full
         with torch.no_grad():
             for (n, p), o in zip(ordered, offs):
                 view = self.param_arena[o:o + p.numel()].view(p.shape)
@@ -93,6 +101,8 @@ class PipelineStage:
                 p.data = view
                 self.sink.bind(p, self.grad[o:o + p.numel()].view(p.shape))
                 self.param_names.append((n, o, tuple(p.shape)))
+                if self.tp_size > 1 and getattr(p, "_tp_replicated", True):
+                    self.tp_replicated.append((o, p.numel()))
         self.clip_sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
         self.clip_coef = torch.ones(1, dtype=torch.float32, device=dev)
         if dev.type == "cuda":
@@ -114,7 +124,7 @@ class PipelineStage:
         import os
         import torch.distributed as dist
         if (self.device.type != "cuda" or self.dp_group is None or dist.get_world_size(self.dp_group) == 1
-                or self.n_total == 0 or os.environ.get("PPB_FUSED_DP", "1") == "0"):
+                or self.n_total == 0 or self.tp_size > 1 or os.environ.get("PPB_FUSED_DP", "1") == "0"):
             return False
         from ..ops.collective import FusedGradAllReduce
         dp = dist.get_world_size(self.dp_group)
@@ -181,7 +191,16 @@ class PipelineStage:
         # on CUDA the offset lives in device memory (set right before the launches of a micro-batch), so the seeds
         # baked into captured kernels are micro-batch independent; the CPU program adds the same number on the host
         off = 0 if self.device.type == "cuda" else self._mb_offset(mb)
-        return Ctx(self.args, batch, seq, self.base_seed, 0, self.training, off)
+        ctx = Ctx(self.args, batch, seq, self.base_seed, 0, self.training, off)
+        if self.tp_size > 1:
+            rows = batch * seq // self.tp_size
+            if batch * seq % self.tp_size or (self.tp is not None and self.tp.rows != rows):
+                raise ValueError(f"tensor parallelism needs equal micro-batches with b*S divisible by tp (got {batch}x{seq})")
+            if self.tp is None:
+                from ..ops.collective import TPComm
+                self.tp = TPComm(self.tp_group, rows, self.args.dim, self.device)
+            ctx.tp = self.tp
+        return ctx
 
     def forward_one_chunk(self, mb: int, inp: torch.Tensor, target: Optional[torch.Tensor] = None,
                           loss_scale: float = 1.0, loss_fn=None) -> torch.Tensor:
@@ -190,7 +209,13 @@ class PipelineStage:
         logits in place).  Returns the stage output ([b*S, d] activations or logits)."""
         if not self._materialized:
             self.materialize()
-        b, S = inp.shape[0], inp.shape[1]
+        if self.tp_size > 1 and not self.is_first:   # [b*S/tp, d] rows from the previous tensor-parallel stage
+            S = self.seq_len if self.seq_len is not None else (target.shape[1] if target is not None else None)
+            if S is None:
+                raise ValueError("a tensor-parallel stage needs seq_len (set by the runner) to interpret its input rows")
+            b = inp.reshape(-1, self.args.dim).shape[0] * self.tp_size // S
+        else:
+            b, S = inp.shape[0], inp.shape[1]
         ctx = self._ctx(mb, b, S)
         st: dict = {}
         if self.device.type == "cuda":
@@ -199,7 +224,11 @@ class PipelineStage:
             out = stage_forward(self.submod, inp, ctx, st)
             if self.is_last and target is not None and self.submod.output is not None:
                 if loss_fn is None:
-                    self.losses[mb] = stage_loss(out, target, loss_scale, st)
+                    self.losses[mb] = stage_loss(out, target, loss_scale, st, ctx.tp)
+                    if ctx.tp is not None:   # every rank holds its rows' share of the mean; report the mean
+                        ctx.tp.all_reduce(self.losses[mb])
+                elif ctx.tp is not None:
+                    raise NotImplementedError("python loss_fn with tensor parallelism: use the fused loss (loss_fn=None)")
                 else:  # arbitrary user loss: one autograd hop over the logits only
                     with torch.enable_grad():
                         lg = out.detach().float().view(b, S, -1).requires_grad_(True)
@@ -211,7 +240,7 @@ class PipelineStage:
         self.stash[mb] = st
         self.ctxs[mb] = ctx
         if self.is_last and "dlogits" not in st:
-            self.outputs[mb] = out.view(b, S, -1)
+            self.outputs[mb] = out.view(b, S, -1) if ctx.tp is None else out
         return out
 
     def backward_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None, last: bool = False) -> Optional[torch.Tensor]:
@@ -407,6 +436,21 @@ class PipelineStage:
         return self.backward_one_chunk(mb, dout, last=last)
 
     # ---- gradient reduction + optimizer ---------------------------------------------------------------------------
+    def reduce_tp_grads(self) -> None:
+        """Sum, over the tensor-parallel group, the gradients of the parameters every tp rank holds in full (norms,
+        row-parallel biases, embedding, head): each rank computed them on its own token rows only.  One packed
+        all-reduce per step."""
+        if self.tp_size == 1 or not self.tp_replicated:
+            return
+        import torch.distributed as dist
+        flat = torch.cat([self.grad[o:o + n] for o, n in self.tp_replicated])
+        dist.all_reduce(flat, group=self.tp_group)
+        i = 0
+        for o, n in self.tp_replicated:
+            self.grad[o:o + n].copy_(flat[i:i + n])
+            i += n
+
+
     def all_reduce_grads(self, async_op: bool = False):
         """Data-parallel all-reduce of the whole gradient arena in one collective (baseline path: NCCL/gloo;
         the fused in-kernel path lives in ops.collective)."""

@@ -115,3 +115,68 @@ def train_worker(rank, world_size, schedule_type, results_queue, master_port=Non
     except Exception as e:  # noqa: BLE001
         traceback.print_exc()
         results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_port=None, act="gelu", norm="rmsnorm",
+                     split_bw=False):
+    """(pp x tp) mesh, pre-LN block: loss and per-parameter gradients (each rank's SHARD of them) must equal the
+    single-process full-model ones."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.models.tp import shard_model_for_tp, shard_tensor
+        from ppb200.api import make_schedule
+        from ppb200.parallel.partition import prune_to_stage
+        from ppb200.parallel.stage import PipelineStage
+        from ppb200.parallel.mesh import init_mesh
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        mesh = init_mesh(dp_size=1, pp_size=world_size // tp, tp_size=tp)
+        P = mesh.pp_size
+        args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0, causal=True,
+                         cross_attn=False, activation=act, norm_first=True, norm=norm)
+        torch.manual_seed(4321)
+        full = Transformer(args)
+        B, S = 8, 16
+        g = torch.Generator().manual_seed(7)
+        x = torch.randint(0, 101, (B, S), generator=g)
+        y = torch.randint(0, 101, (B, S), generator=g)
+        oracle = copy.deepcopy(full)
+        loss_ref = torch.nn.functional.cross_entropy(oracle(x).reshape(-1, 101), y.reshape(-1))
+        loss_ref.backward()
+        ref_grads = {n: p.grad.clone() for n, p in oracle.named_parameters()}
+        mdl = copy.deepcopy(full)
+        prune_to_stage(mdl, mesh.pp_idx, P)
+        shard_model_for_tp(mdl, mesh.tp_idx, tp)
+        st = PipelineStage(mdl, mesh.pp_idx, P, torch.device("cpu"), tp_group=mesh.tp_group)
+        custom = None
+        if split_bw:
+            from ppb200.parallel.schedule import zero_bubble_order
+            custom = zero_bubble_order(P, m)
+        sched = make_schedule("1F1B", st, m, None, pp_group=mesh.pp_group, pp_group_bwd=mesh.pp_group_bwd, optimizer=None,
+                              actions=custom)
+        losses = []
+        first, last = 0 in sched.local, (P - 1) in sched.local
+        sched.step(*((x,) if first else ()), target=y if last else None, losses=losses if last else None)
+        max_err = 0.0
+        worst = ""
+        for n, gview in st.grad_views().items():
+            want = shard_tensor(n, ref_grads[n], args.n_heads, mesh.tp_idx, tp)
+            err = (gview - want).abs().max().item() / (want.abs().max().item() + 1e-8)
+            if err > max_err:
+                max_err, worst = err, n
+        out = {"rank": rank, "max_rel_grad_err": max_err, "worst": worst}
+        if last:
+            lp = torch.stack([l.reshape(()) for l in losses]).mean()
+            out["loss_err"] = abs(lp.item() - loss_ref.item())
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, out)
+        if rank == 0:
+            results_queue.put({"ranks": gathered})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

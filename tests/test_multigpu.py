@@ -44,3 +44,17 @@ def test_tensor_parallel_mlp_fused_kernels():
     out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_tp_check.py")])
     res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
     assert res["max_rel_err"] < 2e-2, res
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("act", ["gelu", "relu"])
+def test_tensor_parallel_stage_matches_single_gpu(act):
+    os.environ["ACT"] = act
+    try:
+        out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_tp_stage_check.py")])
+    finally:
+        os.environ.pop("ACT", None)
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert abs(res["loss_tp"] - res["loss_ref"]) < 5e-3 * abs(res["loss_ref"]), res
+    assert res["grad_rel_err_max"] < 3e-2, res          # bf16 activations, different GEMM tilings / summation orders
+    assert res["train_tp"][-1] < res["train_tp"][0] and abs(res["train_tp"][-1] - res["train_ref"][-1]) < 0.05, res

@@ -87,3 +87,32 @@ def test_custom_action_lists_single_rank(tmp_path):
     with pytest.raises(ValueError):      # W without its I
         make_schedule("1F1B", manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu")), 1, None, actions={0: ["0F0", "0W0"]})
     assert ir.from_csv(csv.read_text())[0][2].type.value == "I"
+
+
+@pytest.mark.parametrize("world,tp,n_layers,m,act,norm,split", [
+    (2, 2, 2, 2, "gelu", "rmsnorm", False),      # pure tensor parallel
+    (4, 2, 4, 4, "relu", "layernorm", False),    # pp2 x tp2
+    (4, 2, 4, 4, "gelu", "rmsnorm", True),       # pp2 x tp2 with split backward (I/W) actions
+])
+def test_tensor_parallel_stage_matches_single_process(world, tp, n_layers, m, act, norm, split):
+    from tests._workers import tp_parity_worker
+    res = launch_workers(tp_parity_worker, world, (tp, n_layers, m), {"act": act, "norm": norm, "split_bw": split}, timeout=400)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["max_rel_grad_err"] < 2e-4, r
+        if "loss_err" in r:
+            assert r["loss_err"] < 1e-5, r
+
+
+def test_tp_shard_merge_roundtrip():
+    import torch
+    from ppb200.models import ModelArgs, Transformer
+    from ppb200.models.tp import merge_tp_shards, shard_tensor
+    args = ModelArgs(dim=32, n_layers=2, n_heads=4, vocab_size=50, ffn_dim=48, dropout=0.0, causal=True, cross_attn=False,
+                     norm_first=True)
+    sd = Transformer(args).state_dict()
+    shards = [{k: shard_tensor(k, v, 4, r, 2) for k, v in sd.items()} for r in range(2)]
+    assert shards[0]["layers.0.self_attn.in_proj_weight"].shape == (48, 32)
+    assert shards[0]["layers.0.linear2.weight"].shape == (32, 24)
+    merged = merge_tp_shards(shards, 4)
+    assert all(torch.equal(merged[k], sd[k]) for k in sd)
