@@ -25,21 +25,27 @@ class ModelArgs:
     dropout: float = 0.1         # live in the reference (modules stay in train mode)
     causal: bool = False         # the reference passes no tgt_mask (helper:52)
     cross_attn: bool = True      # layer(h, h): cross-attention whose memory is the layer input
-    activation: str = "relu"     # 'relu' | 'gelu'
+    activation: str = "relu"     # 'relu' | 'gelu' | 'swiglu' (pre-LN block only; linear1 packs gate|up = [2*ffn_dim, dim])
     norm_first: bool = False     # post-LN like the reference; True = GPT-style pre-LN
     norm: str = "layernorm"      # 'layernorm' | 'rmsnorm'
     layer_norm_eps: float = 1e-5
+    rope: bool = False           # rotary position embedding on q, k (pre-LN block only); the reference has no positions
+    rope_theta: float = 10000.0
     dtype: torch.dtype = torch.float32   # parameter/activation dtype: fp32 on CPU, bf16 on B200
 
     def __post_init__(self):
         if self.dim % self.n_heads != 0:
             raise ValueError(f"dim ({self.dim}) must be divisible by n_heads ({self.n_heads})")
-        if self.activation not in ("relu", "gelu"):
+        if self.activation not in ("relu", "gelu", "swiglu"):
             raise ValueError(f"unknown activation {self.activation!r}")
         if self.norm not in ("layernorm", "rmsnorm"):
             raise ValueError(f"unknown norm {self.norm!r}")
         if self.norm_first and self.cross_attn:
             raise ValueError("the pre-LN (GPT) block has no cross-attention; set cross_attn=False")
+        if (self.activation == "swiglu" or self.rope) and not self.norm_first:
+            raise ValueError("swiglu / rope are implemented for the pre-LN block (norm_first=True)")
+        if self.rope and (self.dim // self.n_heads) % 16:
+            raise ValueError("rope needs head_dim % 16 == 0")
 
     @property
     def head_dim(self) -> int:
@@ -48,7 +54,8 @@ class ModelArgs:
     def params_per_layer(self) -> int:
         d, f = self.dim, self.ffn_dim
         attn = 4 * d * d + 4 * d
-        n = attn * (2 if self.cross_attn else 1) + 2 * d * f + f + d
+        up = 2 if self.activation == "swiglu" else 1
+        n = attn * (2 if self.cross_attn else 1) + (1 + up) * d * f + up * f + d
         n += (3 if self.cross_attn else 2) * 2 * d
         return n
 
@@ -60,7 +67,7 @@ class ModelArgs:
         """fwd+bwd model FLOPs per token (3 x forward; attention counted un-masked unless causal)."""
         d, f, V = self.dim, self.ffn_dim, self.vocab_size
         attn_blocks = 2 if self.cross_attn else 1
-        gemm = 2 * (attn_blocks * 4 * d * d + 2 * d * f)
+        gemm = 2 * (attn_blocks * 4 * d * d + (3 if self.activation == "swiglu" else 2) * d * f)
         attn = attn_blocks * 4 * seq_len * d * (0.5 if self.causal else 1.0)
         return 3.0 * (self.n_layers * (gemm + attn) + 2 * d * V)
 
@@ -77,7 +84,10 @@ PRESETS: Dict[str, ModelArgs] = {
                              cross_attn=False, activation="gelu", norm_first=True),
     "gpt2-xl": ModelArgs(dim=1600, n_layers=48, n_heads=25, vocab_size=50257, ffn_dim=6400, causal=True,
                          cross_attn=False, activation="gelu", norm_first=True),
-    # Llama-style width/depth with the GPT block (RMSNorm, causal); SwiGLU/RoPE are not implemented yet
+    # Llama width/depth with the GPT (GELU, learned-position-free) block: the pre-SwiGLU/RoPE comparison point
+    # Llama-style block: pre-LN RMSNorm, causal attention with rotary embeddings, SwiGLU FFN, no dropout
+    "llama-7b": ModelArgs(dim=4096, n_layers=32, n_heads=32, vocab_size=32000, ffn_dim=11008, causal=True, cross_attn=False,
+                          activation="swiglu", norm_first=True, norm="rmsnorm", dropout=0.0, rope=True),
     "llama-7b-shape": ModelArgs(dim=4096, n_layers=32, n_heads=32, vocab_size=32000, ffn_dim=11008, causal=True,
                                 cross_attn=False, activation="gelu", norm_first=True, norm="rmsnorm", dropout=0.0),
 }

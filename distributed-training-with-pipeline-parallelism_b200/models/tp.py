@@ -34,6 +34,7 @@ from ..ops import functional as F
 
 SHARD_DIM = {"self_attn.in_proj_weight": "qkv0", "self_attn.in_proj_bias": "qkv0", "self_attn.out_proj.weight": 1,
              "linear1.weight": 0, "linear1.bias": 0, "linear2.weight": 1}
+# with activation == 'swiglu' linear1 packs gate | up on dim 0: each half is split separately ("pair0")
 
 
 def _shard_key(name: str):
@@ -43,10 +44,14 @@ def _shard_key(name: str):
     return None
 
 
-def shard_tensor(name: str, t: torch.Tensor, n_heads: int, tp_rank: int, tp_size: int) -> torch.Tensor:
+def shard_tensor(name: str, t: torch.Tensor, n_heads: int, tp_rank: int, tp_size: int, swiglu: bool = False) -> torch.Tensor:
     dim = _shard_key(name)
     if dim is None:
         return t
+    if swiglu and name.endswith(("linear1.weight", "linear1.bias")):
+        v = t.reshape(2, t.shape[0] // 2, *t.shape[1:])
+        n = v.shape[1]
+        return v[:, tp_rank * n // tp_size:(tp_rank + 1) * n // tp_size].reshape(-1, *t.shape[1:]).contiguous()
     if dim == "qkv0":
         H = n_heads
         v = t.reshape(3, H, t.shape[0] // (3 * H), *t.shape[1:])
@@ -75,14 +80,15 @@ def shard_model_for_tp(model, tp_rank: int, tp_size: int):
         parts = name.split(".")
         for part in parts[:-1]:
             mod = getattr(mod, part) if not isinstance(mod, nn.ModuleDict) else mod[part]
-        new = nn.Parameter(shard_tensor(name, p.data, a.n_heads, tp_rank, tp_size), requires_grad=p.requires_grad)
+        new = nn.Parameter(shard_tensor(name, p.data, a.n_heads, tp_rank, tp_size, a.activation == "swiglu"),
+                           requires_grad=p.requires_grad)
         new._tp_replicated = False
         setattr(mod, parts[-1], new)
     model.tp_rank, model.tp_size = tp_rank, tp_size
     return model
 
 
-def merge_tp_shards(shards: Sequence[Dict[str, torch.Tensor]], n_heads: int) -> Dict[str, torch.Tensor]:
+def merge_tp_shards(shards: Sequence[Dict[str, torch.Tensor]], n_heads: int, swiglu: bool = False) -> Dict[str, torch.Tensor]:
     """Inverse of ``shard_tensor`` over whole state dicts: tp shards (same stage) -> the reference-layout state dict."""
     tp = len(shards)
     out: Dict[str, torch.Tensor] = {}
@@ -91,6 +97,9 @@ def merge_tp_shards(shards: Sequence[Dict[str, torch.Tensor]], n_heads: int) -> 
         ts = [sd[name] for sd in shards]
         if dim is None:
             out[name] = ts[0].clone()
+        elif swiglu and name.endswith(("linear1.weight", "linear1.bias")):
+            vs = [t.reshape(2, t.shape[0] // 2, *t.shape[1:]) for t in ts]
+            out[name] = torch.cat(vs, dim=1).reshape(-1, *ts[0].shape[1:]).contiguous()
         elif dim == "qkv0":
             hl = n_heads // tp
             vs = [t.reshape(3, hl, t.shape[0] // (3 * hl), *t.shape[1:]) for t in ts]
@@ -121,11 +130,17 @@ def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> t
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
     qkv, y1_full = tp.ag_linear(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    if a.rope:
+        F.rope_(qkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta)
     o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, 0.0, 0)
     a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x_in.dtype)
     z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, 0.0, 0, rms)
     if a.activation == "relu":
         h, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias, "relu")
+    elif a.activation == "swiglu":
+        hpre, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias)    # [T, 2f/tp]: local gate | local up
+        h = F.swiglu_fwd(hpre)
+        st["hpre"] = hpre
     else:
         hpre, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias)
         h = F.gelu_fwd(hpre)
@@ -148,6 +163,8 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     G.bias_grad(g, G(L.linear2.bias))
     if a.activation == "relu":
         dh = torch.where(st["h"] > 0, dh, torch.zeros_like(dh))
+    elif a.activation == "swiglu":
+        dh = F.swiglu_bwd(dh, st["hpre"])
     else:
         dh = _gelu_bwd(dh, st["hpre"])
     # linear1 (column-parallel):  dW1_local += dh^T gather(y3) ;  d y3 rows = reduce-scatter(dh @ W1_local)
@@ -163,6 +180,8 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     dqkv = torch.empty_like(qkv)
     F.attention_bwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], st["o1"], do1, st["lse1"], ctx.B, Hl, a.causal, None,
                     0.0, 0, out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
+    if a.rope:
+        F.rope_(dqkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta, inverse=True)
     G.wgrad(dqkv, st["y1_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
     dy1 = tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True).to(g.dtype)
     dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),

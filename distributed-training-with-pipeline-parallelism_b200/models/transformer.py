@@ -81,7 +81,7 @@ class DecoderLayer(nn.Module):
         self.self_attn = _Attn(d, dt)
         if args.cross_attn:
             self.multihead_attn = _Attn(d, dt)
-        self.linear1 = _Proj(d, args.ffn_dim, dt)
+        self.linear1 = _Proj(d, args.ffn_dim * (2 if args.activation == "swiglu" else 1), dt)   # swiglu: gate | up
         self.linear2 = _Proj(args.ffn_dim, d, dt)
         self.norm1 = _Norm(d, dt, rms)
         if args.cross_attn:
@@ -168,6 +168,8 @@ def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ct
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
     qkv = F.linear_fwd(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    if a.rope:   # q and k are adjacent column blocks of the packed activation: one in-place pass over 2H heads
+        F.rope_(qkv, 0, ctx.S, 2 * H, d // H, a.rope_theta)
     o1, lse1 = F.attention_fwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], ctx.B, H, a.causal, None, p,
                                ctx.seed(layer_id, SITE_ATTN1))
     a1 = F.linear_fwd(o1, L.self_attn.out_proj.weight, L.self_attn.out_proj.bias)
@@ -177,6 +179,10 @@ def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ct
     if a.activation == "relu":
         h = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
         st["h"] = h
+    elif a.activation == "swiglu":
+        hpre = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias)     # [T, 2f]: gate | up
+        h = F.swiglu_fwd(hpre)
+        st.update(hpre=hpre, h=h)
     else:
         hpre = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias)
         h = F.gelu_fwd(hpre)
@@ -195,6 +201,8 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
     G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
     if a.activation == "relu":
         dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
+    elif a.activation == "swiglu":
+        dh = F.swiglu_bwd(F.linear_dgrad(da3, L.linear2.weight), st["hpre"])
     else:
         dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
     G.wgrad(dh, st["y3"], G(L.linear1.weight), G(L.linear1.bias))
@@ -208,6 +216,8 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
     dqkv = torch.empty_like(qkv)
     F.attention_bwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], st["o1"], do1, st["lse1"], ctx.B, H, a.causal, None, p,
                     ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
+    if a.rope:   # gradient of a rotation = the transpose rotation
+        F.rope_(dqkv, 0, ctx.S, 2 * H, d // H, a.rope_theta, inverse=True)
     G.wgrad(dqkv, st["y1"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
     dy1 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
     dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),

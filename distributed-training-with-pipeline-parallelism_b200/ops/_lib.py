@@ -44,6 +44,9 @@ def _declare(lib) -> None:
         "ppb_add_dropout_fwd": [P, P, P, L, F, U, P],
         "ppb_sum_dropout_bwd": [P, P, P, P, P, L, F, U, P],
         "ppb_cast_f32_to_bf16": [P, P, L, P],
+        "ppb_swiglu_fwd": [P, L, P, L, L, I, P],
+        "ppb_swiglu_bwd": [P, L, P, L, P, L, L, I, P],
+        "ppb_rope_inplace": [P, L, I, L, I, I, I, P, I, P],
         "ppb_attn_fwd": [P, P, P, P, P, I, I, I, I, I, L, L, L, L, I, I, I, F, F, U, P],
         "ppb_attn_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, L, L, L, L, I, I, I, F, F, U, P],
         "ppb_attn_bwd_scratch_bytes": [I, I, I, I],

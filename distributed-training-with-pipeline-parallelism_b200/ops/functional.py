@@ -496,3 +496,60 @@ def attention_bwd(q, k, v, o, do, lse, B: int, H: int, causal: bool = False, sca
     _lib.check(rc, "ppb_attn_bwd")
     _lib.count_launch(3)
     return dq, dk, dv
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Llama-style pieces: SwiGLU, rotary position embedding (csrc/llama_ops.cu)
+# ------------------------------------------------------------------------------------------------------------
+def swiglu_fwd(gu: torch.Tensor) -> torch.Tensor:
+    """h [T, f] = silu(gu[:, :f]) * gu[:, f:]  (gu = packed gate/up output of linear1)."""
+    _check_2d(gu, "gu")
+    if not _is_cuda(gu):
+        return ref.swiglu_fwd(gu)
+    T, f = gu.shape[0], gu.shape[1] // 2
+    h = torch.empty((T, f), dtype=gu.dtype, device=gu.device)
+    lib = _lib_required()
+    _lib.check(lib.ppb_swiglu_fwd(gu.data_ptr(), gu.stride(0), h.data_ptr(), h.stride(0), T, f, _stream()), "ppb_swiglu_fwd")
+    _lib.count_launch()
+    return h
+
+
+def swiglu_bwd(dh: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    """d gu [T, 2f] from d h [T, f] and the stashed pre-activation gu."""
+    _check_2d(dh, "dh")
+    _check_2d(gu, "gu")
+    if not _is_cuda(gu):
+        return ref.swiglu_bwd(dh, gu)
+    T, f = dh.shape
+    dgu = torch.empty((T, 2 * f), dtype=gu.dtype, device=gu.device)
+    lib = _lib_required()
+    _lib.check(lib.ppb_swiglu_bwd(dh.data_ptr(), dh.stride(0), gu.data_ptr(), gu.stride(0), dgu.data_ptr(), dgu.stride(0),
+                                  T, f, _stream()), "ppb_swiglu_bwd")
+    _lib.count_launch()
+    return dgu
+
+
+_rope_tables: dict = {}
+
+
+def rope_table(S: int, dh: int, theta: float, device: torch.device) -> torch.Tensor:
+    key = (S, dh, float(theta), str(device))
+    t = _rope_tables.get(key)
+    if t is None:
+        t = ref.rope_table(S, dh, theta, device)
+        _rope_tables[key] = t
+    return t
+
+
+def rope_(x: torch.Tensor, col0: int, S: int, n_heads: int, dh: int, theta: float = 10000.0, inverse: bool = False) -> torch.Tensor:
+    """Rotary position embedding, in place, on ``n_heads`` heads of ``dh`` columns starting at column ``col0`` of the
+    packed activation x [T, *]; position = row % S.  ``inverse`` applies the transpose rotation (the backward)."""
+    _check_2d(x, "x")
+    table = rope_table(S, dh, theta, x.device)
+    if not _is_cuda(x):
+        return ref.rope_(x, col0, S, n_heads, dh, table, inverse)
+    lib = _lib_required()
+    _lib.check(lib.ppb_rope_inplace(x.data_ptr(), x.stride(0), col0, x.shape[0], S, n_heads, dh, table.data_ptr(),
+                                    int(inverse), _stream()), "ppb_rope_inplace")
+    _lib.count_launch()
+    return x

@@ -232,3 +232,38 @@ def attention_bwd(q, k, v, o, do, lse, B, H, causal=False, scale=None, dropout_p
     dk = ds.transpose(-1, -2) @ qf
     back = lambda t, S: t.permute(0, 2, 1, 3).reshape(B * S, D).to(q.dtype)
     return back(dq, Sq), back(dk, Skv), back(dv, Skv)
+
+
+# ---- Llama-style pieces -------------------------------------------------------------------------------------
+def swiglu_fwd(gu):
+    f = gu.shape[1] // 2
+    g, u = gu[:, :f].float(), gu[:, f:].float()
+    return (torch.nn.functional.silu(g) * u).to(gu.dtype)
+
+
+def swiglu_bwd(dh, gu):
+    f = gu.shape[1] // 2
+    g, u, d = gu[:, :f].float(), gu[:, f:].float(), dh.float()
+    s = torch.sigmoid(g)
+    return torch.cat([d * u * (s + g * s * (1 - s)), d * g * s], dim=1).to(gu.dtype)
+
+
+def rope_table(S, dh, theta=10000.0, device="cpu"):
+    """[S, dh/2, 2] fp32 (cos, sin) of pos * theta^(-2i/dh)."""
+    inv = theta ** (-torch.arange(0, dh, 2, dtype=torch.float64) / dh)
+    ang = torch.arange(S, dtype=torch.float64)[:, None] * inv[None, :]
+    return torch.stack([ang.cos(), ang.sin()], dim=-1).float().to(device).contiguous()
+
+
+def rope_(x, col0, S, n_heads, dh, table, inverse=False):
+    """In-place rotary embedding on columns [col0, col0 + n_heads*dh) of x [T, *] (rotate-half pairs, position = row % S)."""
+    T = x.shape[0]
+    v = x[:, col0:col0 + n_heads * dh].float().reshape(T, n_heads, dh)
+    pos = torch.arange(T, device=x.device) % S
+    cos, sin = table[pos, :, 0][:, None, :], table[pos, :, 1][:, None, :]
+    if inverse:
+        sin = -sin
+    a, b = v[..., :dh // 2], v[..., dh // 2:]
+    out = torch.cat([a * cos - b * sin, b * cos + a * sin], dim=-1)
+    x[:, col0:col0 + n_heads * dh] = out.reshape(T, n_heads * dh).to(x.dtype)
+    return x

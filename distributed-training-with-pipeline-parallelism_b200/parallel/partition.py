@@ -42,7 +42,7 @@ def balanced_ranges(n_layers: int, num_stages: int, args: Optional[ModelArgs] = 
         # ~0.20; the cross-entropy pass is HBM-bound (reads and rewrites the [tokens, V] logits).
         d, f, V = args.dim, args.ffn_dim, args.vocab_size
         blocks = 2 if args.cross_attn else 1
-        layer_cost = (blocks * 8 * d * d + 4 * d * f) / 0.40 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
+        layer_cost = (blocks * 8 * d * d + (6 if args.activation == 'swiglu' else 4) * d * f) / 0.40 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
         head_cost = 2 * d * V / 0.9 + 650.0 * V
     # DP over (stage, first layer of the stage): minimise (most expensive stage, then sum of squared costs);
     # every stage gets at least one layer when there are enough layers.

@@ -134,6 +134,18 @@ int ppb_sum_dropout_bwd(const void* dy0, const void* dy1, const void* dy2, void*
                         float dropout_p, unsigned long long seed, void* stream);
 int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
 
+/* ---- Llama-style block pieces (csrc/llama_ops.cu) -------------------------------------------------------------
+ * No counterpart in the reference (its block is nn.TransformerDecoderLayer: ReLU FFN, no positional encoding,
+ * helper:38-46); needed by BASELINE.json config 4 "Llama-style 7B".
+ * SwiGLU on the packed linear1 output gu [T, 2f] (gate columns first): h = silu(g) * u, and its backward.
+ * RoPE (rotate-half pairs (i, i + dh/2)) applied in place to n_heads heads starting at column col0 of x [T, ld];
+ * position = row % S; cos_sin = float2 [S, dh/2]; inverse != 0 applies the transpose rotation (the backward). */
+int ppb_swiglu_fwd(const void* gu, long long ld_gu, void* h, long long ld_h, long long T, int f, void* stream);
+int ppb_swiglu_bwd(const void* dh, long long ld_dh, const void* gu, long long ld_gu, void* dgu, long long ld_dgu,
+                   long long T, int f, void* stream);
+int ppb_rope_inplace(void* x, long long ld, int col0, long long T, int S, int n_heads, int dh, const void* cos_sin,
+                     int inverse, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

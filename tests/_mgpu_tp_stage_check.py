@@ -23,7 +23,8 @@ dist.init_process_group("nccl")
 mesh = init_mesh(dp_size=1, pp_size=1, tp_size=2)
 torch.manual_seed(0)
 args = ModelArgs(dim=256, n_layers=2, n_heads=4, vocab_size=1000, ffn_dim=512, dropout=0.0, causal=True, cross_attn=False,
-                 activation=os.environ.get("ACT", "gelu"), norm_first=True, norm="rmsnorm")
+                 activation=os.environ.get("ACT", "gelu"), norm_first=True, norm="rmsnorm",
+                 rope=os.environ.get("ACT", "gelu") == "swiglu")
 full = Transformer(args)
 g = torch.Generator().manual_seed(7)
 x = torch.randint(0, 1000, (8, 128), generator=g).to(dev)
@@ -49,7 +50,7 @@ st = PipelineStage(mdl, 0, 1, dev, tp_group=mesh.tp_group)
 hist = run(st, 1, None)
 worst, worst_name = 0.0, ""
 for n, gv in st.grad_views().items():
-    want = shard_tensor(n, ref_grads[n], args.n_heads, mesh.tp_idx, 2)
+    want = shard_tensor(n, ref_grads[n], args.n_heads, mesh.tp_idx, 2, args.activation == "swiglu")
     err = ((gv - want).norm() / (want.norm() + 1e-12)).item()
     if err > worst:
         worst, worst_name = err, n

@@ -118,7 +118,7 @@ def train_worker(rank, world_size, schedule_type, results_queue, master_port=Non
 
 
 def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_port=None, act="gelu", norm="rmsnorm",
-                     split_bw=False):
+                     split_bw=False, rope=False):
     """(pp x tp) mesh, pre-LN block: loss and per-parameter gradients (each rank's SHARD of them) must equal the
     single-process full-model ones."""
     try:
@@ -136,7 +136,7 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         mesh = init_mesh(dp_size=1, pp_size=world_size // tp, tp_size=tp)
         P = mesh.pp_size
         args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0, causal=True,
-                         cross_attn=False, activation=act, norm_first=True, norm=norm)
+                         cross_attn=False, activation=act, norm_first=True, norm=norm, rope=rope)
         torch.manual_seed(4321)
         full = Transformer(args)
         B, S = 8, 16
@@ -163,7 +163,7 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         max_err = 0.0
         worst = ""
         for n, gview in st.grad_views().items():
-            want = shard_tensor(n, ref_grads[n], args.n_heads, mesh.tp_idx, tp)
+            want = shard_tensor(n, ref_grads[n], args.n_heads, mesh.tp_idx, tp, act == "swiglu")
             err = (gview - want).abs().max().item() / (want.abs().max().item() + 1e-8)
             if err > max_err:
                 max_err, worst = err, n

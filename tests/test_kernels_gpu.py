@@ -288,3 +288,33 @@ def test_gemm_reducescatter_single_gpu(tp, M, N, K):
         total += x.float() @ w.float().t()
     got = torch.cat(dsts)
     assert rel_err(got, total) < 5e-3
+
+
+# ---- Llama-style pieces (csrc/llama_ops.cu) --------------------------------------------------------------------
+@pytest.mark.parametrize("T,f", [(256, 512), (1000, 1376)])
+def test_swiglu_fwd_bwd_matches_fp32_reference(T, f):
+    from ppb200.ops import functional as F, reference as ref
+    torch.manual_seed(0)
+    gu = torch.randn(T, 2 * f, device="cuda").bfloat16()
+    dh = torch.randn(T, f, device="cuda").bfloat16()
+    h = F.swiglu_fwd(gu)
+    want = ref.swiglu_fwd(gu.float().cpu())
+    assert (h.float().cpu() - want).abs().max().item() < 2e-2 * want.abs().max().item()
+    d = F.swiglu_bwd(dh, gu)
+    want = ref.swiglu_bwd(dh.float().cpu(), gu.float().cpu())
+    assert (d.float().cpu() - want).abs().max().item() < 2e-2 * want.abs().max().item()
+
+
+@pytest.mark.parametrize("S,H,dh", [(128, 4, 64), (96, 2, 128), (64, 3, 16)])
+def test_rope_inplace_matches_fp32_reference(S, H, dh):
+    from ppb200.ops import functional as F, reference as ref
+    torch.manual_seed(1)
+    B, d = 3, H * dh
+    x = torch.randn(B * S, 3 * d, device="cuda").bfloat16()
+    want = ref.rope_(x.float().cpu().clone(), 0, S, 2 * H, dh, ref.rope_table(S, dh))
+    y = x.clone()
+    F.rope_(y, 0, S, 2 * H, dh)
+    assert torch.equal(y[:, 2 * d:], x[:, 2 * d:])                        # v columns untouched
+    assert (y.float().cpu() - want).abs().max().item() < 2e-2 * want.abs().max().item()
+    F.rope_(y, 0, S, 2 * H, dh, inverse=True)
+    assert (y.float() - x.float()).abs().max().item() < 4e-2 * x.float().abs().max().item()

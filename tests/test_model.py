@@ -141,3 +141,75 @@ def test_prenorm_gpt_block_matches_torch_encoder_layer(act):
                              (f"layers.{i}.linear1.weight", tl.linear1.weight), (f"layers.{i}.linear2.bias", tl.linear2.bias),
                              (f"layers.{i}.norm1.weight", tl.norm1.weight), (f"layers.{i}.norm3.bias", tl.norm2.bias)]:
             assert torch.allclose(gm[mine], theirs.grad, atol=3e-5, rtol=1e-3), mine
+
+
+def _llama_reference(sd, args, tokens):
+    """Independent plain-PyTorch (autograd) Llama-style model on the framework's state dict: RMSNorm, rotate-half RoPE,
+    causal attention, SwiGLU with linear1 packed as gate | up."""
+    import torch.nn.functional as Fn
+    d, H = args.dim, args.n_heads
+    dh = d // H
+    B, S = tokens.shape
+
+    def rms(x, w):
+        return x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + args.layer_norm_eps) * w
+
+    inv = args.rope_theta ** (-torch.arange(0, dh, 2, dtype=torch.float64) / dh)
+    ang = (torch.arange(S, dtype=torch.float64)[:, None] * inv[None, :]).float()
+    cos, sin = torch.cat([ang.cos(), ang.cos()], -1), torch.cat([ang.sin(), ang.sin()], -1)   # [S, dh]
+
+    def rope(t):   # [B, H, S, dh]
+        rot = torch.cat([-t[..., dh // 2:], t[..., :dh // 2]], -1)
+        return t * cos + rot * sin
+
+    x = sd["tok_embeddings.weight"][tokens]
+    for i in range(args.n_layers):
+        p = f"layers.{i}."
+        h = rms(x, sd[p + "norm1.weight"])
+        qkv = h @ sd[p + "self_attn.in_proj_weight"].t() + sd[p + "self_attn.in_proj_bias"]
+        q, k, v = (t.reshape(B, S, H, dh).transpose(1, 2) for t in qkv.chunk(3, -1))
+        if args.rope:
+            q, k = rope(q), rope(k)
+        att = Fn.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(B, S, d)
+        x = x + att @ sd[p + "self_attn.out_proj.weight"].t() + sd[p + "self_attn.out_proj.bias"]
+        h = rms(x, sd[p + "norm3.weight"])
+        g, u = (h @ sd[p + "linear1.weight"].t() + sd[p + "linear1.bias"]).chunk(2, -1)
+        x = x + (Fn.silu(g) * u) @ sd[p + "linear2.weight"].t() + sd[p + "linear2.bias"]
+    x = rms(x, sd["norm.weight"])
+    return x @ sd["output.weight"].t() + sd["output.bias"]
+
+
+def test_llama_style_block_matches_autograd_reference():
+    torch.manual_seed(11)
+    args = ModelArgs(dim=64, n_layers=2, n_heads=4, vocab_size=53, ffn_dim=48, dropout=0.0, causal=True, cross_attn=False,
+                     activation="swiglu", norm_first=True, norm="rmsnorm", rope=True)
+    model = Transformer(args)
+    assert model.layers["0"].linear1.weight.shape == (96, 64)       # gate | up
+    tokens = torch.randint(0, 53, (3, 16))
+    target = torch.randint(0, 53, (3, 16))
+    loss = torch.nn.functional.cross_entropy(model(tokens).reshape(-1, 53), target.reshape(-1))
+    loss.backward()
+    sd = {k: v.detach().clone().requires_grad_(True) for k, v in model.state_dict().items()}
+    loss_ref = torch.nn.functional.cross_entropy(_llama_reference(sd, args, tokens).reshape(-1, 53), target.reshape(-1))
+    loss_ref.backward()
+    assert abs(loss.item() - loss_ref.item()) < 1e-5
+    for n, p in model.named_parameters():
+        err = (p.grad - sd[n].grad).abs().max().item() / (sd[n].grad.abs().max().item() + 1e-9)
+        assert err < 2e-4, (n, err)
+
+
+def test_rope_and_swiglu_reference_ops():
+    from ppb200.ops import functional as F, reference as ref
+    x = torch.randn(32, 3 * 64)
+    y = x.clone()
+    F.rope_(y, 0, 16, 2 * 4, 16, 10000.0)
+    assert torch.equal(y[:, 128:], x[:, 128:]) and not torch.allclose(y[:, :128], x[:, :128])   # v untouched
+    assert torch.allclose(y[::16, :128], x[::16, :128])          # position 0 is the identity rotation
+    F.rope_(y, 0, 16, 2 * 4, 16, 10000.0, inverse=True)
+    assert torch.allclose(y, x, atol=1e-5)
+    gu = torch.randn(8, 48, requires_grad=True)
+    h = torch.nn.functional.silu(gu[:, :24]) * gu[:, 24:]
+    dh = torch.randn(8, 24)
+    h.backward(dh)
+    assert torch.allclose(F.swiglu_fwd(gu.detach()), h.detach(), atol=1e-6)
+    assert torch.allclose(F.swiglu_bwd(dh, gu.detach()), gu.grad, atol=1e-5)

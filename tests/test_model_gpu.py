@@ -142,3 +142,22 @@ def test_prenorm_gpt_block_cuda_matches_cpu(act, dropout):
         a, b = gc[n].float(), gg[n].float().cpu()
         rel = ((a - b).norm() / (a.norm() + 1e-6)).item()
         assert rel < 0.12, (n, rel)
+
+
+def test_llama_style_block_cuda_matches_cpu():
+    """SwiGLU + RoPE + RMSNorm pre-LN block: bf16 CUDA program (ppb_swiglu_*, ppb_rope_inplace + the GEMM/attention/norm
+    kernels) against the fp32 CPU program on the same weights."""
+    torch.manual_seed(6)
+    args = ModelArgs(dim=512, n_layers=2, n_heads=8, vocab_size=1000, ffn_dim=1024, dropout=0.0, causal=True,
+                     cross_attn=False, activation="swiglu", norm_first=True, norm="rmsnorm", rope=True)
+    full = Transformer(args)
+    x = torch.randint(0, 1000, (8, 128))
+    y = torch.randint(0, 1000, (8, 128))
+    st_c, loss_c = _run("cpu", full, x, y, 4)
+    st_g, loss_g = _run("cuda", full, x, y, 4)
+    assert abs(loss_c[0] - loss_g[0]) < 3e-2 * abs(loss_c[0]), (loss_c, loss_g)
+    gc, gg = st_c.grad_views(), st_g.grad_views()
+    for n in gc:
+        a, b = gc[n].float(), gg[n].float().cpu()
+        rel = ((a - b).norm() / (a.norm() + 1e-6)).item()
+        assert rel < 0.12, (n, rel)

@@ -47,7 +47,7 @@ def test_tensor_parallel_mlp_fused_kernels():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("act", ["gelu", "relu"])
+@pytest.mark.parametrize("act", ["gelu", "relu", "swiglu"])
 def test_tensor_parallel_stage_matches_single_gpu(act):
     os.environ["ACT"] = act
     try:
