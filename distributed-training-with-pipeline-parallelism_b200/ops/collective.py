@@ -258,6 +258,8 @@ class TPComm:
             self.x_sym = [SymmetricBuffer((self.rows, self.d), torch.bfloat16, self.device, group) for _ in range(2)]
             self.y_sym = [SymmetricBuffer((self.rows, self.d), torch.float32, self.device, group) for _ in range(2)]
             self.kx = self.ky = 0
+            import os
+            self.direct_peer = os.environ.get("PPB_TP_DIRECT_PEER", "0") == "1"
             self.x_sym[0].barrier(0)   # every rank's zeroed reduce-scatter buffers exist before the first push
 
     # ---- all-gather -> GEMM -------------------------------------------------------------------------------------
@@ -280,14 +282,21 @@ class TPComm:
         self.kx ^= 1
         buf.tensor.copy_(x_shard)
         buf.barrier(0)
-        out = allgather_linear(buf.ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major)
-        full = None
-        if need_full:   # the weight-gradient GEMM of this layer wants the gathered rows as its own operand
-            full = torch.empty((self.rows * self.tp, self.d), dtype=torch.bfloat16, device=self.device)
-            for r in range(self.tp):
-                src = buf.tensor if r == self.rank else buf.hdl.get_buffer(r, (self.rows, self.d), torch.bfloat16)
-                full[r * self.rows:(r + 1) * self.rows].copy_(src)
-        return out, full
+        if self.direct_peer and not need_full:
+            # the GEMM's TMA producer loads remote A tiles straight from the peers' buffers.  Every N tile re-fetches
+            # its A tiles and peer memory is not cached in the local L2, so a remote tile crosses NVLink N/256 times
+            # (43x at Llama-7B FFN width: measured 5.4 ms vs 1.5 ms of GEMM time per layer) -- only worth it for narrow N
+            return allgather_linear(buf.ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major), None
+        # one pass over NVLink: pull the peers' shards next to ours (the weight-gradient GEMM wants the gathered rows
+        # anyway), then run the same kernel with every shard pointer local
+        full = torch.empty((self.rows * self.tp, self.d), dtype=torch.bfloat16, device=self.device)
+        for r in range(self.tp):
+            src = buf.tensor if r == self.rank else buf.hdl.get_buffer(r, (self.rows, self.d), torch.bfloat16)
+            full[r * self.rows:(r + 1) * self.rows].copy_(src)
+        base = full.data_ptr()
+        ptrs = [base + r * self.rows * self.d * 2 for r in range(self.tp)]
+        out = allgather_linear(ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major)
+        return out, (full if need_full else None)
 
     # ---- GEMM -> reduce-scatter ---------------------------------------------------------------------------------
     def linear_rs(self, x: torch.Tensor, w: torch.Tensor, w_mn_major: bool = False) -> torch.Tensor:
