@@ -248,6 +248,19 @@ def run_reference(a, rank, local_rank, world):
         return
     from ppb200.utils.clocks import ClockSampler
 
+    # what the helper cannot express is reported, not emulated: it has one block (post-LN, ReLU, FFN 2048), no data or
+    # tensor parallelism (helper:178 creates an unused group) and only torch's three schedules (helper:215-220)
+    why = None
+    if a.model not in ("ref-gpt2-medium", "ref-gpt2-xl", "ref-small"):
+        why = f"the helper's Transformer cannot express model preset {a.model!r} (fixed nn.TransformerDecoderLayer block)"
+    elif a.tp > 1 or a.dp > 1:
+        why = "the helper has no tensor/data parallelism (pipeline stages only)"
+    elif a.schedule not in ("GPipe", "1F1B", "Interleaved1F1B"):
+        why = f"the helper selects among GPipe / 1F1B / Interleaved1F1B only (got {a.schedule})"
+    if why is not None:
+        if rank == 0:
+            emit({"impl": "reference", "unavailable": why})
+        return
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     if world == 1:

@@ -100,6 +100,7 @@ class PipelineSchedule:
         want = (os.environ.get("PPB_CUDA_GRAPHS", "1") != "0") if cuda_graphs is None else cuda_graphs
         self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None and self.tp_size == 1)
         self.graph_warmup_steps = graph_warmup_steps
+        self.nvtx = os.environ.get("PPB_NVTX", "0") == "1"   # NVTX range per action, named with its IR string
         if self.use_graphs:
             for st in self.stages:
                 st.enable_graphs(self._max_inflight(st.stage_index))
@@ -240,9 +241,14 @@ class PipelineSchedule:
         t_begin = tick()
         host_t0 = time.perf_counter()
         idx = -1
+        nvtx = cuda and self.nvtx
         try:
             for idx, a in enumerate(self.order):
                 typ = a.type
+                if nvtx:   # ranges carry the IR string (2F0, 3SEND_B1, ...) so ncu / nsys timelines line up with the schedule
+                    if idx:
+                        torch.cuda.nvtx.range_pop()
+                    torch.cuda.nvtx.range_push(str(a))
                 if typ == T.RECV_F or typ == T.RECV_B:
                     kind = "F" if typ == T.RECV_F else "B"
                     src_stage = a.stage - 1 if kind == "F" else a.stage + 1
@@ -366,6 +372,8 @@ class PipelineSchedule:
                     pass
                 else:
                     raise NotImplementedError(f"action {a} is not executable by this runner")
+            if nvtx and idx >= 0:
+                torch.cuda.nvtx.range_pop()
         except Exception as e:  # same diagnostics contract as torch's runtime (schedules.py:2257-2269)
             grid = sched_ir.grid({self.pp_rank: self.order}, error_at=(self.pp_rank, idx))
             raise RuntimeError(f"[rank {self.pp_rank}] schedule '{self.name}' failed at action {idx} "

@@ -202,3 +202,39 @@ def test_launcher_reports_errors_and_kills_stragglers():
     res = launch_workers(_boom, 2, (), timeout=60)
     assert res == {"error": "boom"} and time.time() - t0 < 25
     assert launch_workers(_silent, 2, (), timeout=60) == {"error": "No results returned"}
+
+
+def test_guarded_allocations_catch_out_of_bounds_writes_and_stale_reads():
+    """The in-repo memory checker (utils/debug.py), exercised on CPU tensors: guard bands + NaN poison."""
+    import torch
+    from ppb200.utils import debug
+    with debug.guarded_allocations(device_type="cpu") as rep:
+        a = torch.empty(16, 8, dtype=torch.float32, device="cpu")
+        assert torch.isnan(a).all()                       # unwritten memory reads as NaN
+        z = torch.zeros(5, dtype=torch.float32, device="cpu")
+        assert (z == 0).all()
+        b = torch.empty_like(a)
+        assert b.shape == a.shape and torch.isnan(b).all()
+        a.fill_(1.0)
+        assert rep.check("clean") == 0
+        c = torch.empty(4, dtype=torch.float32, device="cpu")
+        # simulate a kernel writing 3 floats past the end of c
+        c.as_strided((7,), (1,))[4:].fill_(2.0)
+        assert rep.check("oob") == 1
+        assert "test_utils.py" in rep.violations[0] and "after" in rep.violations[0]
+    assert torch.empty(2).shape == (2,)                   # patches are removed on exit
+    assert torch.empty is not None and not rep.entries
+
+
+def test_determinism_check_reports_mismatches():
+    import torch
+    from ppb200.utils import debug
+    x = torch.arange(64, dtype=torch.float32)
+    assert debug.determinism_check(lambda: (x * 2, None), reps=5, device="cpu")["mismatching"] == 0
+    state = {"n": 0}
+
+    def flaky():
+        state["n"] += 1
+        return (x + (1.0 if state["n"] == 3 else 0.0),)
+    res = debug.determinism_check(flaky, reps=5, device="cpu")
+    assert res["mismatching"] == 1 and res["worst_abs"] == 1.0
