@@ -1,0 +1,85 @@
+#!/usr/bin/env python
+"""CPU-only: predict the schedule sweep (BASELINE.json config 5: GPipe / 1F1B / Interleaved / ZeroBubble at 2/4/8
+stages, 4-64 micro-batches) with the discrete-event simulator fed by MEASURED per-action costs of the flagship model
+(profiles/bench_r1_n4_*.json: per 4096-token micro-batch a decoder layer costs 0.333 ms forward / 0.667 ms backward,
+embedding + final norm + head + loss 0.67 / 0.79 ms; I = 0.78 B, W = 0.23 B), and put the measured points next to
+the prediction.  Writes profiles/schedule_sweep_predicted.md."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from ppb200.models import preset  # noqa: E402
+from ppb200.parallel.partition import stage_ranges  # noqa: E402
+from ppb200.parallel.schedule import ActionType as T, build_schedule, simulate, theoretical_bubble  # noqa: E402
+
+ARGS = preset("ref-gpt2-medium")
+SEQ, GLOBAL_BATCH = 1024, 128
+LAYER_F, LAYER_B, HEAD_F, HEAD_B, OPTIM = 0.333, 0.667, 0.67, 0.79, 0.7
+I_FRAC, W_FRAC = 0.78, 0.23
+
+measured = {}
+for f in sorted(os.listdir(os.path.join(ROOT, "profiles"))):
+    if not f.endswith(".json"):
+        continue
+    try:
+        txt = open(os.path.join(ROOT, "profiles", f)).read()
+        rows = json.loads(txt) if txt.lstrip().startswith("[") else [json.loads([l for l in txt.splitlines() if l.startswith("{")][-1])]
+    except Exception:  # noqa: BLE001
+        continue
+    for r in rows:
+        if "schedule" in r and "stages" in r:                    # schedule_sweep rows
+            measured.setdefault((r["schedule"], r["stages"], r.get("virtual", 1), r["n_microbatches"]), (r["ms_per_step"], "*"))
+        elif "config" in r and r.get("impl") == "ours" and "ref-gpt2-medium" in r["config"].get("model", ""):
+            c = r["config"]
+            par = c.get("parallelism", "")
+            if "dp" in par or "tp" in par or c.get("global_batch") != GLOBAL_BATCH:
+                continue
+            v = int(par.split("xv")[1]) if "xv" in par else 1
+            key = (c["schedule"], r["n_gpus"], v, c["n_microbatches"])
+            if key not in measured or measured[key][1] == "*" or r["ms_per_step"] < measured[key][0]:
+                measured[key] = (r["ms_per_step"], "")      # the latest (fastest) headline-bench measurement wins
+
+lines = ["# Schedule sweep: simulator prediction from measured per-action costs vs measured steps",
+         "",
+         "Flagship model (helper LM at GPT-2-medium scale), seq 1024, global batch 128 split into m micro-batches, balanced",
+         "partition.  `pred ms` = discrete-event simulation of the lowered schedule with the measured action costs scaled by",
+         "micro-batch size; `idle crit` = idle fraction of the busiest rank in that simulation; `theory` = (p-1)/(v*m+p-1).",
+         "The simulation assumes size-independent kernel efficiency, so it is optimistic for small micro-batches (m = 64).",
+         "Measured values marked * come from the early round-1 sweep (`schedule_sweep_p4_r1.json`: before the NCCL channel cap,",
+         "the attention and partition improvements, 12-25 % slower kernels); unmarked ones are the current headline runs.",
+         "",
+         "| schedule | stages | v | m | pred ms | idle crit | theory | measured ms | measured / pred |",
+         "|---|---|---|---|---|---|---|---|---|"]
+for P in (2, 4, 8):
+    for sched, v in (("GPipe", 1), ("1F1B", 1), ("Interleaved1F1B", 2), ("ZeroBubble1F1B", 1)):
+        if ARGS.n_layers % (P * v):
+            continue
+        for m in (4, 8, 16, 32, 64):
+            if sched == "Interleaved1F1B" and m % P:
+                continue
+            if GLOBAL_BATCH % m:
+                continue
+            S = P * v
+            ranges = stage_ranges(ARGS.n_layers, S, "balanced", ARGS, SEQ)
+            scale = (GLOBAL_BATCH // m) * SEQ / 4096.0
+
+            def cost(a, ranges=ranges, S=S, scale=scale):
+                n = ranges[a.stage][1] - ranges[a.stage][0]
+                f = n * LAYER_F + (HEAD_F if a.stage == S - 1 else 0.0)
+                b = n * LAYER_B + (HEAD_B if a.stage == S - 1 else 0.0)
+                return {T.F: f * scale, T.B: b * scale, T.I: b * scale * I_FRAC, T.W: b * scale * W_FRAC,
+                        T.OPTIM: OPTIM / v}.get(a.type, 0.0)
+            try:
+                order = build_schedule(sched, P, m, n_virtual=v)
+            except ValueError:
+                continue
+            res = simulate(order, S, cost=cost)
+            meas = measured.get((sched, P, v, m))
+            lines.append(f"| {sched} | {P} | {v} | {m} | {res.makespan:.1f} | {min(res.bubble.values()):.3f} | "
+                         f"{theoretical_bubble(P, m, v):.3f} | {'' if meas is None else f'{meas[0]:.1f}{meas[1]}'} | "
+                         f"{'' if meas is None else f'{meas[0] / res.makespan:.2f}'} |")
+out = os.path.join(ROOT, "profiles", "schedule_sweep_predicted.md")
+open(out, "w").write("\n".join(lines) + "\n")
+print("\n".join(lines[7:]))
