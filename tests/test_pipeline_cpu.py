@@ -118,3 +118,58 @@ def test_tp_shard_merge_roundtrip():
     assert shards[0]["layers.0.linear2.weight"].shape == (32, 24)
     merged = merge_tp_shards(shards, 4)
     assert all(torch.equal(merged[k], sd[k]) for k in sd)
+
+
+def test_uneven_microbatches_follow_tensor_split_semantics():
+    """B = 10 in 4 micro-batches -> chunks of 3, 3, 2, 2 (torch.tensor_split, microbatch.py:315-427); gradients are the
+    mean over micro-batches of each chunk's mean-token-loss gradient (scale_grads, stage.py:589-591)."""
+    import copy
+    import torch
+    from ppb200.api import make_schedule, manual_model_split
+    from ppb200.models import ModelArgs, Transformer
+    torch.manual_seed(3)
+    args = ModelArgs(dim=32, n_layers=2, n_heads=4, vocab_size=41, ffn_dim=48, dropout=0.0)
+    full = Transformer(args)
+    x, y = torch.randint(0, 41, (10, 8)), torch.randint(0, 41, (10, 8))
+    oracle = copy.deepcopy(full)
+    chunk_losses = []
+    for xc, yc in zip(torch.tensor_split(x, 4), torch.tensor_split(y, 4)):
+        l = torch.nn.functional.cross_entropy(oracle(xc).reshape(-1, 41), yc.reshape(-1))
+        (l / 4).backward()
+        chunk_losses.append(l.item())
+    assert [c.shape[0] for c in torch.tensor_split(x, 4)] == [3, 3, 2, 2]
+    st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
+    sched = make_schedule("GPipe", st, 4, None)
+    losses = []
+    out = sched.step(x, target=y, losses=losses)
+    assert out is None or out.shape[0] == 10
+    assert torch.allclose(torch.tensor([l.item() for l in losses]), torch.tensor(chunk_losses), atol=1e-5)
+    ref = dict(oracle.named_parameters())      # the arena orders parameters by group, so match by name
+    for n, g in st.grad_views().items():
+        assert (g - ref[n].grad).abs().max().item() <= 2e-5 * (ref[n].grad.abs().max().item() + 1e-6), n
+
+
+def test_eval_step_is_forward_only_without_dropout():
+    import copy
+    import torch
+    from ppb200.api import make_schedule, manual_model_split
+    from ppb200.models import ModelArgs, Transformer
+    torch.manual_seed(4)
+    args = ModelArgs(dim=32, n_layers=2, n_heads=4, vocab_size=41, ffn_dim=48, dropout=0.3)
+    full = Transformer(args)
+    x, y = torch.randint(0, 41, (8, 8)), torch.randint(0, 41, (8, 8))
+    oracle = copy.deepcopy(full).eval()
+    with torch.no_grad():
+        want = [torch.nn.functional.cross_entropy(oracle(xc).reshape(-1, 41), yc.reshape(-1)).item()
+                for xc, yc in zip(x.chunk(4), y.chunk(4))]
+    st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
+    sched = make_schedule("1F1B", st, 4, None)
+    n_actions = len(sched.order)
+    losses = []
+    sched.eval_step(x, target=y, losses=losses)
+    assert torch.allclose(torch.tensor([l.item() for l in losses]), torch.tensor(want), atol=1e-5)
+    assert float(st.grad.abs().sum()) == 0.0 and not st.stash            # no backward ran, nothing is kept
+    assert len(sched.order) == n_actions and st.training                 # training order and mode are restored
+    train_losses = []
+    sched.step(x, target=y, losses=train_losses)                          # dropout is live again
+    assert abs(train_losses[0].item() - want[0]) > 1e-4
