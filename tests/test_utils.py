@@ -139,6 +139,48 @@ def test_checkpoint_shards_merge_to_full_state_dict_and_reshard(tmp_path):
     assert float(st4.exp_avg[: st4.n_total].max()) == 0.5
 
 
+def test_checkpoint_roundtrip_across_tensor_parallel_degrees(tmp_path):
+    """(pp, tp) = (2, 2) shards -> merged reference-layout checkpoint -> (1, 1) and back into a (2, 2) rank, parameters
+    and optimizer moments (Llama-style block: packed QKV and packed gate|up splits)."""
+    import copy
+    from ppb200.models.tp import shard_model_for_tp
+    from ppb200.parallel.partition import prune_to_stage
+    from ppb200.parallel.stage import PipelineStage
+    args = ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=50, ffn_dim=48, dropout=0.0, causal=True, cross_attn=False,
+                     activation="swiglu", norm_first=True, norm="rmsnorm", rope=True)
+    torch.manual_seed(1)
+    full = Transformer(args)
+    want = {k: v.clone() for k, v in full.state_dict().items()}
+    group = object()   # stands in for the tp process group: no collective runs in this test
+
+    def make(pp_idx, tp_idx):
+        m = copy.deepcopy(full)
+        prune_to_stage(m, pp_idx, 2)
+        shard_model_for_tp(m, tp_idx, 2)
+        return PipelineStage(m, pp_idx, 2, torch.device("cpu"), tp_group=group).materialize()
+
+    for pp_idx in range(2):
+        for tp_idx in range(2):
+            st = make(pp_idx, tp_idx)
+            st.exp_avg.copy_(st.master * 2.0)          # moments with parameter-shaped structure
+            st.step_count = 3
+            path = checkpoint.save_stage(st, str(tmp_path))
+            assert path.endswith(f"stage_{pp_idx:03d}_tp{tp_idx}.pt")
+    merged = checkpoint.merge_shards(str(tmp_path))
+    assert set(merged) == set(want) and all(torch.equal(merged[k], want[k]) for k in want)
+    from ppb200.api import manual_model_split
+    one = manual_model_split(Transformer(args), 0, 1, torch.device("cpu")).materialize()
+    assert checkpoint.load_stage(one, str(tmp_path)) == 3
+    assert all(torch.equal(v, want[k]) for k, v in one.state_dict().items())
+    assert torch.allclose(one.exp_avg[: one.n_total], one.master[: one.n_total] * 2.0)
+    again = make(1, 1)
+    again.master.zero_()
+    checkpoint.load_stage(again, str(tmp_path))
+    ref = make(1, 1)
+    assert all(torch.equal(a, b) for a, b in zip(again.state_dict().values(), ref.state_dict().values()))
+    assert torch.allclose(again.exp_avg[: again.n_total], ref.master[: ref.n_total] * 2.0)
+
+
 # ---- config ---------------------------------------------------------------------------------------------------------
 def test_run_config_cli_and_presets():
     cfg = RunConfig.from_args(["--model", "ref-gpt2-medium", "--schedule", "Interleaved1F1B", "--pp", "8",
