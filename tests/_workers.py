@@ -118,7 +118,7 @@ def train_worker(rank, world_size, schedule_type, results_queue, master_port=Non
 
 
 def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_port=None, act="gelu", norm="rmsnorm",
-                     split_bw=False, rope=False):
+                     split_bw=False, rope=False, dp=1):
     """(pp x tp) mesh, pre-LN block: loss and per-parameter gradients (each rank's SHARD of them) must equal the
     single-process full-model ones."""
     try:
@@ -133,13 +133,13 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
         torch.set_num_threads(1)
         dist.init_process_group("gloo", rank=rank, world_size=world_size)
-        mesh = init_mesh(dp_size=1, pp_size=world_size // tp, tp_size=tp)
+        mesh = init_mesh(dp_size=dp, pp_size=world_size // (tp * dp), tp_size=tp)
         P = mesh.pp_size
         args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0, causal=True,
                          cross_attn=False, activation=act, norm_first=True, norm=norm, rope=rope)
         torch.manual_seed(4321)
         full = Transformer(args)
-        B, S = 8, 16
+        B, S = 8 * dp, 16
         g = torch.Generator().manual_seed(7)
         x = torch.randint(0, 101, (B, S), generator=g)
         y = torch.randint(0, 101, (B, S), generator=g)
@@ -150,16 +150,20 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         mdl = copy.deepcopy(full)
         prune_to_stage(mdl, mesh.pp_idx, P)
         shard_model_for_tp(mdl, mesh.tp_idx, tp)
-        st = PipelineStage(mdl, mesh.pp_idx, P, torch.device("cpu"), tp_group=mesh.tp_group)
+        st = PipelineStage(mdl, mesh.pp_idx, P, torch.device("cpu"), tp_group=mesh.tp_group, dp_group=mesh.dp_group)
         custom = None
         if split_bw:
             from ppb200.parallel.schedule import zero_bubble_order
             custom = zero_bubble_order(P, m)
         sched = make_schedule("1F1B", st, m, None, pp_group=mesh.pp_group, pp_group_bwd=mesh.pp_group_bwd, optimizer=None,
-                              actions=custom)
+                              actions=custom, dp_group=mesh.dp_group)
         losses = []
         first, last = 0 in sched.local, (P - 1) in sched.local
-        sched.step(*((x,) if first else ()), target=y if last else None, losses=losses if last else None)
+        Bl = B // dp
+        xl, yl = x[mesh.dp_idx * Bl:(mesh.dp_idx + 1) * Bl], y[mesh.dp_idx * Bl:(mesh.dp_idx + 1) * Bl]
+        sched.step(*((xl,) if first else ()), target=yl if last else None, losses=losses if last else None)
+        if dp > 1 and st.n_total:
+            st.grad.div_(dp)      # the ALLREDUCE action summed over the replicas
         max_err = 0.0
         worst = ""
         for n, gview in st.grad_views().items():
@@ -170,6 +174,9 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         out = {"rank": rank, "max_rel_grad_err": max_err, "worst": worst}
         if last:
             lp = torch.stack([l.reshape(()) for l in losses]).mean()
+            if dp > 1:
+                dist.all_reduce(lp, group=mesh.dp_group)
+                lp = lp / dp
             out["loss_err"] = abs(lp.item() - loss_ref.item())
         gathered = [None] * world_size
         dist.all_gather_object(gathered, out)
