@@ -241,6 +241,7 @@ class PipelineSchedule:
         t_begin = tick()
         host_t0 = time.perf_counter()
         idx = -1
+        clip = None
         nvtx = cuda and self.nvtx
         try:
             for idx, a in enumerate(self.order):
@@ -366,6 +367,15 @@ class PipelineSchedule:
                     t0 = tick()
                     opt = dict(self.optimizer)
                     gs = (1.0 / self.m if self.scale_grads else 1.0) / self.dp_size
+                    max_norm = opt.pop("max_grad_norm", None)
+                    if max_norm:
+                        if clip is None:   # once per step: global L2 norm over every stage of every pipeline rank
+                            for w2 in allreduce_works.values():
+                                if w2 is not None:
+                                    w2.wait()
+                            allreduce_works.clear()
+                            clip = self._global_clip_coef(gs, float(max_norm))
+                        opt["clip_coef"] = clip
                     self.local[a.stage].optimizer_step(grad_scale=gs, **opt)
                     timeline.append((a, t0, tick()))
                 elif typ in (T.UNSHARD, T.RESHARD):
@@ -412,6 +422,22 @@ class PipelineSchedule:
         else:
             handle.wait()
         return buf
+
+    def _global_clip_coef(self, grad_scale: float, max_norm: float) -> torch.Tensor:
+        """min(1, max_norm / ||g||) as a device scalar, ||g|| = L2 norm of the averaged gradient of the WHOLE model:
+        per-stage sums of squares (device), one all-reduce over the pipeline group, coefficient computed on the device
+        and consumed by the AdamW kernel -- no host synchronisation.  (The reference has no optimizer)"""
+        tot = None
+        for st in self.stages:
+            s = st.grad_sumsq()
+            tot = s.clone() if tot is None else tot.add_(s)
+        if self.pp_size > 1:
+            dist.all_reduce(tot, group=self.pp_group)
+        coef = self.stages[0].clip_coef
+        from ..ops import functional as F
+        F.clip_coef(tot, grad_scale, max_norm, coef)
+        self.last_grad_norm_sq = tot    # (unscaled) for logging: norm = sqrt(tot) * grad_scale
+        return coef
 
     def eval_step(self, *args, target=None, losses=None):
         """Forward-only pass (torch's schedule.eval(), schedules.py:248-457): runs the F actions of the GPipe

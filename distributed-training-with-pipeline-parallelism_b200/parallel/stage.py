@@ -489,6 +489,18 @@ class PipelineStage:
             self.grad.zero_()
 
     def grad_sumsq(self) -> torch.Tensor:
+        """Sum of squares of this stage's (already reduced) gradients, each parameter counted once across the
+        tensor-parallel group: slices add up over the tp ranks, replicated parameters are counted by one rank."""
+        grad = self.fused_ar.final if self.fused_ar is not None else self.grad
         self.clip_sumsq.zero_()
-        F.sumsq_accum(self.grad[:self.n_total], self.clip_sumsq)
+        if self.n_total:
+            F.sumsq_accum(grad[:self.n_total], self.clip_sumsq)
+        if self.tp_size > 1:
+            import torch.distributed as dist
+            rep = torch.zeros_like(self.clip_sumsq)
+            if self.tp_replicated:
+                F.sumsq_accum(torch.cat([grad[o:o + n] for o, n in self.tp_replicated]), rep)
+            self.clip_sumsq.sub_(rep)
+            dist.all_reduce(self.clip_sumsq, group=self.tp_group)
+            self.clip_sumsq.add_(rep)
         return self.clip_sumsq

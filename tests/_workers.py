@@ -187,3 +187,48 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
     except Exception as e:  # noqa: BLE001
         traceback.print_exc()
         results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def clip_worker(rank, world_size, results_queue, master_port=None, max_norm=0.05):
+    """Global-norm gradient clipping across pipeline ranks == torch.nn.utils.clip_grad_norm_ + AdamW on the full model."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.api import manual_model_split, make_schedule
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        args = ModelArgs(dim=32, n_layers=4, n_heads=4, vocab_size=61, ffn_dim=48, dropout=0.0)
+        torch.manual_seed(5)
+        full = Transformer(args)
+        x, y = torch.randint(0, 61, (8, 8)), torch.randint(0, 61, (8, 8))
+        oracle = copy.deepcopy(full)
+        opt = torch.optim.AdamW(oracle.parameters(), lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0)
+        norms = []
+        for _ in range(3):
+            opt.zero_grad()
+            torch.nn.functional.cross_entropy(oracle(x).reshape(-1, 61), y.reshape(-1)).backward()
+            norms.append(float(torch.nn.utils.clip_grad_norm_(oracle.parameters(), max_norm)))
+            opt.step()
+        want = dict(oracle.state_dict())
+        st = manual_model_split(copy.deepcopy(full), rank, world_size, torch.device("cpu"))
+        sched = make_schedule("1F1B", st, 4, None,
+                              optimizer={"lr": 1e-2, "betas": (0.9, 0.95), "eps": 1e-8, "weight_decay": 0.0, "max_grad_norm": max_norm})
+        got_norms = []
+        for _ in range(3):
+            sched.step(*((x,) if rank == 0 else ()), target=y if rank == world_size - 1 else None,
+                       losses=[] if rank == world_size - 1 else None)
+            got_norms.append(float(sched.last_grad_norm_sq.sqrt()) / 4)        # grad_scale = 1/m
+        err = max((v - want[k]).abs().max().item() for k, v in st.state_dict().items())
+        out = {"rank": rank, "max_param_err": err, "norm_err": max(abs(a - b) for a, b in zip(norms, got_norms)),
+               "clipped": norms[0] > max_norm}
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, out)
+        if rank == 0:
+            results_queue.put({"ranks": gathered})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

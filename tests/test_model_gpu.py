@@ -161,3 +161,29 @@ def test_llama_style_block_cuda_matches_cpu():
         a, b = gc[n].float(), gg[n].float().cpu()
         rel = ((a - b).norm() / (a.norm() + 1e-6)).item()
         assert rel < 0.12, (n, rel)
+
+
+def test_gradient_clipping_cuda_matches_cpu():
+    """Global-norm clipping: device-side sum of squares + coefficient (ppb_sumsq_f32, ppb_clip_coef) feeding the AdamW
+    kernel, against the CPU program on the same weights."""
+    torch.manual_seed(8)
+    args = ModelArgs(dim=256, n_layers=2, n_heads=4, vocab_size=512, ffn_dim=512, dropout=0.0)
+    full = Transformer(args)
+    x = torch.randint(0, 512, (8, 128))
+    y = torch.randint(0, 512, (8, 128))
+    res = {}
+    for dev in ("cpu", "cuda"):
+        st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device(dev))
+        sched = make_schedule("1F1B", st, 4, None, optimizer={"lr": 1e-3, "weight_decay": 0.0, "max_grad_norm": 0.5})
+        hist, norms = [], []
+        for _ in range(3):
+            losses = []
+            sched.step(x.to(dev), target=y.to(dev), losses=losses)
+            hist.append(torch.stack([l.reshape(()) for l in losses]).mean().item())
+            norms.append(float(sched.last_grad_norm_sq.sqrt()) / 4)
+        res[dev] = (hist, norms)
+    assert res["cpu"][1][0] > 0.5                                            # clipping is active
+    for a, b in zip(res["cpu"][1], res["cuda"][1]):
+        assert abs(a - b) < 0.05 * a, res
+    assert res["cuda"][0][-1] < res["cuda"][0][0]
+    assert abs(res["cuda"][0][-1] - res["cpu"][0][-1]) < 3e-2 * res["cpu"][0][-1], res
