@@ -41,11 +41,34 @@ class RunConfig:
     master_port: Optional[int] = None
     trace_path: Optional[str] = None      # chrome trace of the measured timeline
     metrics_path: Optional[str] = None    # JSONL
+    # ---- training loop (ppb200.train) ----
+    log_every: int = 1
+    save_dir: Optional[str] = None        # per-(stage, tp rank) shards in the reference state_dict layout
+    save_every: int = 0                   # 0 = only at the end (when save_dir is set)
+    resume_from: Optional[str] = None     # directory written by save_dir; may have a different (pp, tp) layout
+    data_path: Optional[str] = None       # flat token file (.bin uint16/int32 via --data-dtype, or .npy); default synthetic
+    data_dtype: str = "uint16"
+    lr_warmup_steps: int = 0
+    lr_decay_steps: int = 0               # 0 = constant after warm-up; else cosine down to lr * lr_min_ratio
+    lr_min_ratio: float = 0.1
 
     def optimizer_dict(self) -> Optional[dict]:
         if not self.optimizer:
             return None
-        return {"lr": self.lr, "betas": (self.beta1, self.beta2), "weight_decay": self.weight_decay}
+        d = {"lr": self.lr, "betas": (self.beta1, self.beta2), "weight_decay": self.weight_decay}
+        if self.max_grad_norm:
+            d["max_grad_norm"] = self.max_grad_norm
+        return d
+
+    def lr_at(self, step: int) -> float:
+        """Linear warm-up to ``lr``, then cosine decay to ``lr * lr_min_ratio`` over ``lr_decay_steps`` (0 = constant)."""
+        import math
+        if self.lr_warmup_steps and step < self.lr_warmup_steps:
+            return self.lr * (step + 1) / self.lr_warmup_steps
+        if not self.lr_decay_steps:
+            return self.lr
+        t = min(1.0, (step - self.lr_warmup_steps) / max(1, self.lr_decay_steps - self.lr_warmup_steps))
+        return self.lr * (self.lr_min_ratio + (1.0 - self.lr_min_ratio) * 0.5 * (1.0 + math.cos(math.pi * t)))
 
     def model_args(self):
         from ..models import preset

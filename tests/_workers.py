@@ -232,3 +232,19 @@ def clip_worker(rank, world_size, results_queue, master_port=None, max_norm=0.05
     except Exception as e:  # noqa: BLE001
         traceback.print_exc()
         results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def train_cli_worker(rank, world_size, argv, results_queue, master_port=None):
+    """Run the training entry point (ppb200.train.main) as one rank of a gloo job."""
+    try:
+        import torch
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), LOCAL_RANK=str(rank),
+                          WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        from ppb200 import train
+        out = train.main(list(argv) + ["--device", "cpu"])
+        if rank == world_size - 1:
+            results_queue.put(out)
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

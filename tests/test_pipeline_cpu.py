@@ -184,3 +184,28 @@ def test_global_norm_gradient_clipping_matches_torch(world):
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["clipped"] and r["norm_err"] < 1e-4 and r["max_param_err"] < 2e-4, r   # updates are ~1e-2 per step (lr); Adam amplifies fp32 rounding of near-zero gradients
+
+
+def test_train_entry_point_checkpoint_resume_and_metrics(tmp_path):
+    """ppb200.train on 2 pipeline ranks: an interrupted + resumed run ends where the uninterrupted run ends (same data,
+    same dropout masks, optimizer moments restored), with LR schedule, clipping and JSONL metrics on."""
+    import json
+    from tests._workers import train_cli_worker
+    common = ["--model", "ref-small", "--n-layers", "4", "--n-heads", "4", "--dim", "32", "--vocab-size", "61", "--pp", "2",
+              "--schedule", "1F1B", "--n-microbatches", "4", "--global-batch", "8", "--seq-len", "8", "--dtype", "fp32",
+              "--lr", "0.01", "--lr-warmup-steps", "2", "--lr-decay-steps", "6", "--max-grad-norm", "1.0", "--seed", "3"]
+    full = launch_workers(train_cli_worker, 2, (common + ["--steps", "6", "--metrics-path", str(tmp_path / "a.jsonl")],), timeout=300)
+    assert "error" not in full, full
+    part = launch_workers(train_cli_worker, 2, (common + ["--steps", "3", "--save-dir", str(tmp_path / "ck")],), timeout=300)
+    assert "error" not in part, part
+    assert sorted(p.name for p in (tmp_path / "ck").iterdir()) == ["stage_000.pt", "stage_001.pt"]
+    rest = launch_workers(train_cli_worker, 2, (common + ["--steps", "6", "--resume-from", str(tmp_path / "ck")],), timeout=300)
+    assert "error" not in rest, rest
+    assert rest["steps"] == 3 and len(full["losses"]) == 6
+    assert full["losses"][:3] == pytest.approx(part["losses"], abs=1e-6)
+    assert rest["losses"] == pytest.approx(full["losses"][3:], abs=1e-5)
+    assert all(3.0 < l < 6.0 for l in full["losses"])      # fresh random tokens every step: nothing to learn, ~ln(61)
+    recs = [json.loads(l) for l in open(tmp_path / "a.jsonl")]
+    assert [r["step"] for r in recs] == list(range(6))
+    assert recs[0]["lr"] == pytest.approx(0.005) and recs[1]["lr"] == pytest.approx(0.01) and recs[-1]["lr"] < 0.01
+    assert all(r["tokens_per_s"] > 0 and r["grad_norm"] > 0 and 0 <= r["bubble_fraction"] < 1 for r in recs)

@@ -280,3 +280,23 @@ def test_determinism_check_reports_mismatches():
         return (x + (1.0 if state["n"] == 3 else 0.0),)
     res = debug.determinism_check(flaky, reps=5, device="cpu")
     assert res["mismatching"] == 1 and res["worst_abs"] == 1.0
+
+
+def test_token_file_data_gives_next_token_targets(tmp_path):
+    import numpy as np
+    from ppb200.train import TokenData
+    toks = (np.arange(5000) % 97).astype(np.uint16)
+    path = tmp_path / "tokens.bin"
+    toks.tofile(path)
+    cfg = RunConfig(global_batch=8, seq_len=16, data_path=str(path), seed=1, dp=2)
+    d0, d1 = TokenData(cfg, 97, 0, 2), TokenData(cfg, 97, 1, 2)
+    x, y = d0.batch(5)
+    assert x.shape == (4, 16) and y.shape == (4, 16) and x.dtype == torch.int64
+    assert torch.equal(x[:, 1:], y[:, :-1])                      # targets are the inputs shifted by one token
+    assert torch.equal(d0.batch(5)[0], x)                        # deterministic per (step, dp rank)
+    assert not torch.equal(d1.batch(5)[0], x) and not torch.equal(d0.batch(6)[0], x)
+    syn = TokenData(RunConfig(global_batch=4, seq_len=8), 50, 0, 1).batch(0)
+    assert syn[0].shape == (4, 8) and int(syn[0].max()) < 50
+    assert RunConfig(lr=1.0, lr_warmup_steps=4).lr_at(1) == 0.5
+    c = RunConfig(lr=1.0, lr_warmup_steps=0, lr_decay_steps=10, lr_min_ratio=0.1)
+    assert c.lr_at(0) == 1.0 and abs(c.lr_at(10) - 0.1) < 1e-9 and abs(c.lr_at(5) - 0.55) < 1e-9
