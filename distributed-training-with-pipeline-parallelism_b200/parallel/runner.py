@@ -117,6 +117,7 @@ class PipelineSchedule:
             order = sched_ir.parse_schedule(text) if ":" in text else sched_ir.from_csv(text)
         else:
             order = {int(r): [a if isinstance(a, Action) else Action.from_str(a) for a in acts] for r, acts in actions.items()}
+        order = G.expand_overlap(order)       # OVERLAP_F_B groups run as their sub-actions, in order
         for r in range(self.pp_size):
             order.setdefault(r, [])
         comm = (T.SEND_F, T.SEND_B, T.RECV_F, T.RECV_B)

@@ -166,6 +166,32 @@ def split_bw(order: Order) -> Order:
             for r, acts in order.items()}
 
 
+def overlap_f_b(order: Order) -> Order:
+    """Group every adjacent (F of one micro-batch, B of another) pair of the same rank into one ``OVERLAP_F_B`` action
+    (the unit torch's dual-pipe schedules emit, schedules.py:45-113).  Apply to compute-only orders."""
+    out: Order = {}
+    for r, acts in order.items():
+        res: List[Action] = []
+        i = 0
+        while i < len(acts):
+            a = acts[i]
+            nxt = acts[i + 1] if i + 1 < len(acts) else None
+            if nxt is not None and {a.type, nxt.type} == {T.F, T.B} and a.mb != nxt.mb:
+                res.append(Action(a.stage, T.OVERLAP_F_B, a.mb, (a, nxt)))
+                i += 2
+            else:
+                res.append(a)
+                i += 1
+        out[r] = res
+    return out
+
+
+def expand_overlap(order: Order) -> Order:
+    """Replace every ``OVERLAP_F_B`` by its sub-actions, in order (the runner drives one compute stream per rank, so
+    the grouping is an IR-level statement; lowering, validation and simulation work on the expanded lists)."""
+    return {r: [x for a in acts for x in (a.sub if a.sub is not None else (a,))] for r, acts in order.items()}
+
+
 def merge_bw(order: Order) -> Order:
     """Fuse an ``I`` immediately followed by the ``W`` of the same stage and micro-batch back into one ``B``
     (torch _merge_bw, schedules.py:1204): the fused backward shares loads between dgrad and wgrad and skips the

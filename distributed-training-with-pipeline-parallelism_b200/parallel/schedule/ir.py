@@ -28,6 +28,7 @@ class ActionType(enum.Enum):
     OPTIM = "OPTIM"              # fused AdamW step of the stage
     UNSHARD = "UNSHARD"          # FSDP parameter prefetch slot (placeholder: no FSDP in this framework)
     RESHARD = "RESHARD"          # FSDP release slot
+    OVERLAP_F_B = "OVERLAP_F_B"  # a forward and a backward of different micro-batches issued as one unit (sub-actions)
 
     @property
     def is_compute(self) -> bool:
@@ -49,15 +50,24 @@ class Action:
     stage: int
     type: ActionType
     mb: Optional[int] = None
+    sub: Optional[tuple] = None     # OVERLAP_F_B only: the (F, B) actions it groups (torch _Action.sub_actions)
 
     def __str__(self) -> str:
+        if self.sub is not None:    # torch prints "(2F1;2B0)OVERLAP_F_B" (schedules.py:88-113)
+            return "(" + ";".join(str(a) for a in self.sub) + ")" + self.type.value
         return f"{self.stage}{self.type.value}{'' if self.mb is None else self.mb}"
 
     __repr__ = __str__
 
     @staticmethod
     def from_str(s: str) -> "Action":
-        m = _ACTION_RE.match(s.strip())
+        s = s.strip()
+        if s.startswith("(") and s.endswith(")" + ActionType.OVERLAP_F_B.value):
+            subs = tuple(Action.from_str(t) for t in s[1:-len(ActionType.OVERLAP_F_B.value) - 1].split(";") if t.strip())
+            if len(subs) < 2:
+                raise ValueError(f"OVERLAP_F_B needs at least two sub-actions: {s!r}")
+            return Action(subs[0].stage, ActionType.OVERLAP_F_B, subs[0].mb, subs)
+        m = _ACTION_RE.match(s)
         if not m:
             raise ValueError(f"cannot parse schedule action {s!r}")
         stage, typ, mb = int(m.group(1)), ActionType(m.group(2)), m.group(3)

@@ -74,14 +74,15 @@ def test_custom_action_lists_single_rank(tmp_path):
     csv = tmp_path / "sched.csv"
     csv.write_text("0F0,0F1,0I0,0I1,0W1,0W0,0F2,0F3,0I2,0W2,0I3,0W3\n")
     for key, custom in [("B", None), ("dict", {0: "0F0 0I0 0F1 0I1 0W0 0F2 0I2 0W1 0F3 0I3 0W2 0W3".split()}),
-                        ("csv", str(csv)), ("text", "rank0: 0F0 0B0 0F1 0B1 0F2 0I2 0F3 0I3 0W2 0W3")]:
+                        ("csv", str(csv)), ("text", "rank0: 0F0 0B0 0F1 0B1 0F2 0I2 0F3 0I3 0W2 0W3"),
+                        ("overlap", "rank0: 0F0 (0F1;0B0)OVERLAP_F_B (0F2;0B1)OVERLAP_F_B (0F3;0B2)OVERLAP_F_B 0B3")]:
         st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
         sched = make_schedule("1F1B", st, 4, None, actions=custom)
         losses = []
         sched.step(x, target=y, losses=losses)
         grads[key] = (st.grad[:st.n_total].clone(), torch.stack([l.reshape(()) for l in losses]))
         assert not st.deferred_wgrads
-    for key in ("dict", "csv", "text"):
+    for key in ("dict", "csv", "text", "overlap"):
         assert torch.allclose(grads[key][1], grads["B"][1], atol=1e-6)
         assert (grads[key][0] - grads["B"][0]).norm() <= 1e-5 * grads["B"][0].norm(), key
     with pytest.raises(ValueError):      # W without its I

@@ -216,3 +216,15 @@ def test_concept_figures_and_ascii(tmp_path):
     art = diagram.ascii_timeline(tl, span)
     assert art.count("\n") == 3 and art.splitlines()[3].startswith("rank3: ...0aa1")
     assert abs(max(bub.values()) - 3 / 11) < 1e-9
+
+
+def test_overlap_f_b_text_form_and_passes():
+    from ppb200.parallel.schedule import overlap_f_b, expand_overlap, one_f_one_b_order
+    a = Action.from_str("(2F1;2B0)OVERLAP_F_B")
+    assert a.type == T.OVERLAP_F_B and [str(x) for x in a.sub] == ["2F1", "2B0"] and str(a) == "(2F1;2B0)OVERLAP_F_B"
+    assert parse_schedule("rank0: 0F0 (0F1;0B0)OVERLAP_F_B 0B1")[0][1] == a.__class__(0, T.OVERLAP_F_B, 1, (Action(0, T.F, 1), Action(0, T.B, 0)))
+    base = one_f_one_b_order(4, 8)
+    grouped = overlap_f_b(base)
+    assert any(x.type == T.OVERLAP_F_B for x in grouped[0]) and expand_overlap(grouped) == base
+    with pytest.raises(ValueError):
+        Action.from_str("(2F1)OVERLAP_F_B")
