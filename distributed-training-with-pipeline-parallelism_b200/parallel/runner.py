@@ -35,7 +35,7 @@ class PipelineSchedule:
                  schedule: Optional[str] = None, pp_group=None, pp_group_bwd=None, dp_group=None,
                  optimizer: Optional[dict] = None,
                  scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None,
-                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2, actions=None):
+                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2, actions=None, recompute: bool = False):
         self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
         if not self.stages:
             raise ValueError("need at least one stage")
@@ -98,7 +98,11 @@ class PipelineSchedule:
         # CUDA graphs: one forward + one backward graph per (stage, in-flight slot); eager for the first steps
         import os
         want = (os.environ.get("PPB_CUDA_GRAPHS", "1") != "0") if cuda_graphs is None else cuda_graphs
-        self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None and self.tp_size == 1)
+        self.recompute = bool(recompute)    # trade one extra forward per micro-batch for O(1) stashed activations per slot
+        for st in self.stages:
+            st.recompute = self.recompute
+        self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None and self.tp_size == 1
+                               and not self.recompute)
         self.graph_warmup_steps = graph_warmup_steps
         self.nvtx = os.environ.get("PPB_NVTX", "0") == "1"   # NVTX range per action, named with its IR string
         if self.use_graphs:

@@ -58,6 +58,7 @@ class PipelineStage:
         self.deferred_wgrads: Dict[int, list] = {}   # micro-batch -> weight-gradient work recorded by an I action
         self.nslots = 0
         self.graphs = None
+        self.recompute = False    # activation recomputation: forward keeps its input only, backward re-runs the forward
         self.has_params = any(True for _ in submodule.parameters())
 
     # ---- memory layout --------------------------------------------------------------------------------------
@@ -237,17 +238,34 @@ class PipelineStage:
                     out.copy_(g.view(out.shape).to(out.dtype))
                     st["dlogits"] = out
                     self.losses[mb] = loss.detach().reshape(1).float()
-        self.stash[mb] = st
-        self.ctxs[mb] = ctx
         if self.is_last and "dlogits" not in st:
             self.outputs[mb] = out.view(b, S, -1) if ctx.tp is None else out
+        if self.recompute and self.training and loss_fn is None:
+            # activation recomputation: keep only what is needed to run this forward again right before its backward
+            # (the counter-based dropout streams regenerate the same masks from the same seed + offset)
+            st = {"_recompute": (inp, target, loss_scale)}
+        self.stash[mb] = st
+        self.ctxs[mb] = ctx
         return out
+
+    def _rebuild_stash(self, mb: int, st: dict, ctx: Ctx) -> dict:
+        inp, target, loss_scale = st["_recompute"]
+        st = {}
+        with torch.no_grad():
+            out = stage_forward(self.submod, inp, ctx, st)
+            if self.is_last and target is not None and self.submod.output is not None:
+                stage_loss(out, target, loss_scale, st, ctx.tp)
+        return st
 
     def backward_one_chunk(self, mb: int, dout: Optional[torch.Tensor] = None, last: bool = False) -> Optional[torch.Tensor]:
         """Backward for micro-batch ``mb``; ``dout`` is the gradient received from the next stage (None on the last
         stage: the fused loss already left dlogits in the stash).  Returns the input gradient [b*S, d] or None."""
         st = self.stash.pop(mb)
         ctx = self.ctxs.pop(mb)
+        if self.device.type == "cuda":
+            self._set_mb_seed(mb)
+        if "_recompute" in st:
+            st = self._rebuild_stash(mb, st, ctx)
         if dout is None:
             if "dlogits" not in st:
                 raise RuntimeError(f"stage {self.stage_index}: backward of micro-batch {mb} without a gradient or a loss")
@@ -258,8 +276,6 @@ class PipelineStage:
         if fused is not None:
             fused.begin_last_backward()   # this backward's weight-gradient GEMMs carry the DP all-reduce
             self.sink.fused_ar = fused
-        if self.device.type == "cuda":
-            self._set_mb_seed(mb)
         try:
             with torch.no_grad():
                 return stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)

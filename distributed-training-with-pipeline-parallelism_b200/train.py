@@ -110,7 +110,7 @@ def main(argv: Optional[List[str]] = None) -> dict:
     if cfg.resume_from:
         start_step = max(checkpoint.load_stage(st, cfg.resume_from) for st in stages)
     opt = cfg.optimizer_dict()
-    sched = make_schedule(cfg.schedule, stages, cfg.n_microbatches, None, optimizer=opt, **groups)
+    sched = make_schedule(cfg.schedule, stages, cfg.n_microbatches, None, optimizer=opt, recompute=cfg.recompute, **groups)
     first, last = 0 in sched.local, (num_stages - 1) in sched.local
     data = TokenData(cfg, margs.vocab_size, dp_idx, cfg.dp)
     tokens_per_step = cfg.global_batch * cfg.seq_len

@@ -41,6 +41,7 @@ class RunConfig:
     master_port: Optional[int] = None
     trace_path: Optional[str] = None      # chrome trace of the measured timeline
     metrics_path: Optional[str] = None    # JSONL
+    recompute: bool = False               # activation recomputation (memory for one extra forward per micro-batch)
     # ---- training loop (ppb200.train) ----
     log_every: int = 1
     save_dir: Optional[str] = None        # per-(stage, tp rank) shards in the reference state_dict layout

@@ -187,3 +187,26 @@ def test_gradient_clipping_cuda_matches_cpu():
         assert abs(a - b) < 0.05 * a, res
     assert res["cuda"][0][-1] < res["cuda"][0][0]
     assert abs(res["cuda"][0][-1] - res["cpu"][0][-1]) < 3e-2 * res["cpu"][0][-1], res
+
+
+def test_activation_recomputation_cuda():
+    """recompute=True on CUDA (eager launches): same losses and the same training trajectory as the stashing run."""
+    torch.manual_seed(10)
+    args = ModelArgs(dim=256, n_layers=2, n_heads=4, vocab_size=512, ffn_dim=512, dropout=0.1)
+    full = Transformer(args)
+    x = torch.stack([torch.randperm(512)[:128] for _ in range(8)])
+    y = torch.randint(0, 512, (8, 128))
+    res = {}
+    for rc in (False, True):
+        st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cuda"))
+        sched = make_schedule("1F1B", st, 4, None, optimizer={"lr": 1e-3, "weight_decay": 0.0}, cuda_graphs=False, recompute=rc)
+        hist = []
+        for _ in range(3):
+            losses = []
+            sched.step(x.cuda(), target=y.cuda(), losses=losses)
+            hist.append(torch.stack([l.reshape(()) for l in losses]).mean().item())
+        res[rc] = (hist, st.master[:st.n_total].clone())
+        assert sched.use_graphs is False
+    assert max(abs(a - b) for a, b in zip(res[False][0], res[True][0])) < 5e-4, res
+    rel = ((res[False][1] - res[True][1]).norm() / res[False][1].norm()).item()
+    assert rel < 3e-4, rel

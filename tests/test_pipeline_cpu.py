@@ -210,3 +210,28 @@ def test_train_entry_point_checkpoint_resume_and_metrics(tmp_path):
     assert [r["step"] for r in recs] == list(range(6))
     assert recs[0]["lr"] == pytest.approx(0.005) and recs[1]["lr"] == pytest.approx(0.01) and recs[-1]["lr"] < 0.01
     assert all(r["tokens_per_s"] > 0 and r["grad_norm"] > 0 and 0 <= r["bubble_fraction"] < 1 for r in recs)
+
+
+@pytest.mark.parametrize("order", [None, "0F0 0F1 0I0 0I1 0W0 0F2 0W1 0I2 0F3 0I3 0W2 0W3"])
+def test_activation_recomputation_gives_identical_gradients(order):
+    """recompute=True keeps only each micro-batch's stage input and re-runs the forward before its backward; with the
+    counter-based dropout streams the regenerated masks -- hence loss and gradients -- are identical (dropout 0.2)."""
+    import copy
+    import torch
+    from ppb200.api import make_schedule, manual_model_split
+    from ppb200.models import ModelArgs, Transformer
+    torch.manual_seed(9)
+    args = ModelArgs(dim=32, n_layers=2, n_heads=4, vocab_size=41, ffn_dim=48, dropout=0.2)
+    full = Transformer(args)
+    x, y = torch.randint(0, 41, (8, 8)), torch.randint(0, 41, (8, 8))
+    res = {}
+    for rc in (False, True):
+        st = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
+        sched = make_schedule("1F1B", st, 4, None, recompute=rc, actions=None if order is None else {0: order.split()})
+        losses = []
+        sched.step(x, target=y, losses=losses)
+        if rc:
+            assert not st.stash
+        res[rc] = (torch.stack([l.reshape(()) for l in losses]), st.grad[:st.n_total].clone())
+    assert torch.equal(res[False][0], res[True][0])
+    assert torch.allclose(res[False][1], res[True][1], atol=1e-7)
