@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--virtual-stages", type=int, default=1)
     ap.add_argument("--dp", type=int, default=1)
     ap.add_argument("--tp", type=int, default=1, help="intra-stage tensor parallel degree (pre-LN presets, dropout 0)")
-    ap.add_argument("--partition", default="balanced", choices=["reference", "balanced"])
+    ap.add_argument("--partition", default="balanced", choices=["reference", "balanced", "fine"])
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")

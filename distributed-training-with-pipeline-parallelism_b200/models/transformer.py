@@ -225,14 +225,8 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
     return [total, dx_ln]
 
 
-def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
-    """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
-    ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
-    if ctx.tp is not None:
-        from .tp import tp_prenorm_forward
-        return tp_prenorm_forward(L, layer_id, x0, ctx, st)
-    if ctx.args.norm_first:
-        return _prenorm_forward(L, layer_id, x0, ctx, st)
+def _postln_attention_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Self-attention and cross-attention sub-blocks of the post-LN reference layer: x0 -> x2."""
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     st["x0"] = x0
@@ -255,6 +249,29 @@ def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st
         z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p,
                                                       ctx.seed(layer_id, SITE_RES2), rms)
         st.update(q2=q2, kv2=kv2, o2=o2, lse2=lse2, z2=z2, x2=x2, mean2=mean2, rstd2=rstd2)
+    return x2
+
+
+def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
+    ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
+    if ctx.tp is not None:
+        from .tp import tp_prenorm_forward
+        return tp_prenorm_forward(L, layer_id, x0, ctx, st)
+    if ctx.args.norm_first:
+        return _prenorm_forward(L, layer_id, x0, ctx, st)
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    # a stage boundary may fall INSIDE a layer (partition rule 'fine'): part 'attn' = the attention sub-blocks (ends at
+    # x2, the input of the feed-forward block), part 'ffn' = the feed-forward block; 'full' = both
+    part = getattr(L, "part", "full")
+    if part == "ffn":
+        x2 = x0
+        st["x2" if a.cross_attn else "x1"] = x2
+    else:
+        x2 = _postln_attention_forward(L, layer_id, x0, ctx, st)
+        if part == "attn":
+            return x2
     # ---- feed-forward ----
     if a.activation == "relu":
         h = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
@@ -281,7 +298,9 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
         return _prenorm_backward(L, layer_id, dys, ctx, st, G)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms = a.norm == "rmsnorm"
-    x0 = st["x0"]
+    part = getattr(L, "part", "full")
+    if part == "attn":   # the feed-forward block of this layer lives on the next stage: dys are gradients w.r.t. x2
+        return _postln_attention_backward(L, layer_id, list(dys), ctx, st, G)
     # ---- FFN ----
     dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
                           ctx.seed(layer_id, SITE_RES3), rms)
@@ -293,7 +312,17 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
         dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
     G.wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias))
     dx2 = F.linear_dgrad(dh, L.linear1.weight)
-    dys1 = [dz3, dx2]
+    if part == "ffn":
+        return [dz3, dx2]
+    return _postln_attention_backward(L, layer_id, [dz3, dx2], ctx, st, G)
+
+
+def _postln_attention_backward(L: DecoderLayer, layer_id: int, dys1: List[torch.Tensor], ctx: Ctx, st: dict,
+                               G: GradSink) -> List[torch.Tensor]:
+    """Backward of ``_postln_attention_forward``: gradients w.r.t. x2 -> gradients w.r.t. the layer input x0."""
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms = a.norm == "rmsnorm"
+    x0 = st["x0"]
     dx0_extra = None
     # ---- cross-attention ----
     if a.cross_attn:

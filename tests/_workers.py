@@ -10,7 +10,7 @@ if ROOT not in sys.path:
 
 
 def parity_worker(rank, world_size, schedule_type, n_layers, v, m, results_queue, master_port=None, optimizer=None,
-                  dp=1, device="cpu"):
+                  dp=1, device="cpu", rule="reference"):
     """Pipelined loss + per-parameter grads must equal the single-process full-model ones (same seed, dropout 0)."""
     try:
         import torch
@@ -41,7 +41,7 @@ def parity_worker(rank, world_size, schedule_type, n_layers, v, m, results_queue
         stages = []
         for i in range(v):
             mdl = copy.deepcopy(full)
-            st = manual_model_split(mdl, mesh.pp_idx + P * i, num_stages, torch.device("cpu"))
+            st = manual_model_split(mdl, mesh.pp_idx + P * i, num_stages, torch.device("cpu"), rule=rule)
             st.dp_group = mesh.dp_group
             stages.append(st)
         sched = make_schedule(schedule_type, stages, m, None, pp_group=mesh.pp_group, dp_group=mesh.dp_group,

@@ -235,3 +235,15 @@ def test_activation_recomputation_gives_identical_gradients(order):
         res[rc] = (torch.stack([l.reshape(()) for l in losses]), st.grad[:st.n_total].clone())
     assert torch.equal(res[False][0], res[True][0])
     assert torch.allclose(res[False][1], res[True][1], atol=1e-7)
+
+
+@pytest.mark.parametrize("schedule,world,n_layers,v,m", [("1F1B", 4, 5, 1, 4), ("Interleaved1F1B", 2, 4, 2, 4)])
+def test_fine_partition_cuts_inside_layers_and_keeps_parity(schedule, world, n_layers, v, m):
+    """Partition rule 'fine': stage boundaries may fall between the attention sub-blocks and the feed-forward block of a
+    layer; pipelined loss and gradients still equal the single-process ones."""
+    res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), {"rule": "fine"}, timeout=400)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["max_rel_grad_err"] < 2e-4, r
+        if "loss_err" in r:
+            assert r["loss_err"] < 1e-5, r

@@ -50,6 +50,25 @@ def test_prune_and_direct_build_give_the_same_stage_keys():
     assert any(k.startswith("layers.4.") for k in Pn.prune_to_stage(Transformer(args), 2, 3).state_dict())
 
 
+def test_fine_partition_state_dicts_tile_the_full_model():
+    import copy
+    args = ModelArgs(dim=32, n_layers=5, n_heads=4, vocab_size=50, ffn_dim=64, dropout=0.0)
+    full = Transformer(args)
+    keys = set(full.state_dict())
+    seen, cut_inside = set(), False
+    for s in range(4):
+        parts = Pn.stage_layer_parts(5, 4, s, "fine", args, 16)
+        cut_inside |= any(p != "full" for _, p in parts)
+        sd = Pn.prune_to_stage(copy.deepcopy(full), s, 4, rule="fine", seq_len=16).state_dict()
+        assert not (seen & set(sd))                       # every parameter lives on exactly one stage
+        seen |= set(sd)
+        built = Pn.build_stage_model(args, s, 4, rule="fine", seq_len=16, device=torch.device("cpu"), seed=0).state_dict()
+        assert set(built) == set(sd)
+    assert seen == keys and cut_inside
+    units = Pn.fine_unit_ranges(24, 8, ModelArgs(dim=1024, n_layers=24, n_heads=16, vocab_size=50257), 1024)
+    assert units[0][0] == 0 and units[-1][1] == 48 and all(a[1] == b[0] for a, b in zip(units, units[1:]))
+
+
 def test_interleaved_fallback_rule_matches_helper():
     # helper:181-185: two chunks per rank iff n_layers % (2 * world) == 0
     for n_layers, world, want in [(4, 2, 2), (8, 4, 2), (4, 4, 1), (12, 4, 1), (12, 2, 2)]:
