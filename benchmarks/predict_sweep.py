@@ -11,13 +11,11 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from ppb200.models import preset  # noqa: E402
-from ppb200.parallel.partition import stage_ranges  # noqa: E402
-from ppb200.parallel.schedule import ActionType as T, build_schedule, simulate, theoretical_bubble  # noqa: E402
+from ppb200.utils.autotune import UnitCosts, predict  # noqa: E402
 
 ARGS = preset("ref-gpt2-medium")
 SEQ, GLOBAL_BATCH = 1024, 128
-LAYER_F, LAYER_B, HEAD_F, HEAD_B, OPTIM = 0.333, 0.667, 0.67, 0.79, 0.7
-I_FRAC, W_FRAC = 0.78, 0.23
+COSTS = UnitCosts()      # the measured flagship costs
 
 measured = {}
 for f in sorted(os.listdir(os.path.join(ROOT, "profiles"))):
@@ -61,25 +59,14 @@ for P in (2, 4, 8):
                 continue
             if GLOBAL_BATCH % m:
                 continue
-            S = P * v
-            ranges = stage_ranges(ARGS.n_layers, S, "balanced", ARGS, SEQ)
-            scale = (GLOBAL_BATCH // m) * SEQ / 4096.0
-
-            def cost(a, ranges=ranges, S=S, scale=scale):
-                n = ranges[a.stage][1] - ranges[a.stage][0]
-                f = n * LAYER_F + (HEAD_F if a.stage == S - 1 else 0.0)
-                b = n * LAYER_B + (HEAD_B if a.stage == S - 1 else 0.0)
-                return {T.F: f * scale, T.B: b * scale, T.I: b * scale * I_FRAC, T.W: b * scale * W_FRAC,
-                        T.OPTIM: OPTIM / v}.get(a.type, 0.0)
             try:
-                order = build_schedule(sched, P, m, n_virtual=v)
-            except ValueError:
+                pr = predict(ARGS, P, sched, m, GLOBAL_BATCH, SEQ, v, "balanced", COSTS)
+            except (ValueError, RuntimeError):
                 continue
-            res = simulate(order, S, cost=cost)
             meas = measured.get((sched, P, v, m))
-            lines.append(f"| {sched} | {P} | {v} | {m} | {res.makespan:.1f} | {min(res.bubble.values()):.3f} | "
-                         f"{theoretical_bubble(P, m, v):.3f} | {'' if meas is None else f'{meas[0]:.1f}{meas[1]}'} | "
-                         f"{'' if meas is None else f'{meas[0] / res.makespan:.2f}'} |")
+            lines.append(f"| {sched} | {P} | {v} | {m} | {pr['ms']:.1f} | {pr['idle_critical']:.3f} | "
+                         f"{pr['theory']:.3f} | {'' if meas is None else f'{meas[0]:.1f}{meas[1]}'} | "
+                         f"{'' if meas is None else f'{meas[0] / pr['ms']:.2f}'} |")
 out = os.path.join(ROOT, "profiles", "schedule_sweep_predicted.md")
 open(out, "w").write("\n".join(lines) + "\n")
 print("\n".join(lines[7:]))

@@ -228,3 +228,23 @@ def test_overlap_f_b_text_form_and_passes():
     assert any(x.type == T.OVERLAP_F_B for x in grouped[0]) and expand_overlap(grouped) == base
     with pytest.raises(ValueError):
         Action.from_str("(2F1)OVERLAP_F_B")
+
+
+def test_autotuner_predictions_track_the_measured_steps():
+    """Simulator + measured per-action costs reproduce the measured B200 steps of the flagship config (profiles/) and rank
+    the candidates consistently."""
+    from ppb200.models import preset
+    from ppb200.utils.autotune import UnitCosts, predict, recommend
+    a = preset("ref-gpt2-medium")
+    for pp, sched, measured in [(2, "1F1B", 428.8), (4, "1F1B", 260.4), (8, "1F1B", 155.9), (8, "ZeroBubble1F1B", 146.2)]:
+        p = predict(a, pp, sched, 32, 128, 1024, costs=UnitCosts())
+        assert abs(p["ms"] / measured - 1.0) < 0.08, (pp, sched, p["ms"], measured)
+        assert 0.0 <= p["idle_critical"] <= p["idle_max"] < 1.0
+    rows = recommend(a, 8, 128, 1024)
+    assert rows and rows == sorted(rows, key=lambda r: r["ms"])
+    best_1f1b = min(r["ms"] for r in rows if r["schedule"] == "1F1B")
+    best_zb = min(r["ms"] for r in rows if r["schedule"] == "ZeroBubble1F1B")
+    assert best_zb < best_1f1b                          # as measured: 146 vs 156 ms
+    assert all((128 // r["n_microbatches"]) * 1024 >= 4096 for r in rows)
+    llama = UnitCosts.from_model(preset("llama-7b"), 2048)
+    assert llama.layer_f > 5 * UnitCosts().layer_f      # a 7B layer is far more expensive than a GPT-2-medium one
