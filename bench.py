@@ -41,7 +41,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="ref-gpt2-medium")
-    ap.add_argument("--schedule", default="1F1B", choices=["GPipe", "1F1B", "Interleaved1F1B", "ZeroBubble1F1B"])
+    ap.add_argument("--schedule", default="1F1B", choices=["GPipe", "1F1B", "Interleaved1F1B", "ZeroBubble1F1B", "ZeroBubbleInterleaved"])
     ap.add_argument("--global-batch", type=int, default=128)
     ap.add_argument("--seq-len", type=int, default=1024)
     ap.add_argument("--microbatches", type=int, default=32)

@@ -526,6 +526,11 @@ class ScheduleZeroBubble1F1B(PipelineSchedule):
     schedule_name = "ZeroBubble1F1B"
 
 
+class ScheduleZeroBubbleInterleaved(PipelineSchedule):
+    """Interleaved (virtual-stage) visiting order with split backward: bubble ~ (p-1)(F + I - W) / v."""
+    schedule_name = "ZeroBubbleInterleaved"
+
+
 class ScheduleInterleaved1F1B(PipelineSchedule):
     """Virtual stages, depth-first interleaved 1F1B (torch ScheduleInterleaved1F1B, used at helper:220)."""
     schedule_name = "Interleaved1F1B"
@@ -533,10 +538,10 @@ class ScheduleInterleaved1F1B(PipelineSchedule):
 
 def make_schedule(name: str, stages, n_microbatches: int, loss_fn=None, **kw) -> PipelineSchedule:
     cls = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B, "Interleaved1F1B": ScheduleInterleaved1F1B,
-           "ZeroBubble1F1B": ScheduleZeroBubble1F1B}.get(name)
+           "ZeroBubble1F1B": ScheduleZeroBubble1F1B, "ZeroBubbleInterleaved": ScheduleZeroBubbleInterleaved}.get(name)
     if cls is None:
         raise ValueError(f"unknown schedule {name!r}")
-    if name != "Interleaved1F1B" and not isinstance(stages, PipelineStage):
+    if name not in ("Interleaved1F1B", "ZeroBubbleInterleaved") and not isinstance(stages, PipelineStage):
         stages = list(stages)
         if len(stages) != 1:
             raise ValueError(f"{name} runs one stage per rank")

@@ -18,7 +18,7 @@ from .ir import Action, ActionType as T
 Order = Dict[int, List[Action]]
 
 SCHEDULES = ("GPipe", "1F1B", "Interleaved1F1B")   # the reference's three (helper:215-219)
-EXTRA_SCHEDULES = ("ZeroBubble1F1B",)
+EXTRA_SCHEDULES = ("ZeroBubble1F1B", "ZeroBubbleInterleaved")
 
 
 def stage_to_rank_loop(pp_size: int) -> Callable[[int], int]:
@@ -154,6 +154,76 @@ def zero_bubble_order(pp_size: int, n_microbatches: int, max_in_flight: Optional
         t += 1
         if t > 8 * (m + p) + 64:
             raise RuntimeError("zero_bubble_order did not converge")
+    return order
+
+
+def zero_bubble_interleaved_order(pp_size: int, n_virtual: int, n_microbatches: int,
+                                 max_deferred_w: Optional[int] = None) -> Order:
+    """Split-backward list schedule for ``n_virtual`` stages per rank (loop placement, stage = chunk * pp_size + rank):
+    the interleaved-1F1B visiting order (rounds of ``pp_size`` micro-batches per chunk, forward chunks ascending,
+    backward chunks descending) with every backward split into I and W and the W's filling idle ticks.
+
+    Same construction as ``zero_bubble_order``: one action per rank and unit-cost tick, priorities  forced W (more than
+    ``max_deferred_w`` waiting, default ``pp_size * n_virtual``)  >  ready I  >  ready F while the rank holds fewer
+    full activation stashes than interleaved 1F1B would (its warm-up count + 1)  >  pending W.  Every action is issued
+    only after its producers finished in an earlier tick, so the order cannot deadlock."""
+    p, v, m = pp_size, n_virtual, n_microbatches
+    S = p * v
+    done_f: Dict[tuple, int] = {}
+    done_i: Dict[tuple, int] = {}
+    nf = {s: 0 for s in range(S)}          # next micro-batch index per stage, per action type (in-order per stage)
+    ni = {s: 0 for s in range(S)}
+    nw = {s: 0 for s in range(S)}
+    order: Order = {r: [] for r in range(p)}
+    wcap = max_deferred_w if max_deferred_w is not None else p * v
+    BIG = 1 << 60
+    t = 0
+    while any(nw[s] < m for s in range(S)):
+        picks = []
+        for r in range(p):
+            mine = [k * p + r for k in range(v)]
+            cap = min((v - 1) * p + 2 * (p - 1 - r), m * v) + 1
+            live = sum(nf[s] - ni[s] for s in mine)
+            waiting = sum(ni[s] - nw[s] for s in mine)
+            # the next forward / input-gradient of a rank is fixed by the interleaved visiting order (no skipping ahead:
+            # a rank that ran later rounds of chunk 0 early would fill its stash budget and starve the deeper chunks)
+            todo_i = [s for s in mine if ni[s] < m]
+            todo_f = [s for s in mine if nf[s] < m]
+            ready_i, ready_f = [], []
+            if todo_i:
+                s = min(todo_i, key=lambda s: (ni[s] // p, -(s // p), ni[s]))          # backward: last chunk first
+                if done_f.get((s, ni[s]), BIG) <= t and (s == S - 1 or done_i.get((s + 1, ni[s]), BIG) <= t):
+                    ready_i = [s]
+            if todo_f:
+                s = min(todo_f, key=lambda s: (nf[s] // p, s // p, nf[s]))             # forward: first chunk first
+                if s == 0 or done_f.get((s - 1, nf[s]), BIG) <= t:
+                    ready_f = [s]
+            pending_w = [s for s in mine if nw[s] < ni[s]]
+            if waiting >= wcap and pending_w:
+                s = min(pending_w, key=lambda s: (nw[s] // p, -(s // p), nw[s]))
+                picks.append((r, T.W, s, nw[s]))
+            elif ready_i:
+                s = min(ready_i, key=lambda s: (ni[s] // p, -(s // p), ni[s]))      # backward: last chunk first
+                picks.append((r, T.I, s, ni[s]))
+            elif ready_f and live < cap:
+                s = min(ready_f, key=lambda s: (nf[s] // p, s // p, nf[s]))         # forward: first chunk first
+                picks.append((r, T.F, s, nf[s]))
+            elif pending_w:
+                s = min(pending_w, key=lambda s: (nw[s] // p, -(s // p), nw[s]))
+                picks.append((r, T.W, s, nw[s]))
+        for r, typ, s, k in picks:
+            order[r].append(Action(s, typ, k))
+            if typ == T.F:
+                done_f[(s, k)] = t + 1
+                nf[s] += 1
+            elif typ == T.I:
+                done_i[(s, k)] = t + 1
+                ni[s] += 1
+            else:
+                nw[s] += 1
+        t += 1
+        if t > 16 * (m * v + p) + 256:
+            raise RuntimeError("zero_bubble_interleaved_order did not converge")
     return order
 
 
@@ -407,6 +477,8 @@ def build_schedule(name: str, pp_size: int, n_microbatches: int, n_virtual: int 
         if n_virtual != 1:
             raise ValueError("ZeroBubble1F1B runs one stage per rank")
         order = merge_bw(zero_bubble_order(pp_size, n_microbatches))
+    elif name == "ZeroBubbleInterleaved":
+        order = merge_bw(zero_bubble_interleaved_order(pp_size, n_virtual, n_microbatches))
     else:
         raise ValueError(f"unknown schedule {name!r}; expected one of {SCHEDULES + EXTRA_SCHEDULES}")
     num_stages = pp_size * n_virtual

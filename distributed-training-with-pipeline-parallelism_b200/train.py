@@ -94,7 +94,7 @@ def main(argv: Optional[List[str]] = None) -> dict:
 
     margs = cfg.model_args()
     margs.dtype = torch.bfloat16 if (use_cuda and cfg.dtype == "bf16") else torch.float32
-    v = cfg.virtual_stages if cfg.schedule == "Interleaved1F1B" else 1
+    v = cfg.virtual_stages if "Interleaved" in cfg.schedule else 1
     num_stages = cfg.pp * v
     stages = []
     for i in range(v):

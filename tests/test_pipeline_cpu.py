@@ -18,6 +18,8 @@ pytestmark = pytest.mark.timeout(600)
     ("Interleaved1F1B", 4, 8, 2, 8),
     ("ZeroBubble1F1B", 2, 4, 1, 4),       # backward split into I / W actions
     ("ZeroBubble1F1B", 4, 4, 1, 8),
+    ("ZeroBubbleInterleaved", 2, 4, 2, 4),    # virtual stages + split backward
+    ("ZeroBubbleInterleaved", 4, 8, 2, 8),
 ])
 def test_pipeline_matches_single_process(schedule, world, n_layers, v, m):
     res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), timeout=400)

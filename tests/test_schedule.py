@@ -248,3 +248,20 @@ def test_autotuner_predictions_track_the_measured_steps():
     assert all((128 // r["n_microbatches"]) * 1024 >= 4096 for r in rows)
     llama = UnitCosts.from_model(preset("llama-7b"), 2048)
     assert llama.layer_f > 5 * UnitCosts().layer_f      # a 7B layer is far more expensive than a GPT-2-medium one
+
+
+@pytest.mark.parametrize("p,v,m", [(2, 2, 4), (4, 2, 8), (4, 3, 8), (8, 2, 32), (2, 3, 6)])
+def test_zero_bubble_interleaved_is_valid_and_beats_both_parents(p, v, m):
+    from ppb200.parallel.schedule import zero_bubble_interleaved_order
+    raw = zero_bubble_interleaved_order(p, v, m)
+    for r, acts in raw.items():
+        assert {a.stage % p for a in acts} == {r}                                   # loop placement
+        for typ in (T.F, T.I, T.W):
+            assert sum(a.type == typ for a in acts) == m * v
+    order = build_schedule("ZeroBubbleInterleaved", p, m, n_virtual=v)              # validates internally
+    kw = dict(f_cost=1.0 / v, b_cost=2.0 / v)
+    zbi = simulate(order, p * v, **kw).makespan
+    inter = simulate(build_schedule("Interleaved1F1B", p, m, n_virtual=v), p * v, **kw).makespan
+    zb = simulate(build_schedule("ZeroBubble1F1B", p, m), p).makespan
+    assert zbi < inter and zbi <= zb
+    assert zbi <= 3 * m + (p - 1) / v + 1e-9 + 1.0 / v          # bubble of ZB-H1 divided by the number of chunks (+ one slot)
