@@ -28,7 +28,7 @@ def _color(a: Action, pp_size: int) -> str:
     chunk = a.stage // max(1, pp_size)
     if a.type == T.F:
         return _F_COLORS[chunk % len(_F_COLORS)]
-    if a.type == T.B:
+    if a.type in (T.B, T.I):
         return _B_COLORS[chunk % len(_B_COLORS)]
     return _OTHER.get(a.type.value, "#cccccc")
 
@@ -57,6 +57,7 @@ def svg_timeline(timeline: Dict[int, Sequence[Tuple[Action, float, float]]], mak
     out.append(f'<rect x="{left}" y="{y - 9}" width="10" height="10" fill="{_F_COLORS[0]}"/><text x="{left + 14}" y="{y}">forward</text>')
     out.append(f'<rect x="{left + 70}" y="{y - 9}" width="10" height="10" fill="{_B_COLORS[0]}"/><text x="{left + 84}" y="{y}">backward</text>')
     out.append(f'<rect x="{left + 150}" y="{y - 9}" width="10" height="10" fill="#f0f0f0" stroke="#ccc"/><text x="{left + 164}" y="{y}">idle (bubble)</text>')
+    out.append(f'<rect x="{left + 250}" y="{y - 9}" width="10" height="10" fill="{_OTHER["W"]}"/><text x="{left + 264}" y="{y}">weight gradient (W)</text>')
     out.append("</svg>")
     return "\n".join(out)
 
@@ -96,7 +97,8 @@ def write_concept_figures(out_dir: str, pp_size: int = 4, n_microbatches: int = 
     specs = [("bubble", "GPipe", pp_size, 1, 1, "Naive model parallelism (1 micro-batch): only one stage works at a time"),
              ("gpipe", "GPipe", pp_size, n_microbatches, 1, f"GPipe, {pp_size} stages x {n_microbatches} micro-batches"),
              ("1f1b", "1F1B", pp_size, n_microbatches, 1, f"1F1B, {pp_size} stages x {n_microbatches} micro-batches (same bubble, <= P micro-batches in flight)"),
-             ("interleave", "Interleaved1F1B", pp_size, n_microbatches, 2, f"Interleaved 1F1B, {pp_size} ranks x 2 virtual stages x {n_microbatches} micro-batches")]
+             ("interleave", "Interleaved1F1B", pp_size, n_microbatches, 2, f"Interleaved 1F1B, {pp_size} ranks x 2 virtual stages x {n_microbatches} micro-batches"),
+             ("zerobubble", "ZeroBubble1F1B", pp_size, n_microbatches, 1, f"ZeroBubble1F1B, {pp_size} stages x {n_microbatches} micro-batches: backward = I (green) + W (yellow)")]
     for fname, sched, P, m, v, title in specs:
         tl, span, bub = timeline_of(sched, P, m, v)
         title = f"{title} -- bubble {max(bub.values()):.3f} (theory {theoretical_bubble(P, m, v):.3f})"

@@ -208,7 +208,7 @@ def test_validator_rejects_w_before_i():
 def test_concept_figures_and_ascii(tmp_path):
     from ppb200.utils import diagram
     paths = diagram.write_concept_figures(str(tmp_path))
-    assert len(paths) == 4
+    assert len(paths) == 5
     for p in paths:
         txt = open(p).read()
         assert txt.startswith("<svg") and txt.rstrip().endswith("</svg>")
