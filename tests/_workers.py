@@ -248,3 +248,59 @@ def train_cli_worker(rank, world_size, argv, results_queue, master_port=None):
     except Exception as e:  # noqa: BLE001
         traceback.print_exc()
         results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def tp_clip_worker(rank, world_size, results_queue, master_port=None, max_norm=0.05):
+    """tp=2 (x pp): the global gradient norm counts sharded parameters once per shard and replicated ones once; the
+    clipped AdamW update equals torch's on the unsharded model."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.models.tp import shard_model_for_tp, shard_tensor
+        from ppb200.api import make_schedule
+        from ppb200.parallel.partition import prune_to_stage
+        from ppb200.parallel.stage import PipelineStage
+        from ppb200.parallel.mesh import init_mesh
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        mesh = init_mesh(dp_size=1, pp_size=world_size // 2, tp_size=2)
+        P = mesh.pp_size
+        args = ModelArgs(dim=64, n_layers=2 * P, n_heads=4, vocab_size=61, ffn_dim=96, dropout=0.0, causal=True,
+                         cross_attn=False, activation="swiglu", norm_first=True, norm="rmsnorm", rope=True)
+        torch.manual_seed(6)
+        full = Transformer(args)
+        x, y = torch.randint(0, 61, (8, 16)), torch.randint(0, 61, (8, 16))
+        oracle = copy.deepcopy(full)
+        opt = torch.optim.AdamW(oracle.parameters(), lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0)
+        norms = []
+        for _ in range(2):
+            opt.zero_grad()
+            torch.nn.functional.cross_entropy(oracle(x).reshape(-1, 61), y.reshape(-1)).backward()
+            norms.append(float(torch.nn.utils.clip_grad_norm_(oracle.parameters(), max_norm)))
+            opt.step()
+        want = dict(oracle.state_dict())
+        mdl = copy.deepcopy(full)
+        prune_to_stage(mdl, mesh.pp_idx, P)
+        shard_model_for_tp(mdl, mesh.tp_idx, 2)
+        st = PipelineStage(mdl, mesh.pp_idx, P, torch.device("cpu"), tp_group=mesh.tp_group)
+        sched = make_schedule("1F1B", st, 4, None, pp_group=mesh.pp_group, pp_group_bwd=mesh.pp_group_bwd,
+                              optimizer={"lr": 1e-2, "betas": (0.9, 0.95), "eps": 1e-8, "weight_decay": 0.0, "max_grad_norm": max_norm})
+        first, last = 0 in sched.local, (P - 1) in sched.local
+        got = []
+        for _ in range(2):
+            sched.step(*((x,) if first else ()), target=y if last else None, losses=[] if last else None)
+            got.append(float(sched.last_grad_norm_sq.sqrt()) / 4)
+        err = max((v - shard_tensor(k, want[k], args.n_heads, mesh.tp_idx, 2, True)).abs().max().item()
+                  for k, v in st.state_dict().items())
+        out = {"rank": rank, "max_param_err": err, "norm_err": max(abs(a - b) for a, b in zip(norms, got))}
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, out)
+        if rank == 0:
+            results_queue.put({"ranks": gathered})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

@@ -249,3 +249,12 @@ def test_fine_partition_cuts_inside_layers_and_keeps_parity(schedule, world, n_l
         assert r["max_rel_grad_err"] < 2e-4, r
         if "loss_err" in r:
             assert r["loss_err"] < 1e-5, r
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_gradient_clipping_with_tensor_parallel_shards(world):
+    from tests._workers import tp_clip_worker
+    res = launch_workers(tp_clip_worker, world, (), timeout=300)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["norm_err"] < 1e-4 and r["max_param_err"] < 2e-4, r
