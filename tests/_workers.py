@@ -118,7 +118,7 @@ def train_worker(rank, world_size, schedule_type, results_queue, master_port=Non
 
 
 def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_port=None, act="gelu", norm="rmsnorm",
-                     split_bw=False, rope=False, dp=1):
+                     split_bw=False, rope=False, dp=1, recompute=False):
     """(pp x tp) mesh, pre-LN block: loss and per-parameter gradients (each rank's SHARD of them) must equal the
     single-process full-model ones."""
     try:
@@ -156,7 +156,7 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
             from ppb200.parallel.schedule import zero_bubble_order
             custom = zero_bubble_order(P, m)
         sched = make_schedule("1F1B", st, m, None, pp_group=mesh.pp_group, pp_group_bwd=mesh.pp_group_bwd, optimizer=None,
-                              actions=custom, dp_group=mesh.dp_group)
+                              actions=custom, dp_group=mesh.dp_group, recompute=recompute)
         losses = []
         first, last = 0 in sched.local, (P - 1) in sched.local
         Bl = B // dp

@@ -98,12 +98,14 @@ def test_custom_action_lists_single_rank(tmp_path):
     (4, 2, 4, 4, "relu", "layernorm", False, False),    # pp2 x tp2
     (4, 2, 4, 4, "gelu", "rmsnorm", True, False),       # pp2 x tp2 with split backward (I/W) actions
     (4, 2, 4, 4, "swiglu", "rmsnorm", False, True),     # Llama-style block (SwiGLU + RoPE), pp2 x tp2
+    (4, 2, 4, 4, "swiglu", "layernorm", True, True),    # same with split backward + activation recomputation (norm name flags it)
 ])
 def test_tensor_parallel_stage_matches_single_process(world, tp, n_layers, m, act, norm, split, rope):
     from tests._workers import tp_parity_worker
     dp = 2 if world < 0 else 1
     res = launch_workers(tp_parity_worker, abs(world), (tp, n_layers, m),
-                         {"act": act, "norm": norm, "split_bw": split, "rope": rope, "dp": dp}, timeout=400)
+                         {"act": act, "norm": "rmsnorm" if (split and rope) else norm, "split_bw": split, "rope": rope, "dp": dp,
+                          "recompute": bool(split and rope)}, timeout=400)
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["max_rel_grad_err"] < 2e-4, r
