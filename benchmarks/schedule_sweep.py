@@ -21,7 +21,8 @@ from ppb200.parallel.stage import PipelineStage  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--microbatches", default="4,8,16,32,64")
-ap.add_argument("--schedules", default="GPipe,1F1B,Interleaved1F1B")
+ap.add_argument("--schedules", default="GPipe,1F1B,Interleaved1F1B,ZeroBubble1F1B,ZeroBubbleInterleaved")
+ap.add_argument("--partition", default="balanced", choices=["reference", "balanced", "fine"])
 ap.add_argument("--global-batch", type=int, default=128)
 ap.add_argument("--seq-len", type=int, default=1024)
 ap.add_argument("--steps", type=int, default=2)
@@ -39,7 +40,7 @@ margs = preset(a.model, dtype=torch.bfloat16)
 rows = []
 for sched_name in a.schedules.split(","):
     v = 1
-    if sched_name == "Interleaved1F1B":
+    if "Interleaved" in sched_name:
         for cand in (2, 3, 4):
             if margs.n_layers % (world * cand) == 0:
                 v = cand
@@ -47,7 +48,7 @@ for sched_name in a.schedules.split(","):
     for m in [int(x) for x in a.microbatches.split(",")]:
         if sched_name != "GPipe" and m < world:
             continue
-        if sched_name == "Interleaved1F1B" and m % max(1, m // world) != 0:
+        if "Interleaved" in sched_name and m % max(1, m // world) != 0:
             continue
         if a.global_batch % m != 0:
             continue
@@ -55,7 +56,7 @@ for sched_name in a.schedules.split(","):
             stages = []
             for i in range(v):
                 sidx = rank + world * i
-                model = build_stage_model(margs, sidx, world * v, rule="balanced", seq_len=a.seq_len, device=dev, seed=1)
+                model = build_stage_model(margs, sidx, world * v, rule=a.partition, seq_len=a.seq_len, device=dev, seed=1)
                 stages.append(PipelineStage(model, sidx, world * v, dev))
             sched = make_schedule(sched_name, stages, m, None, pp_group=mesh.pp_group, pp_group_bwd=mesh.pp_group_bwd,
                                   optimizer={"lr": 1e-4})

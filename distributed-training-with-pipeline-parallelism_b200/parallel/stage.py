@@ -181,6 +181,7 @@ class PipelineStage:
         self.ctxs.clear()
         self.outputs.clear()
         self.losses.clear()
+        self.deferred_wgrads.clear()
         if self.device.type == "cuda" and self._materialized:
             self.seed_offset.fill_(self.step_count * 0x632BE5AB)
 
