@@ -126,6 +126,8 @@ def _gelu_bwd(dh: torch.Tensor, hpre: torch.Tensor) -> torch.Tensor:
 def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> torch.Tensor:
     """x_in: this rank's [T/tp, d] rows of the residual stream.  Returns the same rows of the layer output."""
     a, tp = ctx.args, ctx.tp
+    if getattr(L, "part", "full") != "full":
+        raise NotImplementedError("tensor parallelism with stage boundaries inside a layer (partition 'fine') is not implemented")
     dl, Hl = a.dim // tp.tp, a.n_heads // tp.tp
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)

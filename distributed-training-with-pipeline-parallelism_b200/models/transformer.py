@@ -166,6 +166,11 @@ def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ct
     """Pre-LN (GPT-style) block:  x += drop(attn(LN1(x)));  x += drop(ffn(LN3(x)))   -- causal self-attention only."""
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    part = getattr(L, "part", "full")      # 'attn' / 'ffn': the stage boundary falls inside this layer (partition 'fine')
+    if part == "ffn":                      # input = the residual stream after the attention block
+        z3 = x_in
+        _, y3, mean3, rstd3 = F.add_dropout_norm_fwd(z3, None, L.norm3.weight, L.norm3.bias, eps, 0.0, 0, rms, need_z=False)
+        return _prenorm_ffn_forward(L, layer_id, z3, y3, mean3, rstd3, ctx, st)
     _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
     qkv = F.linear_fwd(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
     if a.rope:   # q and k are adjacent column blocks of the packed activation: one in-place pass over 2H heads
@@ -173,9 +178,17 @@ def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ct
     o1, lse1 = F.attention_fwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], ctx.B, H, a.causal, None, p,
                                ctx.seed(layer_id, SITE_ATTN1))
     a1 = F.linear_fwd(o1, L.self_attn.out_proj.weight, L.self_attn.out_proj.bias)
+    st.update(x_in=x_in, y1=y1, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1)
+    if part == "attn":                     # the feed-forward block (and norm3) live on the next stage
+        return F.add_dropout_fwd(x_in, a1, p, ctx.seed(layer_id, SITE_RES1))
     # residual add + dropout fused with the NEXT norm: z3 is the updated residual stream, y3 = LN3(z3)
     z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, p,
                                                   ctx.seed(layer_id, SITE_RES1), rms)
+    return _prenorm_ffn_forward(L, layer_id, z3, y3, mean3, rstd3, ctx, st)
+
+
+def _prenorm_ffn_forward(L: DecoderLayer, layer_id: int, z3, y3, mean3, rstd3, ctx: Ctx, st: dict) -> torch.Tensor:
+    a, p = ctx.args, ctx.p
     if a.activation == "relu":
         h = F.linear_fwd(y3, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
         st["h"] = h
@@ -189,7 +202,7 @@ def _prenorm_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ct
         st.update(hpre=hpre, h=h)
     a3 = F.linear_fwd(h, L.linear2.weight, L.linear2.bias)
     x_out = F.add_dropout_fwd(z3, a3, p, ctx.seed(layer_id, SITE_RES3))
-    st.update(x_in=x_in, y1=y1, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1, z3=z3, y3=y3, mean3=mean3, rstd3=rstd3)
+    st.update(z3=z3, y3=y3, mean3=mean3, rstd3=rstd3)
     return x_out
 
 
@@ -197,6 +210,10 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
                       G: "GradSink") -> List[torch.Tensor]:
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms = a.norm == "rmsnorm"
+    part = getattr(L, "part", "full")
+    if part == "attn":      # dys are gradients w.r.t. z3 (the residual stream after the attention block)
+        total, da1 = F.sum_dropout_bwd(list(dys), p, ctx.seed(layer_id, SITE_RES1))
+        return _prenorm_attention_backward(L, layer_id, total, da1, ctx, st, G)
     g, da3 = F.sum_dropout_bwd(dys, p, ctx.seed(layer_id, SITE_RES3))          # d x_out, and through the FFN dropout
     G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
     if a.activation == "relu":
@@ -209,7 +226,16 @@ def _prenorm_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor
     dy3 = F.linear_dgrad(dh, L.linear1.weight)
     dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
                            0.0, 0, rms, need_da=False)
+    if part == "ffn":
+        return [g, dz3_ln]
     total, da1 = F.sum_dropout_bwd([g, dz3_ln], p, ctx.seed(layer_id, SITE_RES1))  # d z3 = residual + through LN3
+    return _prenorm_attention_backward(L, layer_id, total, da1, ctx, st, G)
+
+
+def _prenorm_attention_backward(L: DecoderLayer, layer_id: int, total: torch.Tensor, da1: torch.Tensor, ctx: Ctx, st: dict,
+                                G: "GradSink") -> List[torch.Tensor]:
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms = a.norm == "rmsnorm"
     G.wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias))
     do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
     qkv = st["qkv"]

@@ -105,8 +105,9 @@ def _min_max_partition(costs: List[float], num_stages: int, tail_cost: float) ->
 
 
 def fine_unit_ranges(n_layers: int, num_stages: int, args: ModelArgs, seq_len: int = 1024) -> List[Tuple[int, int]]:
-    """Stage boundaries at HALF-layer granularity for the post-LN reference block: unit 2i = the attention sub-blocks of
-    layer i (self + cross attention, ends at the input of the feed-forward block), unit 2i+1 = its feed-forward block.
+    """Stage boundaries at HALF-layer granularity: unit 2i = the attention sub-blocks of layer i (post-LN reference block:
+    self + cross attention, ends at the input of the feed-forward block; pre-LN block: attention + its residual add),
+    unit 2i+1 = its feed-forward block.
     Returns [u0, u1) unit ranges.  Only one [tokens, d] tensor crosses such a cut (the cross-attention memory is the
     layer input, so a cut between the two attention blocks would have to ship two).  At 8 stages the flagship model
     goes from a most expensive stage of 4.0 layer-equivalents (whole layers) to 3.7."""
@@ -135,8 +136,7 @@ def stage_ranges(n_layers: int, num_stages: int, rule: str = "reference", args: 
 
 
 def _fine_units(n_layers: int, num_stages: int, args: Optional[ModelArgs], seq_len: int):
-    if args is None or args.norm_first:
-        # the pre-LN block fuses the residual add with the next norm; it is cut at whole layers
+    if args is None:
         return [(2 * a, 2 * b) for a, b in balanced_ranges(n_layers, num_stages, args, seq_len)]
     return fine_unit_ranges(n_layers, num_stages, args, seq_len)
 

@@ -86,7 +86,7 @@ def recommend(args: ModelArgs, pp: int, global_batch: int, seq_len: int, microba
     if microbatches is None:
         microbatches = [m for m in (4, 8, 16, 32, 64, 128) if global_batch % m == 0]
     rows: List[dict] = []
-    rules = ("balanced",) if args.norm_first else ("balanced", "fine")
+    rules = ("balanced", "fine")
     for sched in ("GPipe", "1F1B", "Interleaved1F1B", "ZeroBubble1F1B", "ZeroBubbleInterleaved"):
         for v in (range(2, max_virtual + 1) if "Interleaved" in sched else (1,)):
             if args.n_layers < pp * v:

@@ -260,3 +260,37 @@ def test_gradient_clipping_with_tensor_parallel_shards(world):
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["norm_err"] < 1e-4 and r["max_param_err"] < 2e-4, r
+
+
+@pytest.mark.parametrize("act,rope", [("gelu", False), ("swiglu", True)])
+def test_fine_partition_of_the_prenorm_block(act, rope):
+    """Pre-LN (GPT / Llama) layers cut between the attention residual and the feed-forward block: three virtual stages on
+    one rank (no communication needed) against the unsplit model."""
+    import copy
+    import torch
+    from ppb200.api import make_schedule, manual_model_split
+    from ppb200.models import ModelArgs, Transformer
+    from ppb200.parallel.partition import stage_layer_parts
+    torch.manual_seed(12)
+    args = ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=47, ffn_dim=96, dropout=0.1, causal=True, cross_attn=False,
+                     activation=act, norm_first=True, norm="rmsnorm", rope=rope)
+    full = Transformer(args)
+    x, y = torch.randint(0, 47, (6, 16)), torch.randint(0, 47, (6, 16))
+    one = manual_model_split(copy.deepcopy(full), 0, 1, torch.device("cpu"))
+    s1 = make_schedule("GPipe", one, 3, None)
+    l1 = []
+    s1.step(x, target=y, losses=l1)
+    assert any(p != "full" for s in range(3) for _, p in stage_layer_parts(4, 3, s, "fine", args, 16))
+    stages = [manual_model_split(copy.deepcopy(full), s, 3, torch.device("cpu"), rule="fine") for s in range(3)]
+    s3 = make_schedule("Interleaved1F1B", stages, 3, None)
+    l3 = []
+    s3.step(x, target=y, losses=l3)
+    assert torch.allclose(torch.stack([l.reshape(()) for l in l1]), torch.stack([l.reshape(()) for l in l3]), atol=1e-6)
+    ref = one.grad_views()
+    seen = set()
+    for st in stages:
+        for n, g in st.grad_views().items():
+            assert n not in seen
+            seen.add(n)
+            assert (g - ref[n]).abs().max().item() <= 2e-5 * (ref[n].abs().max().item() + 1e-6), n
+    assert seen == set(ref)
