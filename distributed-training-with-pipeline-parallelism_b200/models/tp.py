@@ -21,7 +21,9 @@ Sharded parameters keep the reference's key names; split dims (for checkpoint me
     everything else (norms, out_proj.bias, linear2.bias, embedding, head) is replicated; its gradient is computed
     on the local token rows and summed over the tp group once per step (``PipelineStage.reduce_tp_grads``).
 
-Dropout must be 0 on this path (Llama-style models have none): the column shards would need per-rank mask streams.
+Dropout (attention probabilities, the two residual branches) works with per-rank mask streams: the tensor-parallel
+rank is mixed into every seed, so ranks draw independent masks for their rows / heads.  Only the ReLU block's extra
+dropout on the hidden activations is not available here (its fused ReLU+dropout epilogue lives in the plain GEMM).
 """
 from __future__ import annotations
 
@@ -68,8 +70,9 @@ def shard_model_for_tp(model, tp_rank: int, tp_size: int):
         return model
     if not a.norm_first or a.cross_attn:
         raise ValueError("tensor parallelism is implemented for the pre-LN block (norm_first=True, cross_attn=False)")
-    if a.dropout != 0.0:
-        raise ValueError("tensor parallelism needs dropout=0 (per-rank mask streams for column shards are not implemented)")
+    if a.dropout != 0.0 and a.activation == "relu":
+        raise ValueError("tensor parallelism with dropout needs activation 'gelu' or 'swiglu' (the ReLU block also drops "
+                         "the hidden activations, which the all-gather->GEMM epilogue does not do)")
     if a.n_heads % tp_size or a.ffn_dim % tp_size or (a.ffn_dim // tp_size) % 8 or (a.dim // tp_size) % 8:
         raise ValueError(f"heads ({a.n_heads}) and ffn_dim ({a.ffn_dim}) must divide by tp={tp_size} into multiples of 8 columns")
     for name, p in list(model.named_parameters()):
@@ -123,20 +126,29 @@ def _gelu_bwd(dh: torch.Tensor, hpre: torch.Tensor) -> torch.Tensor:
     return (dh.float() * (cdf + a * pdf)).to(dh.dtype)
 
 
+def _tp_seed(ctx, layer_id: int, site: int) -> int:
+    """Dropout stream of one site on THIS tensor-parallel rank: the ranks hold different token rows / heads under the same
+    local indices, so the rank is mixed into the seed (independent masks; forward and backward use the same value)."""
+    return (ctx.seed(layer_id, site) + 0x5851F42D4C957F2D * (ctx.tp.rank + 1)) & ((1 << 64) - 1)
+
+
 def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> torch.Tensor:
     """x_in: this rank's [T/tp, d] rows of the residual stream.  Returns the same rows of the layer output."""
     a, tp = ctx.args, ctx.tp
     if getattr(L, "part", "full") != "full":
         raise NotImplementedError("tensor parallelism with stage boundaries inside a layer (partition 'fine') is not implemented")
     dl, Hl = a.dim // tp.tp, a.n_heads // tp.tp
-    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    rms, eps, p = a.norm == "rmsnorm", a.layer_norm_eps, ctx.p
+    from .transformer import SITE_ATTN1, SITE_RES1, SITE_RES3
     _, y1, mean1, rstd1 = F.add_dropout_norm_fwd(x_in, None, L.norm1.weight, L.norm1.bias, eps, 0.0, 0, rms, need_z=False)
     qkv, y1_full = tp.ag_linear(y1, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
     if a.rope:
         F.rope_(qkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta)
-    o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, 0.0, 0)
+    o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, p,
+                               _tp_seed(ctx, layer_id, SITE_ATTN1))
     a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x_in.dtype)
-    z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, 0.0, 0, rms)
+    z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, p,
+                                                  _tp_seed(ctx, layer_id, SITE_RES1), rms)
     if a.activation == "relu":
         h, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias, "relu")
     elif a.activation == "swiglu":
@@ -148,7 +160,7 @@ def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> t
         h = F.gelu_fwd(hpre)
         st["hpre"] = hpre
     a3 = _rs_finish(tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x_in.dtype)
-    x_out = F.add_dropout_fwd(z3, a3, 0.0, 0)
+    x_out = F.add_dropout_fwd(z3, a3, p, _tp_seed(ctx, layer_id, SITE_RES3))
     st.update(x_in=x_in, y1_full=y1_full, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1, z3=z3, y3_full=y3_full,
               mean3=mean3, rstd3=rstd3, h=h)
     return x_out
@@ -157,12 +169,13 @@ def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> t
 def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: dict, G) -> List[torch.Tensor]:
     a, tp = ctx.args, ctx.tp
     dl, Hl = a.dim // tp.tp, a.n_heads // tp.tp
-    rms = a.norm == "rmsnorm"
-    g, _ = F.sum_dropout_bwd(dys, 0.0, 0)                               # d x_out rows == d a3 rows
-    # linear2 (row-parallel):  d h_local = gather(g) @ W2_local ;  dW2_local += gather(g)^T h_local
-    dh, g_full = tp.ag_linear(g, L.linear2.weight, w_mn_major=True)
+    rms, p = a.norm == "rmsnorm", ctx.p
+    from .transformer import SITE_ATTN1, SITE_RES1, SITE_RES3
+    g, da3 = F.sum_dropout_bwd(dys, p, _tp_seed(ctx, layer_id, SITE_RES3))    # d x_out rows; d a3 = dropout'(d x_out)
+    # linear2 (row-parallel):  d h_local = gather(d a3) @ W2_local ;  dW2_local += gather(d a3)^T h_local
+    dh, g_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True)
     G.wgrad(g_full, st["h"], G(L.linear2.weight), None)
-    G.bias_grad(g, G(L.linear2.bias))
+    G.bias_grad(da3, G(L.linear2.bias))
     if a.activation == "relu":
         dh = torch.where(st["h"] > 0, dh, torch.zeros_like(dh))
     elif a.activation == "swiglu":
@@ -174,14 +187,14 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     dy3 = tp.linear_rs(dh, L.linear1.weight, w_mn_major=True).to(g.dtype)
     dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
                            0.0, 0, rms, need_da=False)
-    total, _ = F.sum_dropout_bwd([g, dz3_ln], 0.0, 0)                  # d z3 rows == d a1 rows
-    do1, t_full = tp.ag_linear(total, L.self_attn.out_proj.weight, w_mn_major=True)
+    total, da1 = F.sum_dropout_bwd([g, dz3_ln], p, _tp_seed(ctx, layer_id, SITE_RES1))   # d z3 rows; d a1 = dropout'(d z3)
+    do1, t_full = tp.ag_linear(da1, L.self_attn.out_proj.weight, w_mn_major=True)
     G.wgrad(t_full, st["o1"], G(L.self_attn.out_proj.weight), None)
-    G.bias_grad(total, G(L.self_attn.out_proj.bias))
+    G.bias_grad(da1, G(L.self_attn.out_proj.bias))
     qkv = st["qkv"]
     dqkv = torch.empty_like(qkv)
     F.attention_bwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], st["o1"], do1, st["lse1"], ctx.B, Hl, a.causal, None,
-                    0.0, 0, out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
+                    p, _tp_seed(ctx, layer_id, SITE_ATTN1), out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
     if a.rope:
         F.rope_(dqkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta, inverse=True)
     G.wgrad(dqkv, st["y1_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))

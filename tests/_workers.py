@@ -304,3 +304,79 @@ def tp_clip_worker(rank, world_size, results_queue, master_port=None, max_norm=0
     except Exception as e:  # noqa: BLE001
         traceback.print_exc()
         results_queue.put({"error": f"rank {rank}: {e}"})
+
+
+def tp_dropout_worker(rank, world_size, results_queue, master_port=None):
+    """tp=2 with dropout on: the explicit backward is the gradient of the (fixed-mask) forward -- central finite
+    difference along a random direction over all sharded and replicated parameters -- and the run is reproducible."""
+    try:
+        import torch
+        import torch.distributed as dist
+        from ppb200.models import ModelArgs, Transformer
+        from ppb200.models.tp import shard_model_for_tp
+        from ppb200.api import make_schedule
+        from ppb200.parallel.stage import PipelineStage
+        from ppb200.parallel.mesh import init_mesh
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world_size))
+        torch.set_num_threads(1)
+        dist.init_process_group("gloo", rank=rank, world_size=world_size)
+        mesh = init_mesh(dp_size=1, pp_size=1, tp_size=2)
+        args = ModelArgs(dim=64, n_layers=2, n_heads=4, vocab_size=61, ffn_dim=96, dropout=0.2, causal=True, cross_attn=False,
+                         activation="gelu", norm_first=True, norm="layernorm")
+        torch.manual_seed(8)
+        full = Transformer(args).double()
+        x, y = torch.randint(0, 61, (4, 16)), torch.randint(0, 61, (4, 16))
+
+        def build():
+            mdl = copy.deepcopy(full)
+            shard_model_for_tp(mdl, mesh.tp_idx, 2)
+            st = PipelineStage(mdl, 0, 1, torch.device("cpu"), tp_group=mesh.tp_group)
+            st.materialize(dtype=torch.float32)
+            return st, make_schedule("1F1B", st, 2, None, pp_group=mesh.pp_group)
+
+        def loss_of(sched):
+            losses = []
+            sched.step(x, target=y, losses=losses)
+            return float(torch.stack([l.reshape(()) for l in losses]).mean())
+
+        st, sched = build()
+        l0 = loss_of(sched)
+        g = st.grad[:st.n_total].clone()
+        st2, sched2 = build()
+        same = loss_of(sched2) == l0 and torch.equal(st2.grad[:st2.n_total], g)
+        # direction: replicated parameters get the same numbers on both ranks, shards get rank-specific ones
+        v = torch.zeros_like(g)
+        rep = set(st.tp_replicated)
+        for n, o, shp in st.param_names:
+            k = int(torch.Size(shp).numel())
+            import zlib
+            gen = torch.Generator().manual_seed(zlib.crc32(n.encode()) % 100000 + (0 if (o, k) in rep else 7 * (rank + 1)))
+            v[o:o + k] = torch.randn(k, generator=gen)
+        dot_sh = torch.zeros(1, dtype=torch.float64)
+        dot_rep = torch.zeros(1, dtype=torch.float64)
+        for n, o, shp in st.param_names:
+            k = int(torch.Size(shp).numel())
+            d = (g[o:o + k].double() * v[o:o + k].double()).sum()
+            if (o, k) in rep:
+                dot_rep += d
+            else:
+                dot_sh += d
+        dist.all_reduce(dot_sh, group=mesh.tp_group)
+        pred = float(dot_sh + dot_rep)
+        eps = 1e-3
+        vals = []
+        for sgn in (+1.0, -1.0):
+            stp, schp = build()
+            stp.param_arena[:stp.n_total].add_(v, alpha=sgn * eps)
+            vals.append(loss_of(schp))
+        fd = (vals[0] - vals[1]) / (2 * eps)
+        out = {"rank": rank, "reproducible": bool(same), "fd": fd, "pred": pred, "dropout_active": abs(l0) > 0}
+        gathered = [None] * world_size
+        dist.all_gather_object(gathered, out)
+        if rank == 0:
+            results_queue.put({"ranks": gathered})
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        traceback.print_exc()
+        results_queue.put({"error": f"rank {rank}: {e}"})

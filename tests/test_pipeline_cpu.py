@@ -294,3 +294,12 @@ def test_fine_partition_of_the_prenorm_block(act, rope):
             seen.add(n)
             assert (g - ref[n]).abs().max().item() <= 2e-5 * (ref[n].abs().max().item() + 1e-6), n
     assert seen == set(ref)
+
+
+def test_tensor_parallel_with_dropout_backward_matches_finite_differences():
+    from tests._workers import tp_dropout_worker
+    res = launch_workers(tp_dropout_worker, 2, (), timeout=300)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["reproducible"], r
+        assert abs(r["fd"] - r["pred"]) < 3e-2 * abs(r["pred"]) + 1e-4, r
