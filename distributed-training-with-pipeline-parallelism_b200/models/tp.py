@@ -35,6 +35,7 @@ import torch.nn as nn
 from ..ops import functional as F
 
 SHARD_DIM = {"self_attn.in_proj_weight": "qkv0", "self_attn.in_proj_bias": "qkv0", "self_attn.out_proj.weight": 1,
+             "multihead_attn.in_proj_weight": "qkv0", "multihead_attn.in_proj_bias": "qkv0", "multihead_attn.out_proj.weight": 1,
              "linear1.weight": 0, "linear1.bias": 0, "linear2.weight": 1}
 # with activation == 'swiglu' linear1 packs gate | up on dim 0: each half is split separately ("pair0")
 
@@ -68,11 +69,10 @@ def shard_model_for_tp(model, tp_rank: int, tp_size: int):
     a = model.args
     if tp_size == 1:
         return model
-    if not a.norm_first or a.cross_attn:
-        raise ValueError("tensor parallelism is implemented for the pre-LN block (norm_first=True, cross_attn=False)")
-    if a.dropout != 0.0 and a.activation == "relu":
-        raise ValueError("tensor parallelism with dropout needs activation 'gelu' or 'swiglu' (the ReLU block also drops "
-                         "the hidden activations, which the all-gather->GEMM epilogue does not do)")
+    if a.norm_first and a.dropout != 0.0 and a.activation == "relu":
+        raise ValueError("tensor parallelism of the pre-LN block with dropout needs activation 'gelu' or 'swiglu'")
+    if not a.norm_first and not a.cross_attn:
+        raise ValueError("the post-LN tensor-parallel program is the reference block (self + cross attention)")
     if a.n_heads % tp_size or a.ffn_dim % tp_size or (a.ffn_dim // tp_size) % 8 or (a.dim // tp_size) % 8:
         raise ValueError(f"heads ({a.n_heads}) and ffn_dim ({a.ffn_dim}) must divide by tp={tp_size} into multiples of 8 columns")
     for name, p in list(model.named_parameters()):
@@ -202,3 +202,95 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
                           0.0, 0, rms, need_da=False)
     return [total, dx_ln]
+
+
+# ------------------------------------------------------------------------------------------------------------
+# the reference's post-LN block (self-attention, cross-attention over the layer input, ReLU/GELU FFN) under TP
+# ------------------------------------------------------------------------------------------------------------
+def tp_postln_forward(L, layer_id: int, x0: torch.Tensor, ctx, st: dict) -> torch.Tensor:
+    """x0: this rank's [T/tp, d] rows.  Same layout as the pre-LN program; the cross-attention block adds a
+    column-parallel q projection of x1 and a column-parallel kv projection of the (already gathered) layer input."""
+    from .transformer import SITE_ATTN1, SITE_ATTN2, SITE_FFN, SITE_RES1, SITE_RES2, SITE_RES3
+    a, tp = ctx.args, ctx.tp
+    if getattr(L, "part", "full") != "full":
+        raise NotImplementedError("tensor parallelism with stage boundaries inside a layer (partition 'fine') is not implemented")
+    dl, Hl, p = a.dim // tp.tp, a.n_heads // tp.tp, ctx.p
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    sd = lambda site: _tp_seed(ctx, layer_id, site)   # noqa: E731
+    # ---- self-attention ----
+    qkv, x0_full = tp.ag_linear(x0, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
+    o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, p, sd(SITE_ATTN1))
+    a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x0.dtype)
+    z1, x1, mean1, rstd1 = F.add_dropout_norm_fwd(x0, a1, L.norm1.weight, L.norm1.bias, eps, p, sd(SITE_RES1), rms)
+    # ---- cross-attention: q from x1, k/v from the layer input ----
+    W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
+    q2, x1_full = tp.ag_linear(x1, W[:dl], bvec[:dl])
+    kv2 = F.linear_fwd(x0_full, W[dl:], bvec[dl:])
+    o2, lse2 = F.attention_fwd(q2, kv2[:, :dl], kv2[:, dl:], ctx.B, Hl, False, None, p, sd(SITE_ATTN2))
+    a2 = _rs_finish(tp.linear_rs(o2, L.multihead_attn.out_proj.weight), L.multihead_attn.out_proj.bias, x0.dtype)
+    z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p, sd(SITE_RES2), rms)
+    # ---- feed-forward ----
+    if a.activation == "relu":
+        h, x2_full = tp.ag_linear(x2, L.linear1.weight, L.linear1.bias, "relu")
+        if p > 0:   # the reference block also drops hidden activations; dropped entries stay 0, which is all backward needs
+            h = F.add_dropout_fwd(torch.zeros_like(h), h, p, sd(SITE_FFN))
+    else:
+        hpre, x2_full = tp.ag_linear(x2, L.linear1.weight, L.linear1.bias)
+        h = F.gelu_fwd(hpre)
+        st["hpre"] = hpre
+    a3 = _rs_finish(tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x0.dtype)
+    z3, x3, mean3, rstd3 = F.add_dropout_norm_fwd(x2, a3, L.norm3.weight, L.norm3.bias, eps, p, sd(SITE_RES3), rms)
+    st.update(x0_full=x0_full, qkv=qkv, o1=o1, lse1=lse1, z1=z1, mean1=mean1, rstd1=rstd1, x1_full=x1_full, q2=q2, kv2=kv2,
+              o2=o2, lse2=lse2, z2=z2, mean2=mean2, rstd2=rstd2, x2_full=x2_full, h=h, z3=z3, mean3=mean3, rstd3=rstd3)
+    return x3
+
+
+def tp_postln_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: dict, G) -> List[torch.Tensor]:
+    from .transformer import SITE_ATTN1, SITE_ATTN2, SITE_RES1, SITE_RES2, SITE_RES3
+    a, tp = ctx.args, ctx.tp
+    dl, Hl, p = a.dim // tp.tp, a.n_heads // tp.tp, ctx.p
+    rms = a.norm == "rmsnorm"
+    sd = lambda site: _tp_seed(ctx, layer_id, site)   # noqa: E731
+    # ---- FFN ----
+    dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
+                          sd(SITE_RES3), rms)
+    dtype = dz3.dtype
+    dh, da3_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True)
+    G.wgrad(da3_full, st["h"], G(L.linear2.weight), None)
+    G.bias_grad(da3, G(L.linear2.bias))
+    if a.activation == "relu":
+        dh = torch.where(st["h"] > 0, dh * (1.0 / (1.0 - p)) if p > 0 else dh, torch.zeros_like(dh))
+    else:
+        dh = _gelu_bwd(dh, st["hpre"])
+    G.wgrad(dh, st["x2_full"], G(L.linear1.weight), G(L.linear1.bias))
+    dx2 = tp.linear_rs(dh, L.linear1.weight, w_mn_major=True).to(dtype)
+    # ---- cross-attention ----
+    W = L.multihead_attn.in_proj_weight
+    gW, gb = G(W), G(L.multihead_attn.in_proj_bias)
+    dz2, da2 = F.norm_bwd([dz3, dx2], st["z2"], st["mean2"], st["rstd2"], L.norm2.weight, G(L.norm2.weight), G(L.norm2.bias),
+                          p, sd(SITE_RES2), rms)
+    do2, da2_full = tp.ag_linear(da2, L.multihead_attn.out_proj.weight, w_mn_major=True)
+    G.wgrad(da2_full, st["o2"], G(L.multihead_attn.out_proj.weight), None)
+    G.bias_grad(da2, G(L.multihead_attn.out_proj.bias))
+    kv2 = st["kv2"]
+    dq2 = torch.empty_like(st["q2"])
+    dkv2 = torch.empty_like(kv2)
+    F.attention_bwd(st["q2"], kv2[:, :dl], kv2[:, dl:], st["o2"], do2, st["lse2"], ctx.B, Hl, False, None, p, sd(SITE_ATTN2),
+                    out=(dq2, dkv2[:, :dl], dkv2[:, dl:]))
+    G.wgrad(dq2, st["x1_full"], gW[:dl], gb[:dl])
+    G.wgrad(dkv2, st["x0_full"], gW[dl:], gb[dl:])
+    dx1 = tp.linear_rs(dq2, W[:dl], w_mn_major=True).to(dtype).clone()       # the reduce-scatter buffer is reused two calls on
+    dx0_extra = tp.linear_rs(dkv2, W[dl:], w_mn_major=True).to(dtype).clone()
+    # ---- self-attention ----
+    dz1, da1 = F.norm_bwd([dz2, dx1], st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
+                          p, sd(SITE_RES1), rms)
+    do1, da1_full = tp.ag_linear(da1, L.self_attn.out_proj.weight, w_mn_major=True)
+    G.wgrad(da1_full, st["o1"], G(L.self_attn.out_proj.weight), None)
+    G.bias_grad(da1, G(L.self_attn.out_proj.bias))
+    qkv = st["qkv"]
+    dqkv = torch.empty_like(qkv)
+    F.attention_bwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], st["o1"], do1, st["lse1"], ctx.B, Hl, a.causal, None, p,
+                    sd(SITE_ATTN1), out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
+    G.wgrad(dqkv, st["x0_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
+    dx0 = tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True).to(dtype)
+    return [dz1, dx0, dx0_extra]

@@ -282,8 +282,8 @@ def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st
     """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
     ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
     if ctx.tp is not None:
-        from .tp import tp_prenorm_forward
-        return tp_prenorm_forward(L, layer_id, x0, ctx, st)
+        from .tp import tp_postln_forward, tp_prenorm_forward
+        return (tp_prenorm_forward if ctx.args.norm_first else tp_postln_forward)(L, layer_id, x0, ctx, st)
     if ctx.args.norm_first:
         return _prenorm_forward(L, layer_id, x0, ctx, st)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
@@ -318,8 +318,8 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
     """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. x3 (summed on load by the norm
     kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. x0."""
     if ctx.tp is not None:
-        from .tp import tp_prenorm_backward
-        return tp_prenorm_backward(L, layer_id, dys, ctx, st, G)
+        from .tp import tp_postln_backward, tp_prenorm_backward
+        return (tp_prenorm_backward if ctx.args.norm_first else tp_postln_backward)(L, layer_id, dys, ctx, st, G)
     if ctx.args.norm_first:
         return _prenorm_backward(L, layer_id, dys, ctx, st, G)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p

@@ -300,8 +300,8 @@ class TPComm:
 
     # ---- GEMM -> reduce-scatter ---------------------------------------------------------------------------------
     def linear_rs(self, x: torch.Tensor, w: torch.Tensor, w_mn_major: bool = False) -> torch.Tensor:
-        """Rows of sum_over_ranks(x_r @ op(w_r)) owned by this rank, fp32 [T/tp, d].  The result is valid until the
-        second-next call (copy or convert it right away).  w is [d, K_local] (or [K_local, d] when w_mn_major)."""
+        """Rows of sum_over_ranks(x_r @ op(w_r)) owned by this rank, fp32 [T/tp, d].  The result lives in a symmetric buffer
+        that the NEXT call re-zeroes: copy or convert it right away.  w is [d, K_local] (or [K_local, d] when w_mn_major)."""
         import torch.distributed as dist
         if not self.cuda:
             y = (x @ (w if w_mn_major else w.t())).float()
@@ -309,7 +309,7 @@ class TPComm:
             return y[self.rank * self.rows:(self.rank + 1) * self.rows]
         cur, other = self.y_sym[self.ky], self.y_sym[self.ky ^ 1]
         self.ky ^= 1
-        other.tensor.zero_()   # consumed two calls ago; peers start adding to it only after the barrier below
+        other.tensor.zero_()   # the previous call's result (already copied out); peers add to it only after the barrier below
         linear_reducescatter(x, w, cur.ptrs, self.d, w_mn_major=w_mn_major)
         cur.barrier(1)
         return cur.tensor

@@ -118,7 +118,7 @@ def train_worker(rank, world_size, schedule_type, results_queue, master_port=Non
 
 
 def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_port=None, act="gelu", norm="rmsnorm",
-                     split_bw=False, rope=False, dp=1, recompute=False):
+                     split_bw=False, rope=False, dp=1, recompute=False, postln=False):
     """(pp x tp) mesh, pre-LN block: loss and per-parameter gradients (each rank's SHARD of them) must equal the
     single-process full-model ones."""
     try:
@@ -137,6 +137,9 @@ def tp_parity_worker(rank, world_size, tp, n_layers, m, results_queue, master_po
         P = mesh.pp_size
         args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0, causal=True,
                          cross_attn=False, activation=act, norm_first=True, norm=norm, rope=rope)
+        if postln:   # the reference's own block: post-LN, self + cross attention
+            args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0, activation=act,
+                             norm=norm)
         torch.manual_seed(4321)
         full = Transformer(args)
         B, S = 8 * dp, 16
@@ -306,7 +309,7 @@ def tp_clip_worker(rank, world_size, results_queue, master_port=None, max_norm=0
         results_queue.put({"error": f"rank {rank}: {e}"})
 
 
-def tp_dropout_worker(rank, world_size, results_queue, master_port=None):
+def tp_dropout_worker(rank, world_size, results_queue, master_port=None, postln=False):
     """tp=2 with dropout on: the explicit backward is the gradient of the (fixed-mask) forward -- central finite
     difference along a random direction over all sharded and replicated parameters -- and the run is reproducible."""
     try:
@@ -323,6 +326,8 @@ def tp_dropout_worker(rank, world_size, results_queue, master_port=None):
         mesh = init_mesh(dp_size=1, pp_size=1, tp_size=2)
         args = ModelArgs(dim=64, n_layers=2, n_heads=4, vocab_size=61, ffn_dim=96, dropout=0.2, causal=True, cross_attn=False,
                          activation="gelu", norm_first=True, norm="layernorm")
+        if postln:   # reference block with ReLU + hidden dropout
+            args = ModelArgs(dim=64, n_layers=2, n_heads=4, vocab_size=61, ffn_dim=96, dropout=0.2)
         torch.manual_seed(8)
         full = Transformer(args).double()
         x, y = torch.randint(0, 61, (4, 16)), torch.randint(0, 61, (4, 16))

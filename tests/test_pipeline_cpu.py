@@ -296,10 +296,23 @@ def test_fine_partition_of_the_prenorm_block(act, rope):
     assert seen == set(ref)
 
 
-def test_tensor_parallel_with_dropout_backward_matches_finite_differences():
+@pytest.mark.parametrize("postln", [False, True])
+def test_tensor_parallel_with_dropout_backward_matches_finite_differences(postln):
     from tests._workers import tp_dropout_worker
-    res = launch_workers(tp_dropout_worker, 2, (), timeout=300)
+    res = launch_workers(tp_dropout_worker, 2, (), {"postln": postln}, timeout=300)
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["reproducible"], r
         assert abs(r["fd"] - r["pred"]) < 3e-2 * abs(r["pred"]) + 1e-4, r
+
+
+@pytest.mark.parametrize("world,act", [(2, "relu"), (4, "gelu")])
+def test_tensor_parallel_reference_block_matches_single_process(world, act):
+    """The reference's post-LN block (self + cross attention) under tensor + sequence parallelism, tp2 and pp2 x tp2."""
+    from tests._workers import tp_parity_worker
+    res = launch_workers(tp_parity_worker, world, (2, world, 4), {"act": act, "norm": "layernorm", "postln": True}, timeout=400)
+    assert "error" not in res, res
+    for r in res["ranks"]:
+        assert r["max_rel_grad_err"] < 2e-4, r
+        if "loss_err" in r:
+            assert r["loss_err"] < 1e-5, r
