@@ -125,6 +125,12 @@ def test_tp_shard_merge_roundtrip():
     assert shards[0]["layers.0.linear2.weight"].shape == (32, 24)
     merged = merge_tp_shards(shards, 4)
     assert all(torch.equal(merged[k], sd[k]) for k in sd)
+    ref_sd = Transformer(ModelArgs(dim=32, n_layers=1, n_heads=4, vocab_size=50, ffn_dim=48)).state_dict()   # reference block
+    parts = [{k: shard_tensor(k, v, 4, r, 4) for k, v in ref_sd.items()} for r in range(4)]
+    assert parts[0]["layers.0.multihead_attn.in_proj_weight"].shape == (24, 32)
+    assert parts[0]["layers.0.multihead_attn.out_proj.weight"].shape == (32, 8)
+    back = merge_tp_shards(parts, 4)
+    assert all(torch.equal(back[k], ref_sd[k]) for k in ref_sd)
 
 
 def test_uneven_microbatches_follow_tensor_split_semantics():
