@@ -48,7 +48,8 @@ def parse():
     ap.add_argument("--virtual-stages", type=int, default=1)
     ap.add_argument("--dp", type=int, default=1)
     ap.add_argument("--tp", type=int, default=1, help="intra-stage tensor parallel degree (pre-LN presets, dropout 0)")
-    ap.add_argument("--partition", default="balanced", choices=["reference", "balanced", "fine"])
+    ap.add_argument("--partition", default="auto", choices=["auto", "reference", "balanced", "fine"],
+                    help="auto = measure the per-unit costs on the GPU, cut inside layers when that lowers the largest stage")
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
@@ -63,6 +64,17 @@ def env_rank():
 
 def emit(obj):
     print(json.dumps(obj), flush=True)
+
+
+def config_dict(a, dims: dict, parallelism: str) -> dict:
+    """The SAME dict from both arms (driver check `same_config`): what is measured, nothing about how."""
+    return {"model": {"name": a.model, "dim": dims["dim"], "n_layers": dims["n_layers"], "n_heads": dims["n_heads"],
+                      "vocab": dims["vocab_size"], "ffn": dims.get("ffn_dim", 2048), "dropout": dims.get("dropout", 0.1),
+                      "block": dims.get("block", "nn.TransformerDecoderLayer semantics: post-LN, self + cross attention over the layer input, ReLU")},
+            "global_batch": a.global_batch, "seq_len": a.seq_len, "n_microbatches": a.microbatches,
+            "schedule": a.schedule, "parallelism": parallelism,
+            "optimizer": "AdamW lr 1e-4 betas (0.9, 0.95) wd 0.1, fused, inside the timed region",
+            "l2": "inputs >> L2: >2 GB of weights+activations touched per step per GPU, no explicit flush"}
 
 
 def max_over_ranks(val: float, device) -> float:
@@ -124,15 +136,21 @@ def run_ours(a, rank, local_rank, world):
     margs = preset(a.model, **over)
     v = a.virtual_stages
     num_stages = P * v
+    from ppb200.parallel import partition as Pn
+    unit_ms = None
+    if a.partition in ("auto", "balanced", "fine") and num_stages > 1 and a.tp == 1:
+        # stage boundaries are chosen from per-unit forward+backward times MEASURED here (about a second), not from constants
+        unit_ms = Pn.calibrate(margs, a.global_batch // a.dp // a.microbatches, a.seq_len, dev)
+    rule = Pn.resolve_rule(a.partition, margs.n_layers, num_stages, margs, a.seq_len, tp=a.tp)
     stages = []
     for i in range(v):
         sidx = pp_idx + P * i
-        model = build_stage_model(margs, sidx, num_stages, rule=a.partition, seq_len=a.seq_len, device=dev, seed=1234)
+        model = build_stage_model(margs, sidx, num_stages, rule=rule, seq_len=a.seq_len, device=dev, seed=1234)
         if a.tp > 1:
             from ppb200.models.tp import shard_model_for_tp
             shard_model_for_tp(model, tp_idx, a.tp)
         st = PipelineStage(model, sidx, num_stages, dev, group=pp_group, dp_group=dp_group, tp_group=tp_group)
-        st.base_seed = 1234
+        st.base_seed = 1234 + 0x9E37 * dp_idx   # replicas draw different dropout masks
         stages.append(st)
     opt = {"lr": 1e-4, "betas": (0.9, 0.95), "weight_decay": 0.1}
     sched = make_schedule(a.schedule, stages, a.microbatches, None, pp_group=pp_group, pp_group_bwd=pp_group_bwd,
@@ -200,7 +218,8 @@ def run_ours(a, rank, local_rank, world):
     peak_mem = max_over_ranks(torch.cuda.max_memory_allocated(dev) / 2**30, dev)
     loss_t = torch.tensor([loss_val if loss_val is not None else -1.0], dtype=torch.float64, device=dev)
     summ = {k: round(v, 3) for k, v in sched.summary().items()}
-    summ["layers"] = [len(st.submod.layers) for st in stages]
+    summ["layers"] = [[f"{k}:{getattr(l, 'part', 'full')}" if getattr(l, 'part', 'full') != 'full' else k
+                       for k, l in st.submod.layers.items()] for st in stages]
     per_rank = [summ]
     if world > 1:
         dist.all_reduce(loss_t, op=dist.ReduceOp.MAX)
@@ -215,10 +234,13 @@ def run_ours(a, rank, local_rank, world):
             "value": tokens / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic random tokens, random-init weights", "impl": "ours",
-            "config": {"model": f"{'helper LM @ GPT-2 medium' if a.model == 'ref-gpt2-medium' else 'LM'} ({a.model}: dim {margs.dim}, {margs.n_layers} layers, {margs.n_heads} heads, vocab {margs.vocab_size}, ffn {margs.ffn_dim}, dropout {margs.dropout})",
-                       "global_batch": a.global_batch, "seq_len": S, "n_microbatches": a.microbatches, "schedule": a.schedule,
-                       "parallelism": par, "partition": a.partition, "optimizer": "fused AdamW (in timed region)",
-                       "l2": "inputs >> L2: >2 GB of weights+activations touched per step per GPU, no explicit flush"},
+            "config": config_dict(a, {"dim": margs.dim, "n_layers": margs.n_layers, "n_heads": margs.n_heads,
+                                      "vocab_size": margs.vocab_size, "ffn_dim": margs.ffn_dim, "dropout": margs.dropout,
+                                      **({} if a.model.startswith("ref-") else {"block": a.model})}, par),
+            "impl_notes": {"partition": rule, "partition_requested": a.partition,
+                           "partition_note": "the one real difference to the reference arm: stage boundaries are balanced on measured per-unit times (and may fall inside a layer); the reference uses helper:70-75 (n_layers // stages, remainder to the last stage)",
+                           "unit_costs_ms": ({k: (round(v, 4) if isinstance(v, float) else v) for k, v in unit_ms.items()} if unit_ms else None),
+                           "stack": "ppb200: explicit fused fwd/bwd stage program, libppb200.so sm_100a kernels, CUDA graphs per slot, NCCL p2p"},
             "bubble_fraction_measured_max": bubble, "bubble_fraction_critical_rank": bubble_min,
             "bubble_fraction_theory": sched.theory_bubble,
             "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
@@ -363,10 +385,10 @@ def run_reference(a, rank, local_rank, world):
                 "value": B * S / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic random tokens, random-init weights", "impl": "reference",
-                "config": {"model": f"{'helper LM @ GPT-2 medium' if a.model == 'ref-gpt2-medium' else 'LM'} ({a.model}: {dims})", "global_batch": B, "seq_len": S,
-                           "n_microbatches": a.microbatches, "schedule": a.schedule, "parallelism": f"pp{world}" + (f"xv{v}" if v > 1 else ""),
-                           "partition": "reference (helper:70-75)", "optimizer": "torch.optim.AdamW(fused=True) after schedule.step (in timed region)",
-                           "stack": "unmodified helper Transformer/manual_model_split + torch.distributed.pipelining + NCCL p2p + cuBLAS/SDPA, bf16 parameters"},
+                "config": config_dict(a, {"dim": margs.dim, "n_layers": margs.n_layers, "n_heads": margs.n_heads,
+                                          "vocab_size": margs.vocab_size}, f"pp{world}" + (f"xv{v}" if v > 1 else "")),
+                "impl_notes": {"partition": "reference (helper:70-75)",
+                               "stack": "unmodified helper Transformer/manual_model_split + torch.distributed.pipelining + NCCL p2p + cuBLAS/SDPA, bf16 parameters, torch.optim.AdamW(fused=True) after schedule.step"},
                 "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": 0, "clocks": clocks, "e2e": e2e,
             })
     except Exception as e:  # noqa: BLE001

@@ -44,22 +44,35 @@ def sources() -> list[str]:
     return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _deps_mtime() -> float:
-    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-    hdrs.append(os.path.join(ROOT, "include", "ppb200.h"))
-    return max(os.path.getmtime(h) for h in hdrs)
+def _fingerprint(src: str) -> str:
+    """Content hash of everything an object file depends on: its source, every header, the flags and the compiler.
+    Staleness is decided by CONTENT, not by mtimes, so a stale .o/.so pair (fresh checkout, copied tree, clock skew)
+    can never pass as up to date."""
+    import hashlib
+    h = hashlib.sha256()
+    files = [os.path.join(CSRC, src)] + sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
+    files.append(os.path.join(ROOT, "include", "ppb200.h"))
+    for f in files:
+        h.update(f.encode())
+        h.update(open(f, "rb").read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(nvcc_path().encode())
+    return h.hexdigest()
 
 
 def compile_one(src: str, force: bool, verbose: bool) -> tuple[str, str]:
     obj = os.path.join(BUILD, src.replace(".cu", ".o"))
+    stamp = obj + ".sha256"
     spath = os.path.join(CSRC, src)
-    if (not force and os.path.exists(obj)
-            and os.path.getmtime(obj) > max(os.path.getmtime(spath), _deps_mtime())):
+    fp = _fingerprint(src)
+    if not force and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read().strip() == fp:
         return obj, ""
     cmd = [nvcc_path(), *NVCC_FLAGS, "-Xptxas", "-v" if verbose else "-warn-spills", "-c", spath, "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+    with open(stamp, "w") as f:
+        f.write(fp)
     return obj, r.stderr
 
 
@@ -72,12 +85,16 @@ def build(force: bool = False, verbose: bool = False) -> str:
         results = list(ex.map(lambda s: compile_one(s, force, verbose), srcs))
     objs = [o for o, _ in results]
     logs = [l for _, l in results if l]
-    newest_obj = max(os.path.getmtime(o) for o in objs)
-    if force or not os.path.exists(LIB) or os.path.getmtime(LIB) < newest_obj:
+    # the library is stamped with the fingerprints of the objects it was linked from
+    lib_fp = "\n".join(open(o + ".sha256").read().strip() for o in objs)
+    lib_stamp = os.path.join(BUILD, "libppb200.so.sha256")
+    if (force or not os.path.exists(LIB) or not os.path.exists(lib_stamp) or open(lib_stamp).read() != lib_fp):
         cmd = [nvcc_path(), "-shared", "-o", LIB, *objs, "-lcudart"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        with open(lib_stamp, "w") as f:
+            f.write(lib_fp)
     if verbose:
         print("\n".join(logs))
     return LIB

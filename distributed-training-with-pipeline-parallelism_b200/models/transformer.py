@@ -251,62 +251,100 @@ def _prenorm_attention_backward(L: DecoderLayer, layer_id: int, total: torch.Ten
     return [total, dx_ln]
 
 
-def _postln_attention_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
-    """Self-attention and cross-attention sub-blocks of the post-LN reference layer: x0 -> x2."""
+# Units of the post-LN reference layer (partition rule 'fine' may put a stage boundary behind any of them):
+#   'self'  : x0 -> x1 = LN1(x0 + drop(SelfAttn(x0)))
+#   'cross' : (x1, x0) -> x2 = LN2(x1 + drop(CrossAttn(q = x1, memory = x0)))
+#   'ffn'   : x2 -> x3 = LN3(x2 + drop(W2 drop(relu(W1 x2))))
+# A cut behind 'self' has to carry BOTH x1 and the layer input x0 (the cross-attention memory): the boundary tensor is
+# the row-wise packing [x1 ; x0] of shape [2T, d], and its gradient is [d x1 ; d x0 (cross-attention share)].
+_PARTS = {"full": ("self", "cross", "ffn"), "attn": ("self", "cross"), "self": ("self",), "cross": ("cross",),
+          "cross+ffn": ("cross", "ffn"), "ffn": ("ffn",)}
+
+
+def part_io_rows(part_first: str, part_last: str, cross_attn: bool) -> tuple:
+    """(input rows multiplier, output rows multiplier) of a stage whose first / last layer own these parts."""
+    if not cross_attn:
+        return 1, 1
+    return (2 if _PARTS[part_first][0] == "cross" else 1), (2 if _PARTS[part_last][-1] == "self" else 1)
+
+
+def _postln_self_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict, packed_out: bool) -> torch.Tensor:
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     st["x0"] = x0
-    # ---- self-attention ----
     qkv = F.linear_fwd(x0, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
     o1, lse1 = F.attention_fwd(qkv[:, :d], qkv[:, d:2 * d], qkv[:, 2 * d:], ctx.B, H, a.causal, None, p,
                                ctx.seed(layer_id, SITE_ATTN1))
     a1 = F.linear_fwd(o1, L.self_attn.out_proj.weight, L.self_attn.out_proj.bias)
+    out = None
+    if packed_out:   # the cross-attention block lives on the next stage: ship [x1 ; x0]
+        T = x0.shape[0]
+        packed = torch.empty((2 * T, d), dtype=x0.dtype, device=x0.device)
+        out = (torch.empty_like(x0), packed[:T], torch.empty(T, dtype=torch.float32, device=x0.device),
+               torch.empty(T, dtype=torch.float32, device=x0.device))
     z1, x1, mean1, rstd1 = F.add_dropout_norm_fwd(x0, a1, L.norm1.weight, L.norm1.bias, eps, p,
-                                                  ctx.seed(layer_id, SITE_RES1), rms)
+                                                  ctx.seed(layer_id, SITE_RES1), rms, out=out)
     st.update(qkv=qkv, o1=o1, lse1=lse1, z1=z1, x1=x1, mean1=mean1, rstd1=rstd1)
-    x2 = x1
-    # ---- cross-attention over the layer input (memory = x0) ----
-    if a.cross_attn:
-        W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
-        q2 = F.linear_fwd(x1, W[:d], bvec[:d])
-        kv2 = F.linear_fwd(x0, W[d:], bvec[d:])
-        o2, lse2 = F.attention_fwd(q2, kv2[:, :d], kv2[:, d:], ctx.B, H, False, None, p, ctx.seed(layer_id, SITE_ATTN2))
-        a2 = F.linear_fwd(o2, L.multihead_attn.out_proj.weight, L.multihead_attn.out_proj.bias)
-        z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p,
-                                                      ctx.seed(layer_id, SITE_RES2), rms)
-        st.update(q2=q2, kv2=kv2, o2=o2, lse2=lse2, z2=z2, x2=x2, mean2=mean2, rstd2=rstd2)
+    if packed_out:
+        F.add_n([x0], out=packed[x0.shape[0]:])
+        return packed
+    return x1
+
+
+def _postln_cross_forward(L: DecoderLayer, layer_id: int, x1: torch.Tensor, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+    """Cross-attention over the layer input (memory = x0)."""
+    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
+    rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
+    W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
+    q2 = F.linear_fwd(x1, W[:d], bvec[:d])
+    kv2 = F.linear_fwd(x0, W[d:], bvec[d:])
+    o2, lse2 = F.attention_fwd(q2, kv2[:, :d], kv2[:, d:], ctx.B, H, False, None, p, ctx.seed(layer_id, SITE_ATTN2))
+    a2 = F.linear_fwd(o2, L.multihead_attn.out_proj.weight, L.multihead_attn.out_proj.bias)
+    z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p,
+                                                  ctx.seed(layer_id, SITE_RES2), rms)
+    st.update(x0=x0, x1=x1, q2=q2, kv2=kv2, o2=o2, lse2=lse2, z2=z2, x2=x2, mean2=mean2, rstd2=rstd2)
     return x2
 
 
-def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
+def layer_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
     """Decoder layer forward on [T, d] tokens (post-LN reference block, or the pre-LN GPT block when
-    ``args.norm_first``).  Fills the stash ``st`` and returns the layer output."""
+    ``args.norm_first``).  Fills the stash ``st`` and returns the layer output.  A layer may hold only some of its
+    units (``L.part``, partition rule 'fine'); see ``_PARTS`` for the boundary tensors."""
     if ctx.tp is not None:
         from .tp import tp_postln_forward, tp_prenorm_forward
-        return (tp_prenorm_forward if ctx.args.norm_first else tp_postln_forward)(L, layer_id, x0, ctx, st)
+        return (tp_prenorm_forward if ctx.args.norm_first else tp_postln_forward)(L, layer_id, x_in, ctx, st)
     if ctx.args.norm_first:
-        return _prenorm_forward(L, layer_id, x0, ctx, st)
+        return _prenorm_forward(L, layer_id, x_in, ctx, st)
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
-    # a stage boundary may fall INSIDE a layer (partition rule 'fine'): part 'attn' = the attention sub-blocks (ends at
-    # x2, the input of the feed-forward block), part 'ffn' = the feed-forward block; 'full' = both
     part = getattr(L, "part", "full")
-    if part == "ffn":
-        x2 = x0
-        st["x2" if a.cross_attn else "x1"] = x2
-    else:
-        x2 = _postln_attention_forward(L, layer_id, x0, ctx, st)
-        if part == "attn":
-            return x2
+    units = _PARTS[part] if a.cross_attn else tuple(u for u in _PARTS[part] if u != "cross")
+    T = ctx.B * ctx.S if ctx.tp is None else x_in.shape[0]
+    h = x_in
+    if "self" in units:
+        h = _postln_self_forward(L, layer_id, x_in, ctx, st, packed_out=(a.cross_attn and units[-1] == "self"))
+        if units[-1] == "self":
+            return h
+    if "cross" in units:
+        if units[0] == "cross":     # boundary tensor [x1 ; x0] from the stage that owns the self-attention block
+            if x_in.shape[0] != 2 * T:
+                raise ValueError(f"layer {layer_id} part {part!r} expects the packed [x1 ; x0] input of {2 * T} rows, got {x_in.shape[0]}")
+            h = _postln_cross_forward(L, layer_id, x_in[:T], x_in[T:], ctx, st)
+        else:
+            h = _postln_cross_forward(L, layer_id, h, x_in, ctx, st)
+        if units[-1] == "cross":
+            return h
     # ---- feed-forward ----
+    x2 = h
+    st["x2" if a.cross_attn else "x1"] = x2
     if a.activation == "relu":
-        h = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
-        st["h"] = h
+        hid = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias, "relu", p, ctx.seed(layer_id, SITE_FFN))
+        st["h"] = hid
     else:  # gelu: keep the pre-activation for backward (dropout on the hidden is not applied in this variant)
         hpre = F.linear_fwd(x2, L.linear1.weight, L.linear1.bias)
-        h = F.gelu_fwd(hpre)
-        st.update(hpre=hpre, h=h)
-    a3 = F.linear_fwd(h, L.linear2.weight, L.linear2.bias)
+        hid = F.gelu_fwd(hpre)
+        st.update(hpre=hpre, h=hid)
+    a3 = F.linear_fwd(hid, L.linear2.weight, L.linear2.bias)
     z3, x3, mean3, rstd3 = F.add_dropout_norm_fwd(x2, a3, L.norm3.weight, L.norm3.bias, eps, p,
                                                   ctx.seed(layer_id, SITE_RES3), rms)
     st.update(z3=z3, mean3=mean3, rstd3=rstd3)
@@ -315,8 +353,9 @@ def layer_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: Ctx, st
 
 def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], ctx: Ctx, st: dict,
                    G: GradSink) -> List[torch.Tensor]:
-    """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. x3 (summed on load by the norm
-    kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. x0."""
+    """Backward of ``layer_forward``.  ``dys`` = up to three gradients w.r.t. the layer output (summed on load by the
+    norm kernel).  Accumulates parameter gradients into ``G`` and returns the (up to three) gradients w.r.t. the
+    layer input (one packed [2T, d] tensor when the input was the packed [x1 ; x0] boundary tensor)."""
     if ctx.tp is not None:
         from .tp import tp_postln_backward, tp_prenorm_backward
         return (tp_prenorm_backward if ctx.args.norm_first else tp_postln_backward)(L, layer_id, dys, ctx, st, G)
@@ -325,36 +364,28 @@ def layer_backward(L: DecoderLayer, layer_id: int, dys: Sequence[torch.Tensor], 
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms = a.norm == "rmsnorm"
     part = getattr(L, "part", "full")
-    if part == "attn":   # the feed-forward block of this layer lives on the next stage: dys are gradients w.r.t. x2
-        return _postln_attention_backward(L, layer_id, list(dys), ctx, st, G)
-    # ---- FFN ----
-    dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
-                          ctx.seed(layer_id, SITE_RES3), rms)
-    x2 = st["x2"] if a.cross_attn else st["x1"]
-    G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
-    if a.activation == "relu":
-        dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
-    else:
-        dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
-    G.wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias))
-    dx2 = F.linear_dgrad(dh, L.linear1.weight)
-    if part == "ffn":
-        return [dz3, dx2]
-    return _postln_attention_backward(L, layer_id, [dz3, dx2], ctx, st, G)
-
-
-def _postln_attention_backward(L: DecoderLayer, layer_id: int, dys1: List[torch.Tensor], ctx: Ctx, st: dict,
-                               G: GradSink) -> List[torch.Tensor]:
-    """Backward of ``_postln_attention_forward``: gradients w.r.t. x2 -> gradients w.r.t. the layer input x0."""
-    a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
-    rms = a.norm == "rmsnorm"
-    x0 = st["x0"]
-    dx0_extra = None
-    # ---- cross-attention ----
-    if a.cross_attn:
+    units = _PARTS[part] if a.cross_attn else tuple(u for u in _PARTS[part] if u != "cross")
+    dys = list(dys)
+    dx0_extras: List[torch.Tensor] = []
+    if "ffn" in units:
+        dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
+                              ctx.seed(layer_id, SITE_RES3), rms)
+        x2 = st["x2"] if a.cross_attn else st["x1"]
+        G.wgrad(da3, st["h"], G(L.linear2.weight), G(L.linear2.bias))
+        if a.activation == "relu":
+            dh = F.linear_dgrad(da3, L.linear2.weight, mask_pos_aux=st["h"], alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
+        else:
+            dh = F.linear_dgrad(da3, L.linear2.weight, gelu_aux=st["hpre"])
+        G.wgrad(dh, x2, G(L.linear1.weight), G(L.linear1.bias))
+        dx2 = F.linear_dgrad(dh, L.linear1.weight)
+        dys = [dz3, dx2]
+        if units[0] == "ffn":
+            return dys
+    if "cross" in units:
+        x0, T = st["x0"], st["x0"].shape[0]
         W = L.multihead_attn.in_proj_weight
         gW, gb = G(W), G(L.multihead_attn.in_proj_bias)
-        dz2, da2 = F.norm_bwd(dys1, st["z2"], st["mean2"], st["rstd2"], L.norm2.weight, G(L.norm2.weight),
+        dz2, da2 = F.norm_bwd(dys, st["z2"], st["mean2"], st["rstd2"], L.norm2.weight, G(L.norm2.weight),
                               G(L.norm2.bias), p, ctx.seed(layer_id, SITE_RES2), rms)
         G.wgrad(da2, st["o2"], G(L.multihead_attn.out_proj.weight), G(L.multihead_attn.out_proj.bias))
         do2 = F.linear_dgrad(da2, L.multihead_attn.out_proj.weight)
@@ -366,10 +397,20 @@ def _postln_attention_backward(L: DecoderLayer, layer_id: int, dys1: List[torch.
         G.wgrad(dq2, st["x1"], gW[:d], gb[:d])
         G.wgrad(dkv2, x0, gW[d:], gb[d:])
         dx1 = F.linear_dgrad(dq2, W[:d])
-        dx0_extra = F.linear_dgrad(dkv2, W[d:])
-        dys1 = [dz2, dx1]
+        if units[0] == "cross":     # the self-attention block lives on the previous stage: ship [d x1 ; d x0]
+            packed = torch.empty((2 * T, d), dtype=x0.dtype, device=x0.device)
+            F.add_n([dz2, dx1], out=packed[:T])
+            F.linear_dgrad(dkv2, W[d:], out=packed[T:])
+            return [packed]
+        dx0_extras = [F.linear_dgrad(dkv2, W[d:])]
+        dys = [dz2, dx1]
     # ---- self-attention ----
-    dz1, da1 = F.norm_bwd(dys1, st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias), p,
+    x0 = st["x0"]
+    if a.cross_attn and units[-1] == "self":   # gradients of the packed [x1 ; x0] boundary tensor
+        T = x0.shape[0]
+        dx0_extras = [g[T:] for g in dys]
+        dys = [g[:T] for g in dys]
+    dz1, da1 = F.norm_bwd(dys, st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias), p,
                           ctx.seed(layer_id, SITE_RES1), rms)
     G.wgrad(da1, st["o1"], G(L.self_attn.out_proj.weight), G(L.self_attn.out_proj.bias))
     do1 = F.linear_dgrad(da1, L.self_attn.out_proj.weight)
@@ -379,9 +420,9 @@ def _postln_attention_backward(L: DecoderLayer, layer_id: int, dys1: List[torch.
                     ctx.seed(layer_id, SITE_ATTN1), out=(dqkv[:, :d], dqkv[:, d:2 * d], dqkv[:, 2 * d:]))
     G.wgrad(dqkv, x0, G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
     dx0 = F.linear_dgrad(dqkv, L.self_attn.in_proj_weight)
-    out = [dz1, dx0]
-    if dx0_extra is not None:
-        out.append(dx0_extra)
+    out = [dz1, dx0] + dx0_extras
+    if len(out) > 3:    # the fan-in kernels sum at most three gradients
+        out = [dz1, dx0, F.add_n(dx0_extras)]
     return out
 
 

@@ -30,52 +30,86 @@ def reference_ranges(n_layers: int, num_stages: int) -> List[Tuple[int, int]]:
     return out
 
 
-def balanced_ranges(n_layers: int, num_stages: int, args: Optional[ModelArgs] = None, seq_len: int = 1024) -> List[Tuple[int, int]]:
-    """Contiguous split minimising the most expensive stage, with the LM head (and loss) charged to the last one."""
+# ----------------------------------------------------------------------------------------------------------------
+# cost model: measured per-unit times when available, an analytic estimate otherwise
+# ----------------------------------------------------------------------------------------------------------------
+# Units of a layer (the places a stage boundary may fall, rule 'fine'):
+#   post-LN reference block with cross-attention: 'self' | 'cross' | 'ffn'   (a cut behind 'self' ships TWO tensors:
+#       x1 and the layer input x0, which is the cross-attention memory -- packed as [2T, d] rows)
+#   every other block (pre-LN GPT / Llama, post-LN without cross-attention): 'attn' | 'ffn'
+_MEASURED: dict = {}
+
+
+def layer_units(args: ModelArgs) -> Tuple[str, ...]:
+    if not args.norm_first and args.cross_attn:
+        return ("self", "cross", "ffn")
+    return ("attn", "ffn")
+
+
+def _cost_key(args: ModelArgs, seq_len: int, tokens: int):
+    return (args.dim, args.n_heads, args.ffn_dim, args.vocab_size, args.cross_attn, args.norm_first, args.activation,
+            args.causal, round(args.dropout, 4), str(args.dtype), seq_len, tokens)
+
+
+def set_measured_costs(args: ModelArgs, seq_len: int, costs: dict, tokens: int = 0) -> None:
+    """Register measured forward+backward times (any unit, e.g. ms) of one micro-batch for the units of ``args``:
+    keys = the names in ``layer_units(args)`` plus 'head' (final norm + LM head + loss) and 'embed'.  From then on every
+    partition rule balances these numbers instead of the analytic estimate (``measure_unit_costs`` produces them)."""
+    need = set(layer_units(args)) | {"head", "embed"}
+    if not need <= set(costs):
+        raise ValueError(f"measured costs need the keys {sorted(need)}, got {sorted(costs)}")
+    _MEASURED[_cost_key(args, seq_len, 0)] = dict(costs)
+    if tokens:
+        _MEASURED[_cost_key(args, seq_len, tokens)] = dict(costs)
+
+
+def clear_measured_costs() -> None:
+    _MEASURED.clear()
+
+
+def unit_costs(args: Optional[ModelArgs], seq_len: int = 1024) -> dict:
+    """{'<unit>': cost, ..., 'head': cost, 'embed': cost, 'source': 'measured' | 'model'} per micro-batch."""
     if args is None:
-        layer_cost, head_cost = 1.0, 1.0
+        return {"attn": 0.5, "ffn": 0.5, "self": 0.4, "cross": 0.4, "head": 1.0, "embed": 0.0, "source": "uniform"}
+    m = _MEASURED.get(_cost_key(args, seq_len, 0))
+    if m is not None:
+        return {**m, "source": "measured"}
+    # Analytic fallback (no GPU measurement available, e.g. planning on a CPU box): FLOPs per token weighted by the
+    # efficiency each part reached on B200 in round 1 (layer GEMMs ~0.40 of the tensor-core peak, attention ~0.20, the
+    # vocabulary-sized head GEMMs ~0.9, the loss pass HBM-bound).  Only RATIOS matter.
+    d, f, V = args.dim, args.ffn_dim, args.vocab_size
+    attn_core = 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
+    proj = 8 * d * d / 0.40
+    ffn = (6 if args.activation == "swiglu" else 4) * d * f / 0.40
+    out = {"ffn": ffn, "head": 2 * d * V / 0.9 + 650.0 * V, "embed": 0.0, "source": "model"}
+    if "self" in layer_units(args):
+        out.update(self=proj + attn_core, cross=proj + attn_core)
     else:
-        # FLOPs per token weighted by the efficiency each part reaches on B200, calibrated on measured per-action
-        # times (profiles/bench_r1_n4_1f1b_v2.json: forward+backward of a decoder layer 1.00 ms, of embedding + final
-        # norm + head + loss 1.46 ms per 4096-token micro-batch): the vocabulary-sized head GEMMs run near the
-        # tensor-core roofline (~0.9), the d x d / d x f GEMMs of a layer at ~0.40, attention (exp-bound softmax) at
-        # ~0.20; the cross-entropy pass is HBM-bound (reads and rewrites the [tokens, V] logits).
-        d, f, V = args.dim, args.ffn_dim, args.vocab_size
-        blocks = 2 if args.cross_attn else 1
-        layer_cost = (blocks * 8 * d * d + (6 if args.activation == 'swiglu' else 4) * d * f) / 0.40 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
-        head_cost = 2 * d * V / 0.9 + 650.0 * V
-    # DP over (stage, first layer of the stage): minimise (most expensive stage, then sum of squared costs);
-    # every stage gets at least one layer when there are enough layers.
-    INF = (float("inf"), float("inf"))
-    S, L = num_stages, n_layers
-    min_layers = 1 if L >= S else 0
-    best = [[INF] * (L + 1) for _ in range(S + 1)]   # best[s][i]: stages s.. cover layers i..L-1
-    cut = [[L] * (L + 1) for _ in range(S + 1)]
-    for i in range(L + 1):
-        if L - i >= min_layers:
-            c = (L - i) * layer_cost + head_cost
-            best[S - 1][i] = (c, c * c)
-    for s in range(S - 2, -1, -1):
-        for i in range(L + 1):
-            for j in range(i + min_layers, L + 1):
-                nxt = best[s + 1][j]
-                if nxt[0] == float("inf"):
-                    continue
-                c = (j - i) * layer_cost
-                w = (max(c, nxt[0]), c * c + nxt[1])
-                if w < best[s][i]:
-                    best[s][i], cut[s][i] = w, j
-    out, i = [], 0
-    for s in range(S):
-        j = cut[s][i] if s < S - 1 else L
-        out.append((i, j))
-        i = j
+        out.update(attn=proj + attn_core)
     return out
 
 
-def _min_max_partition(costs: List[float], num_stages: int, tail_cost: float) -> List[Tuple[int, int]]:
+def _layer_cost(args: Optional[ModelArgs], seq_len: int) -> Tuple[float, float, float]:
+    c = unit_costs(args, seq_len)
+    units = layer_units(args) if args is not None else ("attn", "ffn")
+    return sum(c[u] for u in units), c["head"], c["embed"]
+
+
+def balanced_ranges(n_layers: int, num_stages: int, args: Optional[ModelArgs] = None, seq_len: int = 1024) -> List[Tuple[int, int]]:
+    """Contiguous split at WHOLE-layer granularity minimising the most expensive stage, with the LM head (and loss)
+    charged to the last stage and the embedding to the first."""
+    layer_cost, head_cost, embed_cost = _layer_cost(args, seq_len)
+    if args is None:
+        layer_cost, head_cost, embed_cost = 1.0, 1.0, 0.0
+    if n_layers < num_stages:   # more stages than layers: every stage gets at most one layer (reference quirk 8)
+        return [(min(s, n_layers), min(s + 1, n_layers)) for s in range(num_stages)]
+    units = _min_max_partition([layer_cost] * n_layers, num_stages, head_cost, embed_cost)
+    return units
+
+
+def _min_max_partition(costs: List[float], num_stages: int, tail_cost: float, head_cost: float = 0.0) -> List[Tuple[int, int]]:
     """Contiguous split of ``costs`` into ``num_stages`` non-empty groups minimising (largest group, sum of squares);
-    ``tail_cost`` is added to the last group."""
+    ``tail_cost`` is added to the last group, ``head_cost`` to the first."""
     n, S = len(costs), num_stages
     pre = [0.0]
     for c in costs:
@@ -84,15 +118,17 @@ def _min_max_partition(costs: List[float], num_stages: int, tail_cost: float) ->
     best = [[INF] * (n + 1) for _ in range(S + 1)]
     cut = [[n] * (n + 1) for _ in range(S + 1)]
     for i in range(n):
-        c = pre[n] - pre[i] + tail_cost
+        c = pre[n] - pre[i] + tail_cost + (head_cost if S == 1 else 0.0)
         best[S - 1][i] = (c, c * c)
     for s in range(S - 2, -1, -1):
         for i in range(n):
+            if s > 0 and i == 0:
+                continue
             for j in range(i + 1, n):
                 nxt = best[s + 1][j]
                 if nxt[0] == float("inf"):
                     continue
-                c = pre[j] - pre[i]
+                c = pre[j] - pre[i] + (head_cost if s == 0 else 0.0)
                 w = (max(c, nxt[0]), c * c + nxt[1])
                 if w < best[s][i]:
                     best[s][i], cut[s][i] = w, j
@@ -105,33 +141,56 @@ def _min_max_partition(costs: List[float], num_stages: int, tail_cost: float) ->
 
 
 def fine_unit_ranges(n_layers: int, num_stages: int, args: ModelArgs, seq_len: int = 1024) -> List[Tuple[int, int]]:
-    """Stage boundaries at HALF-layer granularity: unit 2i = the attention sub-blocks of layer i (post-LN reference block:
-    self + cross attention, ends at the input of the feed-forward block; pre-LN block: attention + its residual add),
-    unit 2i+1 = its feed-forward block.
-    Returns [u0, u1) unit ranges.  Only one [tokens, d] tensor crosses such a cut (the cross-attention memory is the
-    layer input, so a cut between the two attention blocks would have to ship two).  At 8 stages the flagship model
-    goes from a most expensive stage of 4.0 layer-equivalents (whole layers) to 3.7."""
-    d, f, V = args.dim, args.ffn_dim, args.vocab_size
-    blocks = 2 if args.cross_attn else 1
-    attn_cost = blocks * 8 * d * d / 0.40 + blocks * 4 * seq_len * d * (0.5 if args.causal else 1.0) / 0.20
-    ffn_cost = (6 if args.activation == "swiglu" else 4) * d * f / 0.40
-    head_cost = 2 * d * V / 0.9 + 650.0 * V
-    costs = [attn_cost if u % 2 == 0 else ffn_cost for u in range(2 * n_layers)]
-    if 2 * n_layers < num_stages:
-        raise ValueError(f"{n_layers} layers cannot be cut into {num_stages} stages")
-    return _min_max_partition(costs, num_stages, head_cost)
+    """Stage boundaries at SUB-layer granularity.  With U = len(layer_units(args)) units per layer, unit U*i + k is
+    block k of layer i; returns [u0, u1) unit ranges.  The reference block has three units (self-attention |
+    cross-attention | feed-forward, roughly 0.4 / 0.4 / 0.2 of a layer at the flagship shape), so the most expensive
+    of 8 stages of the 24-layer flagship drops from 4.0 layer-equivalents (whole layers) to about 3.4."""
+    units = layer_units(args)
+    c = unit_costs(args, seq_len)
+    costs = [c[units[u % len(units)]] for u in range(len(units) * n_layers)]
+    if len(costs) < num_stages:
+        raise ValueError(f"{n_layers} layers ({len(costs)} units) cannot be cut into {num_stages} stages")
+    return _min_max_partition(costs, num_stages, c["head"], c["embed"])
+
+
+def _stage_costs(n_layers: int, num_stages: int, rule: str, args: ModelArgs, seq_len: int) -> List[float]:
+    c = unit_costs(args, seq_len)
+    units = layer_units(args)
+    out = []
+    for s in range(num_stages):
+        w = sum(sum(c[u] for u in part_units(part, units)) for _, part in stage_layer_parts(n_layers, num_stages, s, rule, args, seq_len))
+        out.append(w + (c["head"] if s == num_stages - 1 else 0.0) + (c["embed"] if s == 0 else 0.0))
+    return out
+
+
+def resolve_rule(rule: str, n_layers: int, num_stages: int, args: Optional[ModelArgs], seq_len: int = 1024,
+                 tp: int = 1) -> str:
+    """'auto' -> 'fine' when sub-layer cuts lower the most expensive stage by more than 2 % (and the configuration
+    supports them), else 'balanced'.  Other rule names pass through."""
+    if rule != "auto":
+        return rule
+    if args is None or num_stages == 1 or tp > 1 or len(layer_units(args)) * n_layers < num_stages:
+        return "balanced"
+    try:
+        fine = max(_stage_costs(n_layers, num_stages, "fine", args, seq_len))
+        bal = max(_stage_costs(n_layers, num_stages, "balanced", args, seq_len))
+    except ValueError:
+        return "balanced"
+    return "fine" if fine < 0.98 * bal else "balanced"
 
 
 def stage_ranges(n_layers: int, num_stages: int, rule: str = "reference", args: Optional[ModelArgs] = None,
                  seq_len: int = 1024) -> List[Tuple[int, int]]:
     """[start, end) LAYER ranges per stage.  For rule 'fine' a boundary layer appears in both neighbouring stages
-    (see ``stage_layer_parts`` for which half each of them owns)."""
+    (see ``stage_layer_parts`` for which units each of them owns)."""
+    rule = resolve_rule(rule, n_layers, num_stages, args, seq_len)
     if rule == "reference":
         return reference_ranges(n_layers, num_stages)
     if rule == "balanced":
         return balanced_ranges(n_layers, num_stages, args, seq_len)
     if rule == "fine":
-        return [(u0 // 2, (u1 + 1) // 2) for u0, u1 in _fine_units(n_layers, num_stages, args, seq_len)]
+        U = len(layer_units(args)) if args is not None else 2
+        return [(u0 // U, (u1 + U - 1) // U) for u0, u1 in _fine_units(n_layers, num_stages, args, seq_len)]
     raise ValueError(f"unknown partition rule {rule!r}")
 
 
@@ -141,29 +200,57 @@ def _fine_units(n_layers: int, num_stages: int, args: Optional[ModelArgs], seq_l
     return fine_unit_ranges(n_layers, num_stages, args, seq_len)
 
 
+def part_name(k0: int, k1: int, units: Tuple[str, ...]) -> str:
+    """Name of the contiguous unit range [k0, k1) of one layer: 'full', or the owned unit names joined by '+'
+    ('self+cross' is spelled 'attn', as it was before the three-way split existed)."""
+    if k0 == 0 and k1 == len(units):
+        return "full"
+    name = "+".join(units[k0:k1])
+    return "attn" if name == "self+cross" else name
+
+
+def part_units(part: str, units: Tuple[str, ...]) -> Tuple[str, ...]:
+    if part == "full":
+        return tuple(units)
+    if part == "attn" and "attn" not in units:
+        return ("self", "cross")
+    return tuple(part.split("+"))
+
+
 def stage_layer_parts(n_layers: int, num_stages: int, stage_index: int, rule: str, args: Optional[ModelArgs] = None,
                       seq_len: int = 1024) -> List[Tuple[int, str]]:
-    """[(layer index, 'full' | 'attn' | 'ffn'), ...] owned by ``stage_index``."""
+    """[(layer index, part), ...] owned by ``stage_index``; part = 'full' or the owned units ('attn', 'ffn', and for
+    the reference block also 'self', 'cross', 'cross+ffn')."""
+    rule = resolve_rule(rule, n_layers, num_stages, args, seq_len)
     if rule != "fine":
         start, end = stage_ranges(n_layers, num_stages, rule, args, seq_len)[stage_index]
         return [(i, "full") for i in range(start, end)]
+    units = layer_units(args) if args is not None else ("attn", "ffn")
+    U = len(units)
     u0, u1 = _fine_units(n_layers, num_stages, args, seq_len)[stage_index]
     out = []
-    for i in range(u0 // 2, (u1 + 1) // 2):
-        has_attn, has_ffn = u0 <= 2 * i < u1, u0 <= 2 * i + 1 < u1
-        out.append((i, "full" if (has_attn and has_ffn) else ("attn" if has_attn else "ffn")))
+    for i in range(u0 // U, (u1 + U - 1) // U):
+        k0, k1 = max(u0, U * i) - U * i, min(u1, U * (i + 1)) - U * i
+        out.append((i, part_name(k0, k1, units)))
     return out
 
 
-_ATTN_MODULES = ("self_attn", "multihead_attn", "norm1", "norm2")
-_FFN_MODULES = ("linear1", "linear2", "norm3")
+_UNIT_MODULES = {"self": ("self_attn", "norm1"), "cross": ("multihead_attn", "norm2"),
+                 "attn": ("self_attn", "norm1"), "ffn": ("linear1", "linear2", "norm3")}
 
 
 def _apply_part(layer: DecoderLayer, part: str) -> DecoderLayer:
+    """Keep only the parameters of the units in ``part`` (checkpoint keys of what remains are unchanged)."""
     layer.part = part
-    for name in (_FFN_MODULES if part == "attn" else _ATTN_MODULES if part == "ffn" else ()):
-        if hasattr(layer, name):
-            delattr(layer, name)
+    if part == "full":
+        return layer
+    has_cross = hasattr(layer, "multihead_attn") or hasattr(layer, "norm2")
+    units = ("self", "cross", "ffn") if has_cross else ("attn", "ffn")
+    keep = {m for u in part_units(part, units) for m in _UNIT_MODULES[u]}
+    for u in units:
+        for name in _UNIT_MODULES[u]:
+            if name not in keep and hasattr(layer, name):
+                delattr(layer, name)
     return layer
 
 
@@ -203,3 +290,88 @@ def build_stage_model(args: ModelArgs, stage_index: int, num_stages: int, rule: 
     model.norm = full_tail.norm if stage_index == num_stages - 1 else None
     model.output = full_tail.output if stage_index == num_stages - 1 else None
     return model
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# measured unit costs (what 'balanced' / 'fine' / 'auto' balance on a GPU)
+# ----------------------------------------------------------------------------------------------------------------
+def measure_unit_costs(args: ModelArgs, micro_batch: int, seq_len: int, device: torch.device, iters: int = 4) -> dict:
+    """Forward+backward time (ms, CUDA events) of ONE micro-batch for every unit a stage boundary can separate, for the
+    final norm + LM head + loss ('head') and for the embedding ('embed'): each is built as a one-unit stage and timed
+    as the runner executes it (CUDA-graph replays of the stage program), so the numbers track the kernels as they
+    are today instead of constants calibrated once.  Takes about a second."""
+    from .stage import PipelineStage
+    dev = torch.device(device)
+    d, T = args.dim, micro_batch * seq_len
+    dt = args.dtype if args.dtype != torch.float32 or dev.type != "cuda" else torch.bfloat16
+    margs = ModelArgs(**{**args.__dict__, "n_layers": 1, "dtype": dt})
+    units = layer_units(margs)
+    out: dict = {}
+
+    def run(stage: "PipelineStage", inp, tgt, dout) -> float:
+        stage.materialize()
+        stage.training = True
+        stage.base_seed = 1
+        stage.begin_step()
+        stage.forward_one_chunk(0, inp, tgt)        # eager once: module loading / attribute setting outside any capture
+        stage.backward_one_chunk(0, dout)
+        stage.enable_graphs(1)
+        best = float("inf")
+        for it in range(iters + 2):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            stage.forward_graphed(0, inp, tgt)
+            stage.backward_graphed(0, dout)
+            e1.record()
+            e1.synchronize()
+            if it >= 2:
+                best = min(best, e0.elapsed_time(e1))
+        return best
+
+    def one_unit_model(part: Optional[str], embed: bool, head: bool) -> Transformer:
+        with torch.device(dev):
+            m = Transformer(margs)
+        if part is None:
+            del m.layers["0"]
+        else:
+            _apply_part(m.layers["0"], part)
+        if not embed:
+            m.tok_embeddings = None
+        if not head:
+            m.norm = None
+            m.output = None
+        return m
+
+    gen = torch.Generator(device="cpu").manual_seed(7)
+    tokens = torch.randint(0, args.vocab_size, (micro_batch, seq_len), generator=gen).to(dev)
+    for u in units:
+        st = PipelineStage(one_unit_model(u, False, False), 1, 3, dev)
+        inp = torch.randn(st.in_rows * micro_batch, seq_len, d, device=dev).to(dt) * 0.5
+        dout = torch.randn(st.out_rows * T, d, device=dev).to(dt) * 0.01
+        out[u] = run(st, inp, None, dout)
+        del st
+    st = PipelineStage(one_unit_model(None, False, True), 2, 3, dev)
+    out["head"] = run(st, torch.randn(micro_batch, seq_len, d, device=dev).to(dt) * 0.5, tokens, None)
+    del st
+    st = PipelineStage(one_unit_model(None, True, False), 0, 3, dev)
+    out["embed"] = run(st, tokens, None, torch.randn(T, d, device=dev).to(dt) * 0.01)
+    del st
+    torch.cuda.synchronize(dev)
+    torch.cuda.empty_cache()
+    return out
+
+
+def calibrate(args: ModelArgs, micro_batch: int, seq_len: int, device: torch.device, group=None, src: int = 0) -> dict:
+    """Measure the unit costs on this GPU and make every rank of ``group`` use rank ``src``'s numbers (the partition
+    must be identical on all ranks).  No-op on CPU devices (the analytic model stays in charge)."""
+    import torch.distributed as dist
+    dev = torch.device(device)
+    if dev.type != "cuda":
+        return unit_costs(args, seq_len)
+    costs = measure_unit_costs(args, micro_batch, seq_len, dev)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        box = [costs]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, src) if group is not None else src, group=group)
+        costs = box[0]
+    set_measured_costs(args, seq_len, costs)
+    return {**costs, "source": "measured"}

@@ -80,6 +80,7 @@ class PipelineSchedule:
                                    dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None)
         self.full_order = order
         self.order: List[Action] = order[self.pp_rank]
+        self._retire_in_order = self._retires_in_forward_order(self.order)
         self.theory_bubble = theoretical_bubble(self.pp_size, self.m, self.n_virtual)
         self._shape: Optional[Tuple[int, int]] = None
         self._ring: Dict[Tuple[int, str, int], torch.Tensor] = {}
@@ -101,8 +102,10 @@ class PipelineSchedule:
         self.recompute = bool(recompute)    # trade one extra forward per micro-batch for O(1) stashed activations per slot
         for st in self.stages:
             st.recompute = self.recompute
+        # slot = mb % nslots is only safe when every stage retires micro-batches in the order it forwarded them
+        # (true for all built-in schedules; a user-supplied action list that does not is run without graphs)
         self.use_graphs = bool(want and self.cuda and self.fused_loss and optimizer is not None and self.tp_size == 1
-                               and not self.recompute)
+                               and not self.recompute and self._retire_in_order)
         self.graph_warmup_steps = graph_warmup_steps
         self.nvtx = os.environ.get("PPB_NVTX", "0") == "1"   # NVTX range per action, named with its IR string
         if self.use_graphs:
@@ -138,6 +141,19 @@ class PipelineSchedule:
         from .schedule import simulate
         simulate(order, self.num_stages)     # raises DeadlockError on an order that cannot complete
         return order
+
+    @staticmethod
+    def _retires_in_forward_order(order: List[Action]) -> bool:
+        """True when, per stage, backwards (B or I, and W) come in the same micro-batch order as the forwards."""
+        seq: Dict[Tuple[int, str], List[int]] = {}
+        for a in order:
+            if a.type in (T.F, T.B, T.I, T.W):
+                kind = "F" if a.type == T.F else ("W" if a.type == T.W else "B")
+                seq.setdefault((a.stage, kind), []).append(a.mb)
+        for (stage, kind), mbs in seq.items():
+            if kind != "F" and mbs != [m for m in seq.get((stage, "F"), []) if m in set(mbs)]:
+                return False
+        return True
 
     def _global_rank(self, pp_rank: int) -> int:
         if self.pp_group is None:
@@ -187,8 +203,10 @@ class PipelineSchedule:
     def _ring_buf(self, stage: int, kind: str, mb: int, b: int, S: int) -> torch.Tensor:
         key = (stage, kind, mb)
         buf = self._ring.get(key)
+        st = self.local[stage]
+        # a boundary behind a self-attention block carries the packed [x1 ; x0] tensor (and its gradient): 2x the rows
+        b = b * (st.in_rows if kind == "F" else st.out_rows)
         if buf is None or buf.shape[0] != (b if self.tp_size == 1 else b * S // self.tp_size):
-            st = self.local[stage]
             shape = (b, S, st.args.dim) if self.tp_size == 1 else (b * S // self.tp_size, st.args.dim)
             buf = torch.empty(shape, dtype=st.dtype, device=self.device)
             self._ring[key] = buf
@@ -209,8 +227,8 @@ class PipelineSchedule:
             st.seq_len = S
         tp = self.tp_size
 
-        def act_view(t, b):   # stage boundary tensors: [b, S, d], or this tp rank's [b*S/tp, d] rows
-            return t.view(b, S, -1) if tp == 1 else t.view(b * S // tp, -1)
+        def act_view(t, b):   # stage boundary tensors: [b, S, d] ([2b, S, d] when packed), or this tp rank's [b*S/tp, d] rows
+            return t.view(-1, S, t.shape[-1]) if tp == 1 else t.view(b * S // tp, -1)
 
         cuda = self.cuda
         compute = torch.cuda.current_stream(self.device) if cuda else None
@@ -229,7 +247,9 @@ class PipelineSchedule:
         keep_alive: List[torch.Tensor] = []
         allreduce_works: Dict[int, Any] = {}
         slot_sends: Dict[Tuple[int, str, int], Any] = {}
-        graphs_on = self.use_graphs and self.steps_done >= self.graph_warmup_steps and all(st.training for st in self.stages)
+        # graph slots are captured for ONE micro-batch shape: uneven batches (tensor_split semantics) run eagerly
+        graphs_on = (self.use_graphs and self.steps_done >= self.graph_warmup_steps and B % self.m == 0
+                     and all(st.training for st in self.stages))
         b_count: Dict[int, int] = {}
         timeline: List[Tuple[Action, Any, Any]] = []
         rec = self.record_timeline
@@ -245,12 +265,19 @@ class PipelineSchedule:
 
         t_begin = tick()
         host_t0 = time.perf_counter()
+        host_by: Dict[str, float] = {}
+        _h0, _ht = host_t0, "begin"
         idx = -1
         clip = None
         nvtx = cuda and self.nvtx
         try:
             for idx, a in enumerate(self.order):
                 typ = a.type
+                if idx:     # host time spent issuing the previous action, by action type (where does the host block?)
+                    _hn = time.perf_counter()
+                    host_by[_ht] = host_by.get(_ht, 0.0) + (_hn - _h0)
+                    _h0 = _hn
+                _ht = typ.value
                 if nvtx:   # ranges carry the IR string (2F0, 3SEND_B1, ...) so ncu / nsys timelines line up with the schedule
                     if idx:
                         torch.cuda.nvtx.range_pop()
@@ -401,6 +428,7 @@ class PipelineSchedule:
                 w.wait()
         t_end = tick()
         self._host_ms = (time.perf_counter() - host_t0) * 1e3
+        self._host_by_type = {k: v * 1e3 for k, v in host_by.items()}
         self.timeline = timeline
         self._step_span = (t_begin, t_end)
         self._keep_alive = keep_alive
@@ -488,6 +516,10 @@ class PipelineSchedule:
         out = {f"{k}_ms_mean": sum(v) / len(v) for k, v in acc.items()}
         out.update({f"{k}_ms_max": max(v) for k, v in acc.items()})
         out["host_issue_ms"] = getattr(self, "_host_ms", float("nan"))
+        # host milliseconds by action type: a rank whose GPU waits for its neighbours runs ahead until the launch
+        # queue (or an NCCL enqueue) back-pressures it, so on non-critical ranks host time ~ step time by design
+        for k, v in sorted(getattr(self, "_host_by_type", {}).items(), key=lambda kv: -kv[1])[:4]:
+            out[f"host_ms_in_{k}"] = v
         out.update(self.measured())
         return out
 

@@ -60,6 +60,10 @@ class PipelineStage:
         self.graphs = None
         self.recompute = False    # activation recomputation: forward keeps its input only, backward re-runs the forward
         self.has_params = any(True for _ in submodule.parameters())
+        # a stage boundary behind a self-attention block carries the packed [x1 ; x0] tensor (2x the rows)
+        from ..models.transformer import part_io_rows
+        parts = [getattr(l, "part", "full") for l in submodule.layers.values()]
+        self.in_rows, self.out_rows = part_io_rows(parts[0], parts[-1], self.args.cross_attn and not self.args.norm_first) if parts else (1, 1)
 
     # ---- memory layout --------------------------------------------------------------------------------------
     def materialize(self, dtype: Optional[torch.dtype] = None) -> "PipelineStage":
@@ -217,7 +221,7 @@ class PipelineStage:
                 raise ValueError("a tensor-parallel stage needs seq_len (set by the runner) to interpret its input rows")
             b = inp.reshape(-1, self.args.dim).shape[0] * self.tp_size // S
         else:
-            b, S = inp.shape[0], inp.shape[1]
+            b, S = inp.shape[0] // (1 if self.is_first else self.in_rows), inp.shape[1]
         ctx = self._ctx(mb, b, S)
         st: dict = {}
         if self.device.type == "cuda":
@@ -335,12 +339,12 @@ class PipelineStage:
         self._set_mb_seed(mb)
         if g is None:
             g = {"in": inp.clone(), "tgt": None if target is None else target.clone(), "F": torch.cuda.CUDAGraph(),
-                 "B": None, "dout": None, "din": None, "sends": {},
+                 "B": None, "dout": None, "din_B": None, "din_I": None, "sends": {},
                  # one private pool per slot: within a slot the replay order F -> B (or F -> I -> W) is the capture
                  # order, so its graphs may share scratch; across slots live ranges interleave differently from the
                  # capture order (slot 1's stash is live while slot 0's backward replays), so nothing is shared
                  "pool": torch.cuda.graph_pool_handle()}
-            b, S = inp.shape[0], inp.shape[1]
+            b, S = inp.shape[0] // (1 if self.is_first else self.in_rows), inp.shape[1]
             ctx = Ctx(self.args, b, S, self.base_seed, 0, self.training, 0)   # micro-batch variation comes from the device-side offset only
             st: dict = {}
             n0 = L.launches()
@@ -353,7 +357,11 @@ class PipelineStage:
             g.update(out=out, loss=loss, stash=st, ctx=ctx, nF=L.launches() - n0, shape=(b, S))
             self.graphs[slot] = g
         else:
-            g["in"].copy_(inp)
+            if tuple(inp.shape) != tuple(g["in"].shape):   # never rely on copy_ broadcasting (uneven micro-batches)
+                raise RuntimeError(f"stage {self.stage_index}: graph slot {slot} was captured for input "
+                                   f"{tuple(g['in'].shape)}, got {tuple(inp.shape)}")
+            if inp.data_ptr() != g["in"].data_ptr():       # a receive that landed in the static input needs no copy
+                g["in"].copy_(inp)
             if target is not None:
                 g["tgt"].copy_(target)
             L.count_launch(g["nF"])
@@ -364,6 +372,21 @@ class PipelineStage:
         self.ctxs[mb] = g["ctx"]
         return g["out"]
 
+    @staticmethod
+    def _slot_dout(g: dict, dout: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        """The slot's static output-gradient buffer.  Allocated ONCE per slot and never rebound: a slot can see both a
+        B graph and an I graph (ZeroBubble orders merge only some micro-batches back into B), and every captured graph
+        of the slot must keep reading the buffer the replays copy into."""
+        if dout is None:
+            return None
+        if g.get("dout") is None:
+            g["dout"] = dout.clone()
+        elif dout.data_ptr() != g["dout"].data_ptr():
+            if dout.numel() != g["dout"].numel():
+                raise RuntimeError(f"graph slot captured for an output gradient of {tuple(g['dout'].shape)}, got {tuple(dout.shape)}")
+            g["dout"].copy_(dout.reshape(g["dout"].shape))
+        return g["dout"]
+
     def backward_graphed(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         from ..ops import _lib as L
         slot = mb % self.nslots
@@ -371,22 +394,20 @@ class PipelineStage:
         self._set_mb_seed(mb)
         self.stash.pop(mb, None)
         self.ctxs.pop(mb, None)
+        sd = self._slot_dout(g, dout)
         if g["B"] is None:
-            g["dout"] = None if dout is None else dout.clone()
             g["B"] = torch.cuda.CUDAGraph()
             st, ctx = g["stash"], g["ctx"]
             n0 = L.launches()
             with torch.cuda.graph(g["B"], pool=g["pool"]):
                 with torch.no_grad():
-                    douts = [st["dlogits"]] if g["dout"] is None else [g["dout"]]
-                    g["din"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                    douts = [st["dlogits"]] if sd is None else [sd]
+                    g["din_B"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
             g["nB"] = L.launches() - n0
         else:
-            if dout is not None:
-                g["dout"].copy_(dout.reshape(g["dout"].shape))
             L.count_launch(g["nB"])
         g["B"].replay()
-        return g["din"]
+        return g["din_B"]
 
     def backward_input_graphed(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         """Graph replay of IR action ``I`` on the slot of ``mb``: the deferred weight-gradient operands are static
@@ -397,8 +418,8 @@ class PipelineStage:
         self._set_mb_seed(mb)
         self.stash.pop(mb, None)
         self.ctxs.pop(mb, None)
+        sd = self._slot_dout(g, dout)
         if g.get("I") is None:
-            g["dout"] = None if dout is None else dout.clone()
             g["I"] = torch.cuda.CUDAGraph()
             st, ctx = g["stash"], g["ctx"]
             n0 = L.launches()
@@ -406,18 +427,16 @@ class PipelineStage:
             try:
                 with torch.cuda.graph(g["I"], pool=g["pool"]):
                     with torch.no_grad():
-                        douts = [st["dlogits"]] if g["dout"] is None else [g["dout"]]
-                        g["din"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                        douts = [st["dlogits"]] if sd is None else [sd]
+                        g["din_I"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
             finally:
                 g["wlist"], self.sink.deferred = self.sink.deferred, None
             g["nI"] = L.launches() - n0
             g["W"] = None
         else:
-            if dout is not None:
-                g["dout"].copy_(dout.reshape(g["dout"].shape))
             L.count_launch(g["nI"])
         g["I"].replay()
-        return g["din"]
+        return g["din_I"]
 
     def backward_weight_graphed(self, mb: int, last: bool = False) -> None:
         from ..ops import _lib as L

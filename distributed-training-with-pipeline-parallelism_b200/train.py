@@ -103,7 +103,9 @@ def main(argv: Optional[List[str]] = None) -> dict:
         if cfg.tp > 1:
             shard_model_for_tp(model, tp_idx, cfg.tp)
         st = PipelineStage(model, sidx, num_stages, dev, dp_group=groups.get("dp_group"), tp_group=tp_group)
-        st.base_seed = cfg.seed
+        # replicas see different data and must draw different dropout masks; the tp ranks of one replica share the
+        # base (models/tp.py mixes the tp rank in itself, so forward and backward seeds still match)
+        st.base_seed = cfg.seed + 0x9E37 * dp_idx
         st.materialize()
         stages.append(st)
     start_step = 0

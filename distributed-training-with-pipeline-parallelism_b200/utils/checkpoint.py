@@ -114,6 +114,12 @@ def load_stage(stage, directory: str, with_optimizer: bool = True) -> int:
                 for n, t in cut.items():
                     mine.setdefault(n, {})[slot] = t
             stage.load_optimizer_state_dict({"state": mine, "step": step})
+    if not step:
+        # no optimizer state (saved or requested without it): the step recorded beside the parameters still tells the
+        # training loop where the LR schedule / data stream were, and seeds the dropout streams (stage.step_count)
+        step = max([int(shard.get("step", 0) or 0) for _, shard in files] or [0])
+        if step and hasattr(stage, "step_count"):
+            stage.step_count = step
     return step
 
 

@@ -104,6 +104,25 @@ int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void* dy2, cons
                          const float* rstd, const void* gamma, void* dz, void* da, float* dgamma, float* dbeta, int T,
                          int d, float dropout_p, unsigned long long seed, int rms, void* stream);
 
+/* ---- K4: flash attention forward / backward on tcgen05 (csrc/attention_fwd.cu, attention_bwd.cu) ---------------
+ * q [B*Sq, ldq], k / v [B*Skv, ldk / ldv], o [B*Sq, ldo]: bf16 rows of H heads x dh columns (column-sliced views of a
+ * packed QKV activation are fine; heads are addressed through 4-D TMA maps, nothing is transposed or copied).
+ * lse [B, H, Sq] fp32 (natural log).  causal needs Skv >= Sq; dropout (probability dropout, counter-based mask from
+ * (seed, element index), regenerated in backward) needs an even Skv.  dh: multiple of 8, 8..256 (tcgen05 tiles of
+ * 64 / 128 / 192 / 256 columns, zero-padded by TMA).  reserved* arguments must be 0 / NULL.
+ * Backward writes dq / dk / dv with the row strides of q / k / v; `scratch` = ppb_attn_bwd_scratch_bytes(B, H,
+ * max(Sq, Skv), dh) bytes, 256-byte aligned, no initialisation needed (delta rows + the fp32 dQ accumulator).
+ * Replaces aten.bmm x2 + mul.Scalar + _safe_softmax + dropout and their backwards -- torch transformer.py:1158-1194,
+ * reached from helper:40-44, :52. */
+int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Skv, int dh,
+                 long long ldq, long long ldk, long long ldv, long long ldo, int causal, int reserved0, int reserved1,
+                 float scale, float dropout_p, unsigned long long seed, void* stream);
+long long ppb_attn_bwd_scratch_bytes(int B, int H, int S, int dh);
+int ppb_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dO, const float* lse, void* dq,
+                 void* dk, void* dv, void* scratch, void* reserved_ptr, int B, int H, int Sq, int Skv, int dh,
+                 long long ldq, long long ldk, long long ldv, long long ldo, int causal, int reserved0, int reserved1,
+                 float scale, float dropout_p, unsigned long long seed, void* stream);
+
 /* ---- K7: fused softmax-cross-entropy (loss rows + in-place dlogits) ----------------------------------------
  * Replaces aten._log_softmax + nll_loss_forward/backward + logits.clone() -- helper:54, helper:197-201. */
 int ppb_xent_fwd_bwd(void* logits, long long ld, const long long* targets, float* row_loss, int T, int V,

@@ -10,7 +10,7 @@ if ROOT not in sys.path:
 
 
 def parity_worker(rank, world_size, schedule_type, n_layers, v, m, results_queue, master_port=None, optimizer=None,
-                  dp=1, device="cpu", rule="reference"):
+                  dp=1, device="cpu", rule="reference", costs=None):
     """Pipelined loss + per-parameter grads must equal the single-process full-model ones (same seed, dropout 0)."""
     try:
         import torch
@@ -24,6 +24,9 @@ def parity_worker(rank, world_size, schedule_type, n_layers, v, m, results_queue
         mesh = init_mesh(dp_size=dp, pp_size=world_size // dp)
         P = mesh.pp_size
         args = ModelArgs(dim=64, n_layers=n_layers, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0)
+        if costs is not None:   # force the positions of the sub-layer cuts through "measured" unit costs
+            from ppb200.parallel.partition import set_measured_costs
+            set_measured_costs(args, 1024, costs)
         torch.manual_seed(1234)
         full = Transformer(args)
         B, S = 8 * dp, 16

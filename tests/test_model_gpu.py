@@ -126,6 +126,91 @@ def test_split_backward_schedule_matches_fused_backward(graphs):
     assert rel < 3e-4, (rel, worst, res["1F1B"][0], res["ZeroBubble1F1B"][0])
 
 
+def test_graph_slots_that_see_both_B_and_I_graphs():
+    """A graph slot of a non-last stage can serve a fused backward (B) for one micro-batch and a split backward (I + W)
+    for another (ZeroBubble orders merge only some micro-batches back into B).  Both captured graphs must read the
+    slot's ONE static output-gradient buffer; with graphs on, losses and parameters must track the eager run."""
+    torch.manual_seed(9)
+    args = ModelArgs(dim=256, n_layers=4, n_heads=4, vocab_size=512, ffn_dim=512, dropout=0.1)
+    full = Transformer(args)
+    x = torch.stack([torch.randperm(512)[:128] for _ in range(8)])
+    y = torch.randint(0, 512, (8, 128))
+    order = {0: ("0F0 1F0 1B0 0I0 0F1 1F1 1B1 0B1 0W0 0F2 1F2 1B2 0B2 0F3 1F3 1B3 0I3 0W3").split()}
+    res = {}
+    for graphs in (False, True):
+        stages = [manual_model_split(copy.deepcopy(full), s, 2, torch.device("cuda"), rule="balanced") for s in range(2)]
+        for st in stages:
+            st.base_seed = 11
+        sched = make_schedule("Interleaved1F1B", stages, 4, None, optimizer={"lr": 1e-3, "weight_decay": 0.0},
+                              cuda_graphs=graphs, graph_warmup_steps=1, actions=order)
+        if graphs:
+            assert sched.use_graphs and stages[0].nslots == 2
+        hist = []
+        for _ in range(5):
+            losses = []
+            sched.step(x.cuda(), target=y.cuda(), losses=losses)
+            hist.append(torch.stack([l.reshape(()) for l in losses]).mean().item())
+        res[graphs] = (hist, torch.cat([st.master[:st.n_total] for st in stages]).clone())
+    assert max(abs(a - b) for a, b in zip(res[False][0], res[True][0])) < 5e-4, res
+    rel = ((res[False][1] - res[True][1]).norm() / res[False][1].norm()).item()
+    assert rel < 3e-4, (rel, res[False][0], res[True][0])
+
+
+def test_fine_partition_with_packed_boundary_cuda():
+    """Sub-layer cuts on the GPU (a boundary behind a self-attention block carries the packed [x1 ; x0] tensor): three
+    local virtual stages with forced cut positions against the unsplit model, graphs on, dropout on."""
+    from ppb200.parallel import partition as Pn
+    torch.manual_seed(10)
+    args = ModelArgs(dim=256, n_layers=2, n_heads=4, vocab_size=512, ffn_dim=512, dropout=0.1)
+    full = Transformer(args)
+    x = torch.stack([torch.randperm(512)[:128] for _ in range(6)])
+    y = torch.randint(0, 512, (6, 128))
+    res = {}
+    for split in (False, True):
+        if split:
+            Pn.set_measured_costs(args, 1024, {"self": 1.0, "cross": 1.0, "ffn": 1.0, "head": 0.0, "embed": 0.0})
+        try:
+            n = 3 if split else 1
+            stages = [manual_model_split(copy.deepcopy(full), s, n, torch.device("cuda"), rule="fine" if split else "reference")
+                      for s in range(n)]
+        finally:
+            Pn.clear_measured_costs()
+        if split:   # L0.self+cross | L0.ffn + L1.self | L1.cross+ffn
+            assert [getattr(l, "part", "full") for st in stages for l in st.submod.layers.values()] == ["attn", "ffn", "self", "cross+ffn"]
+            assert stages[1].out_rows == 2 and stages[2].in_rows == 2
+        for st in stages:
+            st.base_seed = 5
+        sched = make_schedule("Interleaved1F1B" if split else "1F1B", stages if split else stages[0], 3, None,
+                              optimizer={"lr": 1e-3, "weight_decay": 0.0}, graph_warmup_steps=1)
+        hist = []
+        for _ in range(4):
+            losses = []
+            sched.step(x.cuda(), target=y.cuda(), losses=losses)
+            hist.append(torch.stack([l.reshape(()) for l in losses]).mean().item())
+        views = {}
+        for st in stages:
+            for name, o, shp in st.param_names:
+                views[name] = st.master[o:o + torch.Size(shp).numel()].clone()
+        res[split] = (hist, views)
+    assert max(abs(a - b) for a, b in zip(res[False][0], res[True][0])) < 5e-4, res
+    assert set(res[False][1]) == set(res[True][1])
+    worst = max(((res[False][1][k] - res[True][1][k]).norm() / (res[False][1][k].norm() + 1e-12)).item() for k in res[False][1])
+    assert worst < 1e-3, worst
+
+
+def test_measured_unit_costs_drive_the_partition():
+    from ppb200.parallel import partition as Pn
+    args = ModelArgs(dim=256, n_layers=6, n_heads=4, vocab_size=2048, ffn_dim=512, dropout=0.1, dtype=torch.bfloat16)
+    try:
+        c = Pn.calibrate(args, 2, 128, torch.device("cuda"))
+        assert c["source"] == "measured" and all(c[k] > 0 for k in ("self", "cross", "ffn", "head", "embed")), c
+        assert Pn.unit_costs(args, 128)["source"] == "measured"
+        parts = [Pn.stage_layer_parts(6, 4, s, "fine", args, 128) for s in range(4)]
+        assert sum(len(p) for p in parts) >= 6
+    finally:
+        Pn.clear_measured_costs()
+
+
 @pytest.mark.parametrize("act,dropout", [("gelu", 0.0), ("relu", 0.1)])
 def test_prenorm_gpt_block_cuda_matches_cpu(act, dropout):
     torch.manual_seed(4)

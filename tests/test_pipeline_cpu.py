@@ -247,11 +247,28 @@ def test_activation_recomputation_gives_identical_gradients(order):
     assert torch.allclose(res[False][1], res[True][1], atol=1e-7)
 
 
-@pytest.mark.parametrize("schedule,world,n_layers,v,m", [("1F1B", 4, 5, 1, 4), ("Interleaved1F1B", 2, 4, 2, 4)])
-def test_fine_partition_cuts_inside_layers_and_keeps_parity(schedule, world, n_layers, v, m):
-    """Partition rule 'fine': stage boundaries may fall between the attention sub-blocks and the feed-forward block of a
-    layer; pipelined loss and gradients still equal the single-process ones."""
-    res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), {"rule": "fine"}, timeout=400)
+_EQUAL_UNITS = {"self": 1.0, "cross": 1.0, "ffn": 1.0, "head": 1.0, "embed": 0.0}
+
+
+@pytest.mark.parametrize("schedule,world,n_layers,v,m,costs", [
+    ("1F1B", 4, 5, 1, 4, None), ("Interleaved1F1B", 2, 4, 2, 4, None),
+    # equal unit costs put a cut behind a self-attention block (packed [x1 ; x0] boundary) and one behind a
+    # cross-attention block: stages = L0 + L1.self | L1.cross+ffn + L2.attn | L2.ffn + L3 | L4 + head
+    ("1F1B", 4, 5, 1, 4, _EQUAL_UNITS), ("Interleaved1F1B", 2, 4, 2, 4, _EQUAL_UNITS)])
+def test_fine_partition_cuts_inside_layers_and_keeps_parity(schedule, world, n_layers, v, m, costs):
+    """Partition rule 'fine': stage boundaries may fall behind the self-attention, the cross-attention or before the
+    feed-forward block of a layer; pipelined loss and gradients still equal the single-process ones."""
+    if costs is not None and n_layers == 5:
+        from ppb200.models import ModelArgs
+        from ppb200.parallel import partition as Pn
+        a = ModelArgs(dim=64, n_layers=5, n_heads=4, vocab_size=101, ffn_dim=96, dropout=0.0)
+        Pn.set_measured_costs(a, 1024, costs)
+        try:
+            parts = [Pn.stage_layer_parts(5, 4, s, "fine", a, 1024) for s in range(4)]
+        finally:
+            Pn.clear_measured_costs()
+        assert parts[0][-1] == (1, "self") and parts[1][0] == (1, "cross+ffn") and parts[1][-1] == (2, "attn"), parts
+    res = launch_workers(parity_worker, world, (schedule, n_layers, v, m), {"rule": "fine", "costs": costs}, timeout=400)
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["max_rel_grad_err"] < 2e-4, r

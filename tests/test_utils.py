@@ -66,7 +66,7 @@ def test_fine_partition_state_dicts_tile_the_full_model():
         assert set(built) == set(sd)
     assert seen == keys and cut_inside
     units = Pn.fine_unit_ranges(24, 8, ModelArgs(dim=1024, n_layers=24, n_heads=16, vocab_size=50257), 1024)
-    assert units[0][0] == 0 and units[-1][1] == 48 and all(a[1] == b[0] for a, b in zip(units, units[1:]))
+    assert units[0][0] == 0 and units[-1][1] == 72 and all(a[1] == b[0] for a, b in zip(units, units[1:]))
 
 
 def test_interleaved_fallback_rule_matches_helper():
