@@ -20,6 +20,9 @@
 
 namespace ppb {
 
+#ifndef PPB_GEMM_PAIR_AUTO
+#define PPB_GEMM_PAIR_AUTO 0   // flipped to 1 once the CTA-pair kernels have a measured win on the flagship shapes
+#endif
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int GEMM_THREADS = 192;  // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer + TMEM owner
@@ -50,23 +53,32 @@ struct DstMaps {
   CUtensorMap m[8];  // fp32 accumulators of every data-parallel replica (own + peers), peer-mapped over NVLink
 };
 
-template <int BN>
+// CG = CTAs per tile (cta_group): 1 = one CTA computes a 128 x BN tile; 2 = a CTA pair computes a 256 x BN tile, each
+// CTA staging its own 128 rows of A and HALF of the B tile (BN/2 rows), so the operand bytes per FLOP that each SM
+// pulls through L2 drop by a third at BN = 256.
+template <int BN, int CG = 1>
 struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int STAGES = (STAGE_BYTES >= 49152) ? 4 : (STAGE_BYTES >= 32768 ? 6 : 8);
   static constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024 align slack
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
-template <int BN, bool A_MN, bool B_MN, int OUT>
+template <int BN, bool A_MN, bool B_MN, int OUT, int CG = 1>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                           const GemmParams& p, const CUtensorMap* dst_maps,
                                           const CUtensorMap* a_maps = nullptr) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, CG>;
+  static_assert(CG == 1 || (OUT != 3 && BN >= 128), "CTA pairs: plain / accumulate outputs, BN >= 128");
+  constexpr int TM = BM * CG;          // rows of the (pair) tile
+  constexpr int BNH = BN / CG;         // B rows staged by one CTA
+  const int cta_rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const bool leader = cta_rank == 0;
+  const int tile0 = blockIdx.x / CG, tile_stride = gridDim.x / CG;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -93,14 +105,18 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);
+      mbar_init(tempty_bar(a), 4 * CG);   // epilogue warps of BOTH CTAs release the accumulator to the leader's issuer
     }
     for (int w = 0; w < 8; ++w) mbar_init(bar_base + 8u * (2 * STAGES + 5 + w), 1);  // fused all-reduce slab loads
     fence_mbar_init();
   }
-  if (warp == 5) tmem_alloc(tmem_ptr_smem, Cfg::TMEM_COLS);
+  if (warp == 5) {
+    if constexpr (CG == 2) tmem_alloc_cg2(tmem_ptr_smem, Cfg::TMEM_COLS);
+    else tmem_alloc(tmem_ptr_smem, Cfg::TMEM_COLS);
+  }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all();   // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_ptr_smem - smem_base));
 
@@ -116,11 +132,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = tile0; t < total_tiles; t += tile_stride) {
         const int mn = t % (p.tiles_m * p.tiles_n);
         const int sp = t / (p.tiles_m * p.tiles_n);
-        const int m0 = m_block_of(mn) * BM;
-        const int n0 = (mn / p.tiles_m) * BN;
+        const int m0 = m_block_of(mn) * TM + cta_rank * BM;       // this CTA's 128 rows of the (pair) tile
+        const int n0 = (mn / p.tiles_m) * BN + cta_rank * BNH;    // this CTA's share of the B rows
         const int kb0 = sp * p.kb_per_split;
         const int kb1 = min(num_kb_total, kb0 + p.kb_per_split);
         // K12: the A rows of this tile come from the shard (possibly on a peer GPU) that owns them
@@ -133,22 +149,27 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
-          mbar_expect_tx(full_bar(stage), Cfg::STAGE_BYTES);
+          // CTA pair: both CTAs' bytes are counted by the LEADER's barrier (the only one the MMA issuer waits on)
+          if (leader) mbar_expect_tx(full_bar(stage), CG * Cfg::STAGE_BYTES);
           const uint32_t sa = smem_base + stage * Cfg::STAGE_BYTES;
           const uint32_t sb = sa + Cfg::A_BYTES;
+          auto load = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1) {
+            if constexpr (CG == 2) tma_load_2d_cg2(dst, tm, full_bar(stage), c0, c1);
+            else tma_load_2d(dst, tm, full_bar(stage), c0, c1);
+          };
           if (!A_MN) {
-            tma_load_2d(sa, ta, full_bar(stage), kb * BK, a_row);  // box {64 k, 128 rows}
+            load(sa, ta, kb * BK, a_row);  // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int i = 0; i < BM / 64; ++i)  // box {64 m, 64 k}
-              tma_load_2d(sa + i * (BK * 128), &tmA, full_bar(stage), m0 + i * 64, kb * BK);
+              load(sa + i * (BK * 128), &tmA, m0 + i * 64, kb * BK);
           }
           if (!B_MN) {
-            tma_load_2d(sb, &tmB, full_bar(stage), kb * BK, n0);  // box {64 k, BN rows}
+            load(sb, &tmB, kb * BK, n0);  // box {64 k, BN/CG rows}
           } else {
 #pragma unroll
-            for (int i = 0; i < BN / 64; ++i)
-              tma_load_2d(sb + i * (BK * 128), &tmB, full_bar(stage), n0 + i * 64, kb * BK);
+            for (int i = 0; i < BNH / 64; ++i)
+              load(sb + i * (BK * 128), &tmB, n0 + i * 64, kb * BK);
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -159,12 +180,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     }
   } else if (warp == 5) {
     // ======================= MMA issuer =======================
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = make_idesc_bf16(TM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      for (int t = tile0; t < total_tiles; t += tile_stride, ++it) {
         const int sp = t / (p.tiles_m * p.tiles_n);
         const int kb0 = sp * p.kb_per_split;
         const int kb1 = min(num_kb_total, kb0 + p.kb_per_split);
@@ -186,15 +207,20 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                                      : make_smem_desc_sw128(sa + k * 32, 16, 1024);
             const uint64_t db = B_MN ? make_smem_desc_sw128(sb + k * 2048, BK * 128, 1024)
                                      : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-            umma_f16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (CG == 2) umma_f16_ss_cg2(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else umma_f16_ss(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(empty_bar(stage));  // smem slot is free once these MMAs have read it
+          // smem slot is free once these MMAs have read it (pair: the slot of BOTH CTAs)
+          if constexpr (CG == 2) umma_commit_cg2(empty_bar(stage));
+          else umma_commit(empty_bar(stage));
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs: each drains its own 128 TMEM lanes)
+        if constexpr (CG == 2) umma_commit_cg2(tfull_bar(acc));
+        else umma_commit(tfull_bar(acc));
       }
     }
     __syncwarp();
@@ -205,9 +231,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     int it = 0;
     int buf = 0;
     uint32_t push_phase = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    for (int t = tile0; t < total_tiles; t += tile_stride, ++it) {
       const int mn = t % (p.tiles_m * p.tiles_n);
-      const int m0 = m_block_of(mn) * BM;
+      const int m0 = m_block_of(mn) * TM + cta_rank * BM;
       const int n0 = (mn / p.tiles_m) * BN;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
@@ -329,7 +355,10 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       // all TMEM reads of this accumulator are complete -> hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (lane == 0) {
+        if constexpr (CG == 2) mbar_arrive_leader(tempty_bar(acc));
+        else mbar_arrive(tempty_bar(acc));
+      }
       if constexpr (OUT == 3) {
         // ---- fused all-reduce: the LAST K-split to finish this 32-row slab streams the completed gradient slab
         //      to every replica (own reduced buffer through L2, the peers' over NVLink) with TMA only ----
@@ -376,7 +405,20 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  if constexpr (CG == 2) cluster_sync_all();   // no CTA of the pair leaves while the other may still signal it
+  if (warp == 5) {
+    if constexpr (CG == 2) tmem_dealloc_cg2(tmem_base, Cfg::TMEM_COLS);
+    else tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// CTA-pair variant: 2-CTA clusters, cta_group::2 UMMA on 256 x BN tiles (see GemmCfg).  Operands are this GPU's
+// memory only (the tensor-parallel kernels that read peer memory keep one CTA per tile and plain TMA loads).
+template <int BN, bool A_MN, bool B_MN, int OUT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmC, const GemmParams p) {
+  gemm_body<BN, A_MN, B_MN, OUT, 2>(tmA, tmB, tmC, p, nullptr);
 }
 
 template <int BN, bool A_MN, bool B_MN, int OUT>
@@ -445,6 +487,45 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUt
   return 0;
 }
 
+template <int BN, bool A_MN, bool B_MN, int OUT>
+static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const GemmParams& p,
+                            int grid, cudaStream_t stream) {
+  using Cfg = GemmCfg<BN, 2>;
+  auto kfn = gemm_tcgen05_pair_kernel<BN, A_MN, B_MN, OUT>;
+  static bool attr_done[64] = {false};
+  int dev = 0;
+  PPB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev >= 64 || !attr_done[dev]) {
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    if (dev < 64) attr_done[dev] = true;
+  }
+  kfn<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);   // grid is even: __cluster_dims__(2,1,1)
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+template <int BN, int OUT>
+static int dispatch_major_pair(int a_mn, int b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                               const GemmParams& p, int grid, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch_gemm_pair<BN, false, false, OUT>(tmA, tmB, tmC, p, grid, s);
+  if (!a_mn && b_mn) return launch_gemm_pair<BN, false, true, OUT>(tmA, tmB, tmC, p, grid, s);
+  if (a_mn && b_mn) return launch_gemm_pair<BN, true, true, OUT>(tmA, tmB, tmC, p, grid, s);
+  return launch_gemm_pair<BN, true, false, OUT>(tmA, tmB, tmC, p, grid, s);
+}
+
+// CTAs per tile: 0 = automatic, 1 / 2 = forced (ppb_set_gemm_cta_group / $PPB_GEMM_CG)
+static int g_gemm_cg = -1;
+static int gemm_cg_setting() {
+  if (g_gemm_cg < 0) {
+    const char* e = getenv("PPB_GEMM_CG");
+    g_gemm_cg = e ? atoi(e) : 0;
+    if (g_gemm_cg < 0 || g_gemm_cg > 2) g_gemm_cg = 0;
+  }
+  return g_gemm_cg;
+}
+// What "automatic" means: pairs whenever the problem has at least two 128-row blocks and the tile is >= 128 wide.
+constexpr bool kPairAuto = PPB_GEMM_PAIR_AUTO;
+
 template <int BN, int OUT>
 static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                           const GemmParams& p, int grid, cudaStream_t s) {
@@ -459,11 +540,15 @@ static int dispatch_major(int a_mn, int b_mn, const CUtensorMap& tmA, const CUte
 // bandwidth bound and 2x slower), and for the accumulate mode the split count minimises
 // waves * (k-blocks per split * cycles per k-block + fixed tile overhead).
 static void choose_config(int M, int N, int K, int out_mode, int force_bn, int force_splits, int* bn_out,
-                          int* splits_out) {
-  const int sms = sm_count();
+                          int* splits_out, int* cg_out = nullptr) {
   const int num_kb = (K + BK - 1) / BK;
   int bn = force_bn ? force_bn : (N > 128 ? 256 : (N > 64 ? 128 : 64));
-  const long long tiles = (long long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+  int cg = gemm_cg_setting();
+  if (cg == 0) cg = (kPairAuto && M > BM && bn >= 128) ? 2 : 1;
+  if (bn < 128 || cg_out == nullptr) cg = 1;
+  if (cg_out) *cg_out = cg;
+  const int sms = sm_count() / cg;   // tiles that run concurrently
+  const long long tiles = (long long)((M + BM * cg - 1) / (BM * cg)) * ((N + bn - 1) / bn);
   const int max_sp = (out_mode == PPB_OUT_F32_ACCUM) ? 16 : 1;
   double best = 1e30;
   int best_sp = 1;
@@ -506,8 +591,8 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   if (epi == PPB_EPI_BIAS_RELU_DROPOUT) PPB_REQUIRE((N % 2) == 0, "ppb_gemm_bf16: dropout epilogue needs even N");
   if (out_mode != PPB_OUT_F32_ACCUM) PPB_REQUIRE(force_splits <= 1, "ppb_gemm_bf16: split-K needs the fp32 accumulate output mode");
 
-  int bn = 128, splits = 1;
-  choose_config(M, N, K, out_mode, force_bn, force_splits, &bn, &splits);
+  int bn = 128, splits = 1, cg = 1;
+  choose_config(M, N, K, out_mode, force_bn, force_splits, &bn, &splits, &cg);
 
   CUtensorMap tmA, tmB, tmC;
   bool ok = true;
@@ -517,7 +602,7 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   else
     ok = ok && make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda * 2, 64, BK);
   if (!b_mn_major)
-    ok = ok && make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn);
+    ok = ok && make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn / cg);
   else
     ok = ok && make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK);
   if (out_mode == PPB_OUT_BF16)
@@ -530,7 +615,7 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.M = M;
   p.N = N;
   p.K = K;
-  p.tiles_m = (M + BM - 1) / BM;
+  p.tiles_m = (M + BM * cg - 1) / (BM * cg);
   p.tiles_n = (N + bn - 1) / bn;
   p.splits = splits;
   p.kb_per_split = (((K + BK - 1) / BK) + splits - 1) / splits;
@@ -549,7 +634,26 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   p.drop_thresh = dropout_thr32(dropout_p);
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   const long long total = (long long)p.tiles_m * p.tiles_n * splits;
-  const int grid = (int)(total < sm_count() ? total : sm_count());
+  const int slots = sm_count() / cg;
+  const int grid = (int)(total < slots ? total : slots) * cg;
+
+  if (cg == 2) {
+#define PPB_DISPATCH_PAIR(BN_)                                                                                   \
+  switch (out_mode) {                                                                                            \
+    case PPB_OUT_BF16: return dispatch_major_pair<BN_, 0>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream); \
+    case PPB_OUT_F32: return dispatch_major_pair<BN_, 1>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream);  \
+    case PPB_OUT_F32_ACCUM: return dispatch_major_pair<BN_, 2>(a_mn_major, b_mn_major, tmA, tmB, tmC, p, grid, stream); \
+    default: break;                                                                                              \
+  }
+    if (bn == 256) {
+      PPB_DISPATCH_PAIR(256)
+    } else {
+      PPB_DISPATCH_PAIR(128)
+    }
+#undef PPB_DISPATCH_PAIR
+    set_error("ppb_gemm_bf16: bad out_mode %d", out_mode);
+    return -2;
+  }
 
 #define PPB_DISPATCH_OUT(BN_)                                                                               \
   switch (out_mode) {                                                                                       \
@@ -570,6 +674,12 @@ extern "C" int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   return -2;
 }
 
+
+extern "C" int ppb_set_gemm_cta_group(int cg) {
+  PPB_REQUIRE(cg >= 0 && cg <= 2, "ppb_set_gemm_cta_group: 0 (automatic), 1 or 2");
+  ppb::g_gemm_cg = cg;
+  return 0;
+}
 
 extern "C" long long ppb_gemm_allreduce_scratch_bytes(int M, int N) {
   return (long long)((M + BM - 1) / BM) * ((N + 63) / 64) * 4 * sizeof(unsigned int) + 256;

@@ -48,6 +48,11 @@ int ppb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, lo
                   const void* aux, long long ld_aux, unsigned long long seed, float dropout_p, int force_bn,
                   int force_splits, void* stream);
 
+/* CTAs per output tile: 1 = one CTA computes a 128 x BN tile (cta_group::1); 2 = a 2-CTA cluster computes a 256 x BN
+ * tile with cta_group::2 UMMAs, each CTA staging its own A rows and half of the B tile; 0 (default) = automatic.
+ * Also $PPB_GEMM_CG.  Operands of a pair launch must be this GPU's memory. */
+int ppb_set_gemm_cta_group(int cg);
+
 /* ---- K10: last-micro-batch wgrad GEMM fused with the data-parallel gradient all-reduce ---------------------------
  * accum[M,N] += A^T B exactly like the wgrad form of ppb_gemm_bf16 (A stored [K, lda], B stored [K, ldb], split-K,
  * TMA reduce-add); additionally, as soon as a 32-row slab of a tile is complete, the CTA that finished it last
