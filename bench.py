@@ -275,8 +275,10 @@ def run_reference(a, rank, local_rank, world):
     why = None
     if a.model not in ("ref-gpt2-medium", "ref-gpt2-xl", "ref-small"):
         why = f"the helper's Transformer cannot express model preset {a.model!r} (fixed nn.TransformerDecoderLayer block)"
-    elif a.tp > 1 or a.dp > 1:
-        why = "the helper has no tensor/data parallelism (pipeline stages only)"
+    elif a.tp > 1:
+        why = "the helper has no tensor parallelism (pipeline stages only) and its fixed block cannot be sharded"
+    elif a.dp > 1 and a.schedule == "Interleaved1F1B":
+        why = "DP baseline is built for one stage per rank (GPipe / 1F1B)"
     elif a.schedule not in ("GPipe", "1F1B", "Interleaved1F1B"):
         why = f"the helper selects among GPipe / 1F1B / Interleaved1F1B only (got {a.schedule})"
     if why is not None:
@@ -291,6 +293,22 @@ def run_reference(a, rank, local_rank, world):
         os.environ.setdefault("RANK", "0")
         os.environ.setdefault("WORLD_SIZE", "1")
     dist.init_process_group("nccl", device_id=dev)
+    # data parallelism is not in the helper (helper:178 creates a group it never uses): the DP baseline is the stock
+    # torch composition SURVEY.md 6.4 names -- the helper's pruned stage module wrapped in DistributedDataParallel
+    # (torch's PipelineStage drives no_sync for all but the last micro-batch), NCCL all-reduce of the gradients
+    dp = a.dp
+    pp_world = world // dp
+    pp_rank, dp_idx = rank % pp_world, rank // pp_world
+    pp_group = dp_group = None
+    if dp > 1:
+        for d in range(dp):
+            g_ = dist.new_group([d * pp_world + p_ for p_ in range(pp_world)])
+            if d == dp_idx:
+                pp_group = g_
+        for p_ in range(pp_world):
+            g_ = dist.new_group([d * pp_world + p_ for d in range(dp)])
+            if p_ == pp_rank:
+                dp_group = g_
     dims = {"ref-gpt2-medium": dict(dim=1024, n_layers=24, n_heads=16, vocab_size=50257),
             "ref-gpt2-xl": dict(dim=1600, n_layers=48, n_heads=25, vocab_size=50257),
             "ref-small": dict()}[a.model]
@@ -300,9 +318,9 @@ def run_reference(a, rank, local_rank, world):
         dims = dict(dim=256, n_layers=max(2 * world * a.virtual_stages, 4), n_heads=4, vocab_size=4096)
     margs = ref.ModelArgs(**dims)
     v = a.virtual_stages if a.schedule == "Interleaved1F1B" else 1
-    num_stages = world * v
-    B, S = a.global_batch, a.seq_len
-    g = torch.Generator().manual_seed(1000)
+    num_stages = pp_world * v
+    B, S = a.global_batch // dp, a.seq_len
+    g = torch.Generator().manual_seed(1000 + dp_idx)
     x_host = torch.randint(0, margs.vocab_size, (B, S), generator=g).pin_memory()
     y_host = torch.randint(0, margs.vocab_size, (B, S), generator=g).pin_memory()
     x, y = x_host.to(dev), y_host.to(dev)
@@ -315,8 +333,20 @@ def run_reference(a, rank, local_rank, world):
     for i in range(v):
         torch.manual_seed(1234)
         model = ref.Transformer(margs).to(torch.bfloat16)
-        stage = ref.manual_model_split(model, rank + world * i, num_stages, dev)
-        model.to(dev)
+        if dp == 1:
+            stage = ref.manual_model_split(model, rank + world * i, num_stages, dev)
+            model.to(dev)
+        else:
+            # the helper's split binds the stage to the WORLD group (helper:93); with replicas the stage must live on its
+            # pipeline group, so the helper prunes the model (its partition rule, helper:60-91) and torch's own
+            # PipelineStage is rebuilt over the DDP-wrapped module
+            from torch.distributed.pipelining import PipelineStage as TorchStage
+            from torch.nn.parallel import DistributedDataParallel as DDP
+            ref.manual_model_split(model, pp_rank + pp_world * i, num_stages, dev)
+            model.to(dev)
+            has_params = any(True for _ in model.parameters())
+            mod = DDP(model, device_ids=[dev.index], process_group=dp_group, gradient_as_bucket_view=True) if has_params else model
+            stage = TorchStage(mod, pp_rank + pp_world * i, num_stages, dev, group=pp_group)
         stages.append(stage)
         params += list(model.parameters())
     if a.schedule == "GPipe":
@@ -331,22 +361,22 @@ def run_reference(a, rank, local_rank, world):
     def step(e2e=False):
         losses.clear()
         if e2e:
-            if rank == 0:
+            if pp_rank == 0:
                 x.copy_(x_host, non_blocking=True)
-            if rank == world - 1:
+            if pp_rank == pp_world - 1:
                 y.copy_(y_host, non_blocking=True)
-        if world == 1:
+        if pp_world == 1:
             schedule.step(x, target=y, losses=losses)
-        elif rank == 0:
+        elif pp_rank == 0:
             schedule.step(x)
-        elif rank == world - 1:
+        elif pp_rank == pp_world - 1:
             schedule.step(target=y, losses=losses)
         else:
             schedule.step()
         if opt is not None:
             opt.step()
             opt.zero_grad(set_to_none=False)
-        if e2e and rank == world - 1:
+        if e2e and pp_rank == pp_world - 1:
             return float(torch.stack(losses).float().mean().item())
         return None
 
@@ -372,8 +402,8 @@ def run_reference(a, rank, local_rank, world):
         if not a.no_e2e:
             step(True)
             ms_e2e = timed(lambda: step(True), a.steps)
-            e2e = {"value": B * S * a.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / a.steps,
-                   "h2d_bytes_per_step": int(2 * B * S * 8), "d2h_bytes_per_step": 4}
+            e2e = {"value": a.global_batch * S * a.steps / (ms_e2e / 1e3), "unit": "tokens/s", "ms_per_step": ms_e2e / a.steps,
+                   "h2d_bytes_per_step": int(dp * 2 * B * S * 8), "d2h_bytes_per_step": 4 * dp}
         loss_val = float(torch.stack(losses).float().mean().item()) if losses else -1.0
         loss_t = torch.tensor([loss_val], dtype=torch.float64, device=dev)
         dist.all_reduce(loss_t, op=dist.ReduceOp.MAX)
@@ -382,12 +412,13 @@ def run_reference(a, rank, local_rank, world):
             ms_step = ms_total / a.steps
             emit({
                 "metric": "tokens/sec (1F1B pipeline training step, max over ranks)" if a.schedule == "1F1B" else f"tokens/sec ({a.schedule})",
-                "value": B * S / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+                "value": a.global_batch * S / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic random tokens, random-init weights", "impl": "reference",
                 "config": config_dict(a, {"dim": margs.dim, "n_layers": margs.n_layers, "n_heads": margs.n_heads,
-                                          "vocab_size": margs.vocab_size}, f"pp{world}" + (f"xv{v}" if v > 1 else "")),
+                                          "vocab_size": margs.vocab_size}, f"pp{pp_world}" + (f"xdp{dp}" if dp > 1 else "") + (f"xv{v}" if v > 1 else "")),
                 "impl_notes": {"partition": "reference (helper:70-75)",
+                               "data_parallel": (None if dp == 1 else "stock torch composition: DistributedDataParallel around the helper's pruned stage module inside torch's PipelineStage (no_sync on all but the last micro-batch), NCCL all-reduce"),
                                "stack": "unmodified helper Transformer/manual_model_split + torch.distributed.pipelining + NCCL p2p + cuBLAS/SDPA, bf16 parameters, torch.optim.AdamW(fused=True) after schedule.step"},
                 "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": 0, "clocks": clocks, "e2e": e2e,
             })

@@ -21,7 +21,7 @@
 namespace ppb {
 
 #ifndef PPB_GEMM_PAIR_AUTO
-#define PPB_GEMM_PAIR_AUTO 0   // flipped to 1 once the CTA-pair kernels have a measured win on the flagship shapes
+#define PPB_GEMM_PAIR_AUTO 1   // measured (profiles/gemm_bench_r2.json): pairs win or tie whenever every SM pair gets a tile
 #endif
 constexpr int BM = 128;
 constexpr int BK = 64;
@@ -49,6 +49,19 @@ struct GemmParams {
   int rs_rows_per_rank;   // K11: C slab rows go to owner (row / rs_rows_per_rank)'s buffer (maps in dst_maps[])
 };
 
+// K12 (fused all-gather): what the copier warps move and how the GEMM tiles learn that a panel has landed.
+struct AgCopy {
+  const unsigned char* src[8];  // every rank's [rows_per_rank, K] bf16 shard (own buffer or a peer's mapped symmetric buffer)
+  unsigned char* full;          // local [M, K] gathered activations (an OUTPUT of the kernel; the A tiles of remote panels are read from here)
+  unsigned int* flags;          // one counter per 128-row panel of `full`, monotonically increasing across calls
+  unsigned int target;          // value every panel counter reaches once this call's chunks have landed
+  int chunks_per_panel;         // 16 KB chunks per 128-row panel (= K / 64)
+  int chunks_per_shard;
+  long long shard_bytes;
+  int tp, rank;
+};
+constexpr int AG_CHUNK = 16384;
+
 struct DstMaps {
   CUtensorMap m[8];  // fp32 accumulators of every data-parallel replica (own + peers), peer-mapped over NVLink
 };
@@ -56,23 +69,25 @@ struct DstMaps {
 // CG = CTAs per tile (cta_group): 1 = one CTA computes a 128 x BN tile; 2 = a CTA pair computes a 256 x BN tile, each
 // CTA staging its own 128 rows of A and HALF of the B tile (BN/2 rows), so the operand bytes per FLOP that each SM
 // pulls through L2 drop by a third at BN = 256.
-template <int BN, int CG = 1>
+template <int BN, int CG = 1, int EXTRA = 0>
 struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (STAGE_BYTES >= 49152) ? 4 : (STAGE_BYTES >= 32768 ? 6 : 8);
   static constexpr int EPI_BYTES = 4 * 2 * EPI_BUF_BYTES;
-  static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024;  // +1024 align slack
+  static constexpr int BAR_BYTES = 512;
+  static constexpr int FIT = (232448 - 1024 - BAR_BYTES - EPI_BYTES - EXTRA) / STAGE_BYTES;   // 227 KB per CTA
+  static constexpr int STAGES = FIT > 8 ? 8 : FIT;   // 4 / 6 / 8 at BN = 256 / 128 / 64 (pairs: 6 / 8)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + EXTRA + 1024;  // +1024 align slack
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
-template <int BN, bool A_MN, bool B_MN, int OUT, int CG = 1>
+template <int BN, bool A_MN, bool B_MN, int OUT, int CG = 1, bool AG2 = false>
 __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                           const GemmParams& p, const CUtensorMap* dst_maps,
-                                          const CUtensorMap* a_maps = nullptr) {
-  using Cfg = GemmCfg<BN, CG>;
+                                          const CUtensorMap* a_maps = nullptr, const AgCopy* agc = nullptr) {
+  using Cfg = GemmCfg<BN, CG, AG2 ? 2 * AG_CHUNK : 0>;
+  static_assert(!AG2 || CG == 1, "the fused all-gather keeps one CTA per tile");
   static_assert(CG == 1 || (OUT != 3 && BN >= 128), "CTA pairs: plain / accumulate outputs, BN >= 128");
   constexpr int TM = BM * CG;          // rows of the (pair) tile
   constexpr int BNH = BN / CG;         // B rows staged by one CTA
@@ -108,6 +123,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       mbar_init(tempty_bar(a), 4 * CG);   // epilogue warps of BOTH CTAs release the accumulator to the leader's issuer
     }
     for (int w = 0; w < 8; ++w) mbar_init(bar_base + 8u * (2 * STAGES + 5 + w), 1);  // fused all-reduce slab loads
+    for (int w = 0; w < 2; ++w) mbar_init(bar_base + 8u * (2 * STAGES + 13 + w), 1);  // fused all-gather chunk loads
     fence_mbar_init();
   }
   if (warp == 5) {
@@ -142,7 +158,20 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         // K12: the A rows of this tile come from the shard (possibly on a peer GPU) that owns them
         const CUtensorMap* ta = &tmA;
         int a_row = m0;
-        if (p.ag_rows_per_rank) {
+        if constexpr (AG2) {
+          // own-shard panels come straight from the own buffer; a remote panel is read from the local gathered copy
+          // once the copier warps (of whichever CTAs moved its chunks) have reported all of them
+          const int owner = m0 / p.ag_rows_per_rank;
+          if (owner == p.ag_rank) {
+            a_row = m0 - owner * p.ag_rows_per_rank;
+          } else {
+            ta = a_maps;
+            const unsigned int* flag = agc->flags + m0 / BM;
+            while (ld_acquire_gpu(flag) < agc->target) {
+            }
+            fence_proxy_async_all();
+          }
+        } else if (p.ag_rows_per_rank) {
           const int owner = m0 / p.ag_rows_per_rank;
           ta = a_maps + owner;
           a_row = m0 - owner * p.ag_rows_per_rank;
@@ -224,6 +253,45 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       }
     }
     __syncwarp();
+  } else if (warp == 6) {
+    // ======================= all-gather copier (K12) =======================
+    // Every CTA moves its share of the shards' 16 KB chunks: bulk copy (peer or own buffer) -> smem -> bulk copy into
+    // the local gathered buffer, then one release-increment of the panel's counter.  Remote shards go first, in the
+    // order the tiles will ask for them; the own shard (nobody waits for it) last.  Plain, non-multicast bulk loads.
+    if constexpr (AG2) {
+      if (lane == 0) {
+        const uint32_t cbar0 = bar_base + 8u * (2 * STAGES + 13);
+        const uint32_t cbuf0 = bar_base + Cfg::BAR_BYTES;
+        const int total = agc->tp * agc->chunks_per_shard;
+        const int panels_per_shard = agc->chunks_per_shard / agc->chunks_per_panel;
+        int nb = 0, prev_panel = -1;
+        uint32_t ph[2] = {0, 0};
+        for (int g = blockIdx.x; g < total; g += gridDim.x, ++nb) {
+          const int s_idx = g / agc->chunks_per_shard, c = g % agc->chunks_per_shard;
+          const int shard = (agc->rank + 1 + s_idx) % agc->tp;
+          const int b = nb & 1;
+          if (nb >= 2) tma_wait_group_read<1>();   // the store that used this buffer two chunks ago has read it out
+          mbar_expect_tx(cbar0 + 8u * b, AG_CHUNK);
+          bulk_load_1d(cbuf0 + b * AG_CHUNK, agc->src[shard] + (size_t)c * AG_CHUNK, AG_CHUNK, cbar0 + 8u * b);
+          mbar_wait(cbar0 + 8u * b, ph[b]);
+          ph[b] ^= 1;
+          bulk_store_1d(agc->full + (size_t)shard * agc->shard_bytes + (size_t)c * AG_CHUNK, cbuf0 + b * AG_CHUNK, AG_CHUNK);
+          tma_commit_group();
+          if (prev_panel >= 0) {                  // the PREVIOUS chunk's store is complete: publish it
+            tma_wait_group<1>();
+            fence_proxy_async_all();
+            red_release_gpu_add(agc->flags + prev_panel, 1u);
+          }
+          prev_panel = shard * panels_per_shard + c / agc->chunks_per_panel;
+        }
+        if (prev_panel >= 0) {
+          tma_wait_group<0>();
+          fence_proxy_async_all();
+          red_release_gpu_add(agc->flags + prev_panel, 1u);
+        }
+      }
+      __syncwarp();
+    }
   } else {
     // ======================= epilogue warps 0..3 =======================
     constexpr int CHUNK = (OUT == 0) ? 64 : 32;  // columns per staged 128-byte row (bf16: 64, fp32: 32)
@@ -456,6 +524,20 @@ gemm_tcgen05_ag_kernel(const __grid_constant__ DstMaps amaps, const __grid_const
   gemm_body<BN, false, B_MN, 0>(amaps.m[0], tmB, tmC, p, nullptr, amaps.m);
 }
 
+// K12, fused form: ONE kernel gathers and multiplies.  A seventh warp per CTA streams the shards (the peers' over
+// NVLink, each byte exactly once) into the local gathered buffer and publishes 128-row panels through release
+// counters; the TMA producer multiplies the own-shard panels first and picks up each remote panel as soon as its
+// counter says it has landed, so the transfer hides under the tensor-core work.  amaps.m[0] = own shard, m[1] = the
+// local gathered buffer.  The gathered activations stay behind for the weight-gradient GEMM of the backward pass.
+constexpr int GEMM_AG_THREADS = GEMM_THREADS + 32;
+template <int BN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_AG_THREADS, 1)
+gemm_tcgen05_agfused_kernel(const __grid_constant__ DstMaps amaps, const __grid_constant__ CUtensorMap tmB,
+                            const __grid_constant__ CUtensorMap tmC, const __grid_constant__ AgCopy agc,
+                            const GemmParams p) {
+  gemm_body<BN, false, B_MN, 0, 1, true>(amaps.m[0], tmB, tmC, p, nullptr, amaps.m + 1, &agc);
+}
+
 // K11: GEMM -> reduce-scatter.  Every rank computes its partial product (its K-slice of a
 // row-parallel layer) and the epilogue reduce-adds each 32-row slab directly into the fp32 buffer of the rank that
 // owns those rows (own slabs through L2, the others over NVLink).  After a barrier each rank holds the reduced
@@ -544,7 +626,14 @@ static void choose_config(int M, int N, int K, int out_mode, int force_bn, int f
   const int num_kb = (K + BK - 1) / BK;
   int bn = force_bn ? force_bn : (N > 128 ? 256 : (N > 64 ? 128 : 64));
   int cg = gemm_cg_setting();
-  if (cg == 0) cg = (kPairAuto && M > BM && bn >= 128) ? 2 : 1;
+  if (cg == 0) {
+    // Pairs only for the big problems (the vocabulary-sized LM-head GEMMs: many tiles or a very long K): measured
+    // +11..14 % there and +3 % at 8192^3 (profiles/gemm_bench_r2.json).  The layer-sized GEMMs tie in isolation and
+    // lose ~3 % inside the captured stage program (a cluster launch needs both SMs of a pair free at once, which
+    // delays the hand-over between back-to-back kernels), so they keep one CTA per tile.
+    const long long pair_tiles = (long long)((M + 2 * BM - 1) / (2 * BM)) * ((N + bn - 1) / bn);
+    cg = (kPairAuto && bn >= 128 && pair_tiles >= 32 && pair_tiles * num_kb >= 16384) ? 2 : 1;
+  }
   if (bn < 128 || cg_out == nullptr) cg = 1;
   if (cg_out) *cg_out = cg;
   const int sms = sm_count() / cg;   // tiles that run concurrently
@@ -815,6 +904,72 @@ extern "C" int ppb_gemm_allgather_bf16(void* const* a_shards, const void* B, voi
   else if (bn == 128) { if (b_mn_major) PPB_LAUNCH_AG(128, true) else PPB_LAUNCH_AG(128, false) }
   else { if (b_mn_major) PPB_LAUNCH_AG(64, true) else PPB_LAUNCH_AG(64, false) }
 #undef PPB_LAUNCH_AG
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
+// K12, fused form (see gemm_tcgen05_agfused_kernel).  `a_shards[r]` = rank r's [M/tp, K] bf16 shard, contiguous rows
+// (own buffer or peer-mapped symmetric memory); `full` = local [M, K] buffer that receives the gathered activations;
+// `flags` = M/128 counters (zero-filled once, then owned by this entry point); `target` = chunks_per_panel * (number
+// of calls made with these flags, this one included) -- ppb_gemm_allgather_fused_chunks_per_panel(K) gives the factor.
+extern "C" int ppb_gemm_allgather_fused_chunks_per_panel(int K) { return (K * 2 * BM) / AG_CHUNK; }
+
+extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, unsigned int* flags, unsigned int target,
+                                             const void* B, void* C, int M, int N, int K, long long ldb, long long ldc,
+                                             int tp, int rank, int b_mn_major, int epi, const void* bias, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "ppb_gemm_allgather_fused_bf16: bad tp/rank %d/%d", tp, rank);
+  PPB_REQUIRE(M > 0 && N > 0 && K > 0 && (M % tp) == 0 && ((M / tp) % BM) == 0,
+              "ppb_gemm_allgather_fused_bf16: rows per rank (M/tp = %d) must be a multiple of %d", M / (tp ? tp : 1), BM);
+  PPB_REQUIRE((K % 64) == 0, "ppb_gemm_allgather_fused_bf16: K must be a multiple of 64 (16 KB chunks of whole rows), got %d", K);
+  PPB_REQUIRE((ldb % 8) == 0 && (ldc % 8) == 0, "ppb_gemm_allgather_fused_bf16: misaligned leading dimension");
+  PPB_REQUIRE(full != nullptr && flags != nullptr && (reinterpret_cast<uintptr_t>(full) % 128) == 0,
+              "ppb_gemm_allgather_fused_bf16: need a 128-byte aligned gathered buffer and the panel counters");
+  PPB_REQUIRE(epi == PPB_EPI_NONE || epi == PPB_EPI_BIAS || epi == PPB_EPI_BIAS_RELU || epi == PPB_EPI_BIAS_GELU,
+              "ppb_gemm_allgather_fused_bf16: unsupported epilogue %d", epi);
+  PPB_REQUIRE(epi == PPB_EPI_NONE || bias != nullptr, "ppb_gemm_allgather_fused_bf16: epilogue needs a bias");
+  int bn, splits;
+  choose_config(M, N, K, PPB_OUT_BF16, 0, 0, &bn, &splits);
+  const int rows = M / tp;
+  DstMaps am;
+  CUtensorMap tmB, tmC;
+  bool ok = make_tmap_2d(&am.m[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, a_shards[rank], (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, BK, BM) &&
+            make_tmap_2d(&am.m[1], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, full, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BK, BM);
+  for (int r = 2; ok && r < 8; ++r) am.m[r] = am.m[0];
+  ok = ok && (b_mn_major ? make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK)
+                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn));
+  ok = ok && make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 2, 64, 32);
+  if (!ok) return -3;
+  GemmParams p;
+  fill_plain_params(p, M, N, K, bn, 1);
+  p.epi = epi;
+  p.bias = reinterpret_cast<const bf16*>(bias);
+  p.ag_rows_per_rank = rows;
+  p.ag_rank = rank;
+  AgCopy agc;
+  for (int r = 0; r < 8; ++r) agc.src[r] = reinterpret_cast<const unsigned char*>(a_shards[r < tp ? r : 0]);
+  agc.full = reinterpret_cast<unsigned char*>(full);
+  agc.flags = flags;
+  agc.target = target;
+  agc.chunks_per_panel = ppb_gemm_allgather_fused_chunks_per_panel(K);
+  agc.shard_bytes = (long long)rows * K * 2;
+  agc.chunks_per_shard = (int)(agc.shard_bytes / AG_CHUNK);
+  agc.tp = tp;
+  agc.rank = rank;
+  // every CTA must be resident at once (tiles wait for chunks that other CTAs move): at most one CTA per SM
+  const long long total = (long long)p.tiles_m * p.tiles_n;
+  const int grid = (int)(total < sm_count() ? total : sm_count());
+#define PPB_LAUNCH_AGF(BN_, BMN_)                                                                                   \
+  {                                                                                                                 \
+    using CfgF = GemmCfg<BN_, 1, 2 * AG_CHUNK>;                                                                     \
+    auto kfn = gemm_tcgen05_agfused_kernel<BN_, BMN_>;                                                              \
+    PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, CfgF::SMEM_BYTES));          \
+    kfn<<<grid, GEMM_AG_THREADS, CfgF::SMEM_BYTES, stream>>>(am, tmB, tmC, agc, p);                                 \
+  }
+  if (bn == 256) { if (b_mn_major) PPB_LAUNCH_AGF(256, true) else PPB_LAUNCH_AGF(256, false) }
+  else if (bn == 128) { if (b_mn_major) PPB_LAUNCH_AGF(128, true) else PPB_LAUNCH_AGF(128, false) }
+  else { if (b_mn_major) PPB_LAUNCH_AGF(64, true) else PPB_LAUNCH_AGF(64, false) }
+#undef PPB_LAUNCH_AGF
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }

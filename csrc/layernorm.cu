@@ -4,10 +4,11 @@
 //   backward:  dy = dy0 (+ dy1 + dy2)   (the fan-in of the post-LN residual graph is summed on load)
 //              dz = norm'(dy) ;  da = dropout'(dz) ;  dgamma += .., dbeta += ..
 //
-// One warp owns one row; a row lives entirely in registers (d <= 2048), so every tensor is read exactly
-// once and written exactly once.  The dropout mask is regenerated from (seed, element index) and is never
-// stored.  dgamma/dbeta partials are reduced warp -> CTA (smem tree) -> scratch, and a second small kernel folds the
-// scratch, column slab by column slab, into the fp32 gradient accumulators (which persist across micro-batches).
+// A row lives entirely in registers (d <= 2048), so every tensor is read exactly once and written exactly once
+// (forward: one warp per row; backward: a group of d/8 threads per row, each thread owning 8 columns of every row
+// its group visits).  The dropout mask is regenerated from (seed, element index) and is never stored.
+// dgamma/dbeta partials are reduced thread -> CTA (smem) -> scratch, and a second small kernel folds the scratch,
+// column slab by column slab, into the fp32 gradient accumulators (which persist across micro-batches).
 //
 // Replaces aten.add + bernoulli_/div_/mul + native_layer_norm(_backward) of the reference's op stream
 // (torch nn.TransformerDecoderLayer post-LN blocks used at
@@ -40,7 +41,7 @@ struct LnFwdParams {
 };
 
 template <int MAXV>
-__global__ void __launch_bounds__(LN_THREADS) ln_fwd_kernel(const LnFwdParams p) {
+__global__ void __launch_bounds__(LN_THREADS, (MAXV <= 4) ? 4 : 1) ln_fwd_kernel(const LnFwdParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nchunks = p.d >> 3;
   const float inv_d = 1.f / float(p.d);
@@ -141,111 +142,161 @@ struct LnBwdParams {
   int rms;
 };
 
-template <int MAXV>
-__global__ void __launch_bounds__(LN_THREADS) ln_bwd_kernel(const LnBwdParams p) {
-  extern __shared__ float red_smem[];  // [LN_WARPS][2][d] per-warp partial accumulators
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+// Backward, "column-owner" layout: a group of TPR threads works on one row at a time and thread t of the group owns
+// the 8 columns [8t, 8t+8) of EVERY row its group visits, so the dgamma / dbeta partial sums live in 16 registers per
+// thread for the whole kernel (no per-warp copies of the full row width).  Rows are processed in batches of RB: all
+// 16-byte loads of a batch (up to 4 tensors x RB rows per thread) are in flight together, then ONE group-wide
+// reduction delivers the two row statistics of all RB rows.  256 threads x 2 CTAs per SM keep > 100 KB of loads in
+// flight per SM, which is what a bandwidth-bound kernel needs on HBM3e.
+template <int TPR>
+__global__ void __launch_bounds__(LN_THREADS, 2) ln_bwd_kernel(const LnBwdParams p) {
+  constexpr int G = LN_THREADS / TPR;   // row groups per CTA
+  constexpr int WPR = TPR / 32;         // warps per row group
+  constexpr int RB = 4;                 // rows per batch
+  extern __shared__ float red_smem[];   // [G][2][d] CTA-level partials of dgamma / dbeta
+  __shared__ float stat[2][G][WPR][2 * RB];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int grp = tid / TPR, t = tid % TPR, wig = t >> 5;
   const int nchunks = p.d >> 3;
+  const bool active = t < nchunks;
   const float inv_d = 1.f / float(p.d);
   const unsigned long long seed_eff = p.seed + ((p.thresh && p.seed_off) ? *p.seed_off : 0ull);
-  float dg[MAXV][8], db[MAXV][8];
+  const int rows_per_cta = (p.T + gridDim.x - 1) / gridDim.x;
+  const int r_begin = blockIdx.x * rows_per_cta;
+  const int r_end = min(p.T, r_begin + rows_per_cta);
+  const int n_iter = (rows_per_cta + G * RB - 1) / (G * RB);   // uniform over the CTA (the groups meet at named barriers)
+
+  float gam[8], dg[8], db[8];
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i)
+  for (int j = 0; j < 8; ++j) gam[j] = dg[j] = db[j] = 0.f;
+  if (active) {
+    const uint4 g4 = *reinterpret_cast<const uint4*>(p.gamma + t * 8);
+    const uint32_t gw[4] = {g4.x, g4.y, g4.z, g4.w};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) dg[i][j] = db[i][j] = 0.f;
-  for (int row = blockIdx.x * LN_WARPS + warp; row < p.T; row += gridDim.x * LN_WARPS) {
-    const long long rbase = (long long)row * p.d;
-    const DropoutStream dstr(seed_eff, (unsigned long long)rbase >> 1);
-    const float mean = p.rms ? 0.f : p.mean[row];
-    const float rstd = p.rstd[row];
-    float xh[MAXV][8], gdy[MAXV][8];
-    float c1 = 0.f, c2 = 0.f;
-#pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nchunks) {
-        const uint4 d4 = *reinterpret_cast<const uint4*>(p.dy0 + rbase + c * 8);
-        uint4 e4 = make_uint4(0, 0, 0, 0), f4 = make_uint4(0, 0, 0, 0);
-        if (p.dy1) e4 = *reinterpret_cast<const uint4*>(p.dy1 + rbase + c * 8);
-        if (p.dy2) f4 = *reinterpret_cast<const uint4*>(p.dy2 + rbase + c * 8);
-        const uint4 z4 = *reinterpret_cast<const uint4*>(p.z + rbase + c * 8);
-        const uint4 g4 = *reinterpret_cast<const uint4*>(p.gamma + c * 8);
-        const uint32_t dw[4] = {d4.x, d4.y, d4.z, d4.w};
-        const uint32_t ew[4] = {e4.x, e4.y, e4.z, e4.w};
-        const uint32_t fw[4] = {f4.x, f4.y, f4.z, f4.w};
-        const uint32_t zw[4] = {z4.x, z4.y, z4.z, z4.w};
-        const uint32_t gw[4] = {g4.x, g4.y, g4.z, g4.w};
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float2 d2 = unpack_bf16(dw[q]), e2 = unpack_bf16(ew[q]), f2 = unpack_bf16(fw[q]);
-          const float2 z2 = unpack_bf16(zw[q]), g2 = unpack_bf16(gw[q]);
-          const float dyx = d2.x + e2.x + f2.x, dyy = d2.y + e2.y + f2.y;
-          const float xx = (z2.x - mean) * rstd, xy = (z2.y - mean) * rstd;
-          xh[i][2 * q] = xx;
-          xh[i][2 * q + 1] = xy;
-          gdy[i][2 * q] = dyx * g2.x;
-          gdy[i][2 * q + 1] = dyy * g2.y;
-          dg[i][2 * q] += dyx * xx;
-          dg[i][2 * q + 1] += dyy * xy;
-          db[i][2 * q] += dyx;
-          db[i][2 * q + 1] += dyy;
-          c1 += gdy[i][2 * q] + gdy[i][2 * q + 1];
-          c2 += gdy[i][2 * q] * xx + gdy[i][2 * q + 1] * xy;
-        }
-      }
-    }
-    c1 = p.rms ? 0.f : warp_sum(c1) * inv_d;
-    c2 = warp_sum(c2) * inv_d;
-#pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nchunks) {
-        uint32_t zo[4], ao[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float gx = rstd * (gdy[i][2 * q] - c1 - xh[i][2 * q] * c2);
-          const float gy = rstd * (gdy[i][2 * q + 1] - c1 - xh[i][2 * q + 1] * c2);
-          zo[q] = pack_bf16(gx, gy);
-          if (p.da) {
-            float ax = gx, ay = gy;
-            if (p.thresh) {
-              const DropPair h = dstr.bits(c * 4 + q);
-              ax = (h.a >= p.thresh) ? gx * p.scale : 0.f;
-              ay = (h.b >= p.thresh) ? gy * p.scale : 0.f;
-            }
-            ao[q] = pack_bf16(ax, ay);
-          }
-        }
-        *reinterpret_cast<uint4*>(p.dz + rbase + c * 8) = make_uint4(zo[0], zo[1], zo[2], zo[3]);
-        if (p.da) *reinterpret_cast<uint4*>(p.da + rbase + c * 8) = make_uint4(ao[0], ao[1], ao[2], ao[3]);
-      }
+    for (int q = 0; q < 4; ++q) {
+      const float2 g2 = unpack_bf16(gw[q]);
+      gam[2 * q] = g2.x;
+      gam[2 * q + 1] = g2.y;
     }
   }
 
-  // warp partials -> smem [warp][2][d] -> CTA partial (plain adds, no atomics) -> scratch[cta][2][d]
-  float* wsm = red_smem + (size_t)warp * 2 * p.d;
+  for (int it = 0; it < n_iter; ++it) {
+    const int row0 = r_begin + (it * G + grp) * RB;
+    float xh[RB][8], gdy[RB][8], cs[2 * RB], rs[RB];
+    // ---- issue every load of the batch before using any of them ----
+    uint4 d4[RB], e4[RB], f4[RB], z4[RB];
+    float mu[RB];
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = lane + 32 * i;
-    if (c < nchunks) {
-      *reinterpret_cast<float4*>(wsm + c * 8) = make_float4(dg[i][0], dg[i][1], dg[i][2], dg[i][3]);
-      *reinterpret_cast<float4*>(wsm + c * 8 + 4) = make_float4(dg[i][4], dg[i][5], dg[i][6], dg[i][7]);
-      *reinterpret_cast<float4*>(wsm + p.d + c * 8) = make_float4(db[i][0], db[i][1], db[i][2], db[i][3]);
-      *reinterpret_cast<float4*>(wsm + p.d + c * 8 + 4) = make_float4(db[i][4], db[i][5], db[i][6], db[i][7]);
+    for (int r = 0; r < RB; ++r) {
+      const int row = row0 + r;
+      const bool ok = active && row < r_end;
+      d4[r] = e4[r] = f4[r] = z4[r] = make_uint4(0, 0, 0, 0);
+      mu[r] = 0.f;
+      rs[r] = 0.f;
+      if (ok) {
+        const long long off = (long long)row * p.d + t * 8;
+        d4[r] = *reinterpret_cast<const uint4*>(p.dy0 + off);
+        if (p.dy1) e4[r] = *reinterpret_cast<const uint4*>(p.dy1 + off);
+        if (p.dy2) f4[r] = *reinterpret_cast<const uint4*>(p.dy2 + off);
+        z4[r] = *reinterpret_cast<const uint4*>(p.z + off);
+        if (!p.rms) mu[r] = __ldg(p.mean + row);
+        rs[r] = __ldg(p.rstd + row);
+      }
     }
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      const uint32_t dw[4] = {d4[r].x, d4[r].y, d4[r].z, d4[r].w};
+      const uint32_t ew[4] = {e4[r].x, e4[r].y, e4[r].z, e4[r].w};
+      const uint32_t fw[4] = {f4[r].x, f4[r].y, f4[r].z, f4[r].w};
+      const uint32_t zw[4] = {z4[r].x, z4[r].y, z4[r].z, z4[r].w};
+      float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float2 d2 = unpack_bf16(dw[q]), e2 = unpack_bf16(ew[q]), f2 = unpack_bf16(fw[q]);
+        const float2 z2 = unpack_bf16(zw[q]);
+        const float dyx = d2.x + e2.x + f2.x, dyy = d2.y + e2.y + f2.y;
+        // rs == 0 on rows / columns this thread does not own, which zeroes every contribution below
+        const float xx = (z2.x - mu[r]) * rs[r], xy = (z2.y - mu[r]) * rs[r];
+        xh[r][2 * q] = xx;
+        xh[r][2 * q + 1] = xy;
+        gdy[r][2 * q] = dyx * gam[2 * q];
+        gdy[r][2 * q + 1] = dyy * gam[2 * q + 1];
+        dg[2 * q] += dyx * xx;
+        dg[2 * q + 1] += dyy * xy;
+        db[2 * q] += dyx;
+        db[2 * q + 1] += dyy;
+        c1 += gdy[r][2 * q] + gdy[r][2 * q + 1];
+        c2 += gdy[r][2 * q] * xx + gdy[r][2 * q + 1] * xy;
+      }
+      cs[2 * r] = c1;
+      cs[2 * r + 1] = c2;
+    }
+    // ---- the two statistics of all RB rows: warp reduce, then across the group's warps ----
+#pragma unroll
+    for (int i = 0; i < 2 * RB; ++i) cs[i] = warp_sum(cs[i]);
+    if constexpr (WPR > 1) {
+      float* my = stat[it & 1][grp][wig];
+      if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < 2 * RB; ++i) my[i] = cs[i];
+      }
+      named_bar_sync(1 + grp, TPR);
+#pragma unroll
+      for (int i = 0; i < 2 * RB; ++i) {
+        float a = 0.f;
+#pragma unroll
+        for (int w = 0; w < WPR; ++w) a += stat[it & 1][grp][w][i];
+        cs[i] = a;
+      }
+    }
+    // ---- dz (and da) ----
+#pragma unroll
+    for (int r = 0; r < RB; ++r) {
+      const int row = row0 + r;
+      if (!(active && row < r_end)) continue;
+      const float c1 = p.rms ? 0.f : cs[2 * r] * inv_d;
+      const float c2 = cs[2 * r + 1] * inv_d;
+      const long long off = (long long)row * p.d + t * 8;
+      const DropoutStream dstr(seed_eff, (unsigned long long)off >> 1);  // d and 8t are even: a pair boundary
+      uint32_t zo[4], ao[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float gx = rs[r] * (gdy[r][2 * q] - c1 - xh[r][2 * q] * c2);
+        const float gy = rs[r] * (gdy[r][2 * q + 1] - c1 - xh[r][2 * q + 1] * c2);
+        zo[q] = pack_bf16(gx, gy);
+        float ax = gx, ay = gy;
+        if (p.da && p.thresh) {
+          const DropPair h = dstr.bits(q);
+          ax = (h.a >= p.thresh) ? gx * p.scale : 0.f;
+          ay = (h.b >= p.thresh) ? gy * p.scale : 0.f;
+        }
+        ao[q] = pack_bf16(ax, ay);
+      }
+      *reinterpret_cast<uint4*>(p.dz + off) = make_uint4(zo[0], zo[1], zo[2], zo[3]);
+      if (p.da) *reinterpret_cast<uint4*>(p.da + off) = make_uint4(ao[0], ao[1], ao[2], ao[3]);
+    }
+  }
+
+  // group partials -> smem [G][2][d] -> CTA partial (plain adds, no atomics) -> scratch[cta][2][d]
+  if (active) {
+    float* gsm = red_smem + (size_t)grp * 2 * p.d + t * 8;
+    *reinterpret_cast<float4*>(gsm) = make_float4(dg[0], dg[1], dg[2], dg[3]);
+    *reinterpret_cast<float4*>(gsm + 4) = make_float4(dg[4], dg[5], dg[6], dg[7]);
+    *reinterpret_cast<float4*>(gsm + p.d) = make_float4(db[0], db[1], db[2], db[3]);
+    *reinterpret_cast<float4*>(gsm + p.d + 4) = make_float4(db[4], db[5], db[6], db[7]);
   }
   __syncthreads();
   float* parts = p.scratch + 64;  // the first 256 bytes of the scratch are a reserved header
   float* part = parts + (size_t)blockIdx.x * 2 * p.d;
-  for (int i = threadIdx.x * 4; i < 2 * p.d; i += LN_THREADS * 4) {
+  for (int i = tid * 4; i < 2 * p.d; i += LN_THREADS * 4) {
     float4 acc = *reinterpret_cast<const float4*>(red_smem + i);
 #pragma unroll
-    for (int w = 1; w < LN_WARPS; ++w) {
-      const float4 t = *reinterpret_cast<const float4*>(red_smem + (size_t)w * 2 * p.d + i);
-      acc.x += t.x;
-      acc.y += t.y;
-      acc.z += t.z;
-      acc.w += t.w;
+    for (int g = 1; g < G; ++g) {
+      const float4 v = *reinterpret_cast<const float4*>(red_smem + (size_t)g * 2 * p.d + i);
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
     }
     *reinterpret_cast<float4*>(part + i) = acc;
   }
@@ -416,7 +467,10 @@ extern "C" int ppb_add_dropout_norm_fwd(const void* resid, const void* a, const 
   p.thresh = (a && dropout_p > 0.f) ? dropout_thr32(dropout_p) : 0u;
   p.scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.rms = rms;
-  const int grid = ln_grid(T);
+  // one row per warp with every row resident at once (4 CTAs x 8 warps per SM at d <= 1024): the kernel is one wave of
+  // 16-byte loads, bandwidth- rather than latency-bound; very large T falls back to a grid-stride loop
+  const int want = (T + LN_WARPS - 1) / LN_WARPS, cap = sm_count() * 16;
+  const int grid = want < cap ? want : cap;
   const int nchunks = d / 8;
   if (nchunks <= 32 * 4)
     ln_fwd_kernel<4><<<grid, LN_THREADS, 0, stream>>>(p);
@@ -438,17 +492,17 @@ extern "C" long long ppb_norm_bwd_scratch_bytes(int T, int d) {
 
 namespace ppb {
 static int launch_ln_bwd(const LnBwdParams& p, int grid, cudaStream_t stream) {
-  const int nchunks = p.d / 8;
-  const size_t smem = (size_t)LN_WARPS * 2 * p.d * sizeof(float);  // <= 128 KB at d = 2048
-  if (nchunks <= 32 * 4) {
-    auto k = ln_bwd_kernel<4>;
-    if (smem > 48 * 1024) PPB_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, LN_THREADS, smem, stream>>>(p);
-  } else {
-    auto k = ln_bwd_kernel<8>;
-    if (smem > 48 * 1024) PPB_CUDA_OK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k<<<grid, LN_THREADS, smem, stream>>>(p);
+  const int nchunks = p.d / 8;   // <= 256 (d <= 2048)
+#define PPB_LN_BWD(TPR_)                                                                        \
+  {                                                                                             \
+    const size_t smem = (size_t)(LN_THREADS / TPR_) * 2 * p.d * sizeof(float); /* <= 32 KB */   \
+    ln_bwd_kernel<TPR_><<<grid, LN_THREADS, smem, stream>>>(p);                                 \
   }
+  if (nchunks <= 32) PPB_LN_BWD(32)
+  else if (nchunks <= 64) PPB_LN_BWD(64)
+  else if (nchunks <= 128) PPB_LN_BWD(128)
+  else PPB_LN_BWD(256)
+#undef PPB_LN_BWD
   PPB_CUDA_OK(cudaGetLastError());
   ln_bwd_finalize_kernel<<<(2 * p.d + 31) / 32, 256, 0, stream>>>(p.scratch + 64, grid, p.d, p.dgamma, p.dbeta);
   PPB_CUDA_OK(cudaGetLastError());

@@ -339,7 +339,7 @@ class PipelineStage:
         self._set_mb_seed(mb)
         if g is None:
             g = {"in": inp.clone(), "tgt": None if target is None else target.clone(), "F": torch.cuda.CUDAGraph(),
-                 "B": None, "dout": None, "din_B": None, "din_I": None, "sends": {},
+                 "B": None, "dout": None, "din": None, "din_B": None, "din_I": None, "sends": {},
                  # one private pool per slot: within a slot the replay order F -> B (or F -> I -> W) is the capture
                  # order, so its graphs may share scratch; across slots live ranges interleave differently from the
                  # capture order (slot 1's stash is live while slot 0's backward replays), so nothing is shared
@@ -387,6 +387,18 @@ class PipelineStage:
             g["dout"].copy_(dout.reshape(g["dout"].shape))
         return g["dout"]
 
+    def _slot_din(self, g: dict) -> Optional[torch.Tensor]:
+        """The slot's static input-gradient buffer, allocated OUTSIDE the graph pool.  A tensor allocated while the
+        backward graph is captured may reuse pool memory that the slot's forward graph uses for temporaries; the
+        consumer of the gradient (an NCCL send still in flight, or a local virtual stage that runs later) would then
+        race with the slot's next forward replay.  The captured backward ends with one copy into this buffer."""
+        if self.is_first:
+            return None
+        if g.get("din") is None:
+            b, S = g["shape"]
+            g["din"] = torch.empty((self.in_rows * b * S, self.args.dim), dtype=self.dtype, device=self.device)
+        return g["din"]
+
     def backward_graphed(self, mb: int, dout: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         from ..ops import _lib as L
         slot = mb % self.nslots
@@ -398,11 +410,13 @@ class PipelineStage:
         if g["B"] is None:
             g["B"] = torch.cuda.CUDAGraph()
             st, ctx = g["stash"], g["ctx"]
+            din_static = self._slot_din(g)
             n0 = L.launches()
             with torch.cuda.graph(g["B"], pool=g["pool"]):
                 with torch.no_grad():
                     douts = [st["dlogits"]] if sd is None else [sd]
-                    g["din_B"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                    din = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                    g["din_B"] = None if din is None else din_static.copy_(din.reshape(din_static.shape))
             g["nB"] = L.launches() - n0
         else:
             L.count_launch(g["nB"])
@@ -422,13 +436,15 @@ class PipelineStage:
         if g.get("I") is None:
             g["I"] = torch.cuda.CUDAGraph()
             st, ctx = g["stash"], g["ctx"]
+            din_static = self._slot_din(g)
             n0 = L.launches()
             self.sink.deferred = []
             try:
                 with torch.cuda.graph(g["I"], pool=g["pool"]):
                     with torch.no_grad():
                         douts = [st["dlogits"]] if sd is None else [sd]
-                        g["din_I"] = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                        din = stage_backward(self.submod, douts, ctx, st, self.sink, need_input_grad=not self.is_first)
+                        g["din_I"] = None if din is None else din_static.copy_(din.reshape(din_static.shape))
             finally:
                 g["wlist"], self.sink.deferred = self.sink.deferred, None
             g["nI"] = L.launches() - n0

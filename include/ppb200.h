@@ -73,6 +73,17 @@ int ppb_gemm_allreduce_bf16(const void* A, const void* B, float* accum, void* co
 int ppb_gemm_allgather_bf16(void* const* a_shards, const void* B, void* C, int M, int N, int K, long long lda,
                             long long ldb, long long ldc, int tp, int rank, int b_mn_major, int epi, const void* bias,
                             void* stream);
+/* K12, fused form: ONE kernel gathers and multiplies.  A copier warp per CTA streams every shard (the peers' over
+ * NVLink with plain bulk copies, each byte once) into the local gathered buffer `full` [M, K] and publishes 128-row
+ * panels through release counters in `flags` (M/128 counters, zero-filled once by the caller, then never touched by
+ * anyone else); the GEMM tiles multiply the own-shard panels first and each remote panel as soon as it has landed.
+ * Shards must be contiguous ([M/tp, K], K % 64 == 0).  `target` = chunks_per_panel(K) * (calls made with these flags
+ * so far, this one included).  `full` keeps the gathered activations (the backward weight-gradient GEMM wants them).
+ * Every CTA of the launch must be co-resident (<= one per SM): run it on a stream that has the GPU to itself. */
+int ppb_gemm_allgather_fused_chunks_per_panel(int K);
+int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, unsigned int* flags, unsigned int target, const void* B,
+                                  void* C, int M, int N, int K, long long ldb, long long ldc, int tp, int rank,
+                                  int b_mn_major, int epi, const void* bias, void* stream);
 /* ---- K11: GEMM -> reduce-scatter (row-parallel layer under tensor parallelism) -----------------------------------
  * dst_shards[o][M/tp, N] (fp32, zeroed by the caller) += rows [o*M/tp, (o+1)*M/tp) of A[M,K] * op(B)^T, for every
  * owner o: each 32-row slab of the partial product is TMA-reduce-added into its owner's buffer (local or over
