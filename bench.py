@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fused-check", action="store_true",
+                    help="skip the K10/K11/K12 parity + roofline check that multi-GPU runs append (ranks 0-1, after the timed regions)")
     ap.add_argument("--trace", default=None, help="write a chrome trace of the measured timeline here")
     ap.add_argument("--small", action="store_true", help="tiny config for smoke tests")
     return ap.parse_args()
@@ -217,6 +219,19 @@ def run_ours(a, rank, local_rank, world):
             write_chrome_trace(evs, a.trace)
     peak_mem = max_over_ranks(torch.cuda.max_memory_allocated(dev) / 2**30, dev)
     loss_t = torch.tensor([loss_val if loss_val is not None else -1.0], dtype=torch.float64, device=dev)
+    # The fused compute+collective kernels (K10 wgrad+all-reduce, K11 GEMM->reduce-scatter, K12 all-gather->GEMM) are not
+    # on the pipeline-only headline path, so every multi-GPU run appends their parity + roofline check over the real
+    # NVLink peers (ranks 0 and 1, outside every timed region): the evidence travels with the driver's own records.
+    fused_paths = None
+    if world > 1 and not a.no_fused_check and not a.small:
+        pair = dist.new_group([0, 1])
+        if rank < 2:
+            try:
+                from ppb200.utils import fused_check
+                fused_paths = fused_check.run(pair, dev)
+            except Exception as e:  # noqa: BLE001
+                fused_paths = {"error": f"{type(e).__name__}: {e}"[:300]}
+        dist.barrier()
     summ = {k: round(v, 3) for k, v in sched.summary().items()}
     summ["layers"] = [[f"{k}:{getattr(l, 'part', 'full')}" if getattr(l, 'part', 'full') != 'full' else k
                        for k, l in st.submod.layers.items()] for st in stages]
@@ -245,6 +260,7 @@ def run_ours(a, rank, local_rank, world):
             "bubble_fraction_theory": sched.theory_bubble,
             "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
             "model_tflops_per_gpu": margs.flops_per_token(S) * tokens / (ms_step / 1e3) / 1e12 / world,
+            "fused_paths": fused_paths,
             "per_rank": per_rank,
         })
     if world > 1:

@@ -264,6 +264,32 @@ extern "C" int ppb_gelu_fwd(const void* x, void* y, long long n, void* stream_) 
   return 0;
 }
 
+// y[t, c] = bf16(x[t, c] + bias[c]): finishes a reduce-scatter (fp32 partial sums -> activation dtype, + the replicated
+// bias of a row-parallel layer) in one pass; bias may be null.  4 columns per thread.
+__global__ void __launch_bounds__(256) bias_cast_f32_bf16_kernel(const float* __restrict__ x, const bf16* __restrict__ bias,
+                                                                 bf16* __restrict__ y, long long n4, int d4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 v = reinterpret_cast<const float4*>(x)[i];
+    if (bias) {
+      const uint2 b = reinterpret_cast<const uint2*>(bias)[i % d4];
+      const float2 b0 = unpack_bf16(b.x), b1 = unpack_bf16(b.y);
+      v.x += b0.x;
+      v.y += b0.y;
+      v.z += b1.x;
+      v.w += b1.y;
+    }
+    reinterpret_cast<uint2*>(y)[i] = make_uint2(pack_bf16(v.x, v.y), pack_bf16(v.z, v.w));
+  }
+}
+
+extern "C" int ppb_bias_cast_f32_to_bf16(const float* x, const void* bias, void* y, long long T, int d, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(T > 0 && d > 0 && (d % 4) == 0, "ppb_bias_cast_f32_to_bf16: need d %% 4 == 0 (got %d)", d);
+  bias_cast_f32_bf16_kernel<<<ew_grid(T * d / 4), 256, 0, stream>>>(x, (const bf16*)bias, (bf16*)y, T * d / 4, d / 4);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
+
 extern "C" int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (n <= 0) return 0;

@@ -916,7 +916,8 @@ extern "C" int ppb_gemm_allgather_fused_chunks_per_panel(int K) { return (K * 2 
 
 extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, unsigned int* flags, unsigned int target,
                                              const void* B, void* C, int M, int N, int K, long long ldb, long long ldc,
-                                             int tp, int rank, int b_mn_major, int epi, const void* bias, void* stream_) {
+                                             int tp, int rank, int b_mn_major, int epi, const void* bias, const void* aux,
+                                             long long ld_aux, float alpha, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   PPB_REQUIRE(tp >= 1 && tp <= 8 && rank >= 0 && rank < tp, "ppb_gemm_allgather_fused_bf16: bad tp/rank %d/%d", tp, rank);
   PPB_REQUIRE(M > 0 && N > 0 && K > 0 && (M % tp) == 0 && ((M / tp) % BM) == 0,
@@ -925,9 +926,13 @@ extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, 
   PPB_REQUIRE((ldb % 8) == 0 && (ldc % 8) == 0, "ppb_gemm_allgather_fused_bf16: misaligned leading dimension");
   PPB_REQUIRE(full != nullptr && flags != nullptr && (reinterpret_cast<uintptr_t>(full) % 128) == 0,
               "ppb_gemm_allgather_fused_bf16: need a 128-byte aligned gathered buffer and the panel counters");
-  PPB_REQUIRE(epi == PPB_EPI_NONE || epi == PPB_EPI_BIAS || epi == PPB_EPI_BIAS_RELU || epi == PPB_EPI_BIAS_GELU,
+  PPB_REQUIRE(epi == PPB_EPI_NONE || epi == PPB_EPI_BIAS || epi == PPB_EPI_BIAS_RELU || epi == PPB_EPI_BIAS_GELU ||
+                  epi == PPB_EPI_MASK_POS || epi == PPB_EPI_GELU_BWD,
               "ppb_gemm_allgather_fused_bf16: unsupported epilogue %d", epi);
-  PPB_REQUIRE(epi == PPB_EPI_NONE || bias != nullptr, "ppb_gemm_allgather_fused_bf16: epilogue needs a bias");
+  if (epi == PPB_EPI_MASK_POS || epi == PPB_EPI_GELU_BWD)
+    PPB_REQUIRE(aux != nullptr && (ld_aux % 8) == 0, "ppb_gemm_allgather_fused_bf16: epilogue %d needs an aux matrix with ld %% 8 == 0", epi);
+  else
+    PPB_REQUIRE(epi == PPB_EPI_NONE || bias != nullptr, "ppb_gemm_allgather_fused_bf16: epilogue needs a bias");
   int bn, splits;
   choose_config(M, N, K, PPB_OUT_BF16, 0, 0, &bn, &splits);
   const int rows = M / tp;
@@ -944,6 +949,9 @@ extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, 
   fill_plain_params(p, M, N, K, bn, 1);
   p.epi = epi;
   p.bias = reinterpret_cast<const bf16*>(bias);
+  p.aux = reinterpret_cast<const bf16*>(aux);
+  p.ld_aux = ld_aux;
+  p.alpha = alpha;
   p.ag_rows_per_rank = rows;
   p.ag_rank = rank;
   AgCopy agc;

@@ -112,18 +112,9 @@ def merge_tp_shards(shards: Sequence[Dict[str, torch.Tensor]], n_heads: int, swi
     return out
 
 
-def _rs_finish(y32: torch.Tensor, bias, dtype) -> torch.Tensor:
-    """fp32 reduce-scatter result (+ replicated bias) -> activation dtype."""
-    if bias is not None:
-        return (y32 + bias.float()).to(dtype)
-    return y32.to(dtype)
-
-
-def _gelu_bwd(dh: torch.Tensor, hpre: torch.Tensor) -> torch.Tensor:
-    a = hpre.float()
-    cdf = 0.5 * (1.0 + torch.erf(a * 0.70710678118))
-    pdf = 0.3989422804 * torch.exp(-0.5 * a * a)
-    return (dh.float() * (cdf + a * pdf)).to(dh.dtype)
+def _rs_finish(tp, y32: torch.Tensor, bias, dtype) -> torch.Tensor:
+    """fp32 reduce-scatter result (+ replicated bias) -> activation dtype (one fused pass on CUDA)."""
+    return tp.rs_finish(y32, bias, dtype)
 
 
 def _tp_seed(ctx, layer_id: int, site: int) -> int:
@@ -146,7 +137,7 @@ def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> t
         F.rope_(qkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta)
     o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, p,
                                _tp_seed(ctx, layer_id, SITE_ATTN1))
-    a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x_in.dtype)
+    a1 = _rs_finish(tp, tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x_in.dtype)
     z3, y3, mean3, rstd3 = F.add_dropout_norm_fwd(x_in, a1, L.norm3.weight, L.norm3.bias, eps, p,
                                                   _tp_seed(ctx, layer_id, SITE_RES1), rms)
     if a.activation == "relu":
@@ -159,7 +150,7 @@ def tp_prenorm_forward(L, layer_id: int, x_in: torch.Tensor, ctx, st: dict) -> t
         hpre, y3_full = tp.ag_linear(y3, L.linear1.weight, L.linear1.bias)
         h = F.gelu_fwd(hpre)
         st["hpre"] = hpre
-    a3 = _rs_finish(tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x_in.dtype)
+    a3 = _rs_finish(tp, tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x_in.dtype)
     x_out = F.add_dropout_fwd(z3, a3, p, _tp_seed(ctx, layer_id, SITE_RES3))
     st.update(x_in=x_in, y1_full=y1_full, mean1=mean1, rstd1=rstd1, qkv=qkv, o1=o1, lse1=lse1, z3=z3, y3_full=y3_full,
               mean3=mean3, rstd3=rstd3, h=h)
@@ -173,18 +164,19 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     from .transformer import SITE_ATTN1, SITE_RES1, SITE_RES3
     g, da3 = F.sum_dropout_bwd(dys, p, _tp_seed(ctx, layer_id, SITE_RES3))    # d x_out rows; d a3 = dropout'(d x_out)
     # linear2 (row-parallel):  d h_local = gather(d a3) @ W2_local ;  dW2_local += gather(d a3)^T h_local
-    dh, g_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True)
-    G.wgrad(g_full, st["h"], G(L.linear2.weight), None)
-    G.bias_grad(da3, G(L.linear2.bias))
+    # (the activation derivative rides in the epilogue of the gather GEMM: ReLU mask / GELU' from the stashed activations)
     if a.activation == "relu":
-        dh = torch.where(st["h"] > 0, dh, torch.zeros_like(dh))
+        dh, g_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True, mask_pos_aux=st["h"])
     elif a.activation == "swiglu":
+        dh, g_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True)
         dh = F.swiglu_bwd(dh, st["hpre"])
     else:
-        dh = _gelu_bwd(dh, st["hpre"])
+        dh, g_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True, gelu_aux=st["hpre"])
+    G.wgrad(g_full, st["h"], G(L.linear2.weight), None)
+    G.bias_grad(da3, G(L.linear2.bias))
     # linear1 (column-parallel):  dW1_local += dh^T gather(y3) ;  d y3 rows = reduce-scatter(dh @ W1_local)
     G.wgrad(dh, st["y3_full"], G(L.linear1.weight), G(L.linear1.bias))
-    dy3 = tp.linear_rs(dh, L.linear1.weight, w_mn_major=True).to(g.dtype)
+    dy3 = tp.rs_finish(tp.linear_rs(dh, L.linear1.weight, w_mn_major=True), None, g.dtype)
     dz3_ln, _ = F.norm_bwd([dy3], st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias),
                            0.0, 0, rms, need_da=False)
     total, da1 = F.sum_dropout_bwd([g, dz3_ln], p, _tp_seed(ctx, layer_id, SITE_RES1))   # d z3 rows; d a1 = dropout'(d z3)
@@ -198,7 +190,7 @@ def tp_prenorm_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: 
     if a.rope:
         F.rope_(dqkv, 0, ctx.S, 2 * Hl, a.dim // a.n_heads, a.rope_theta, inverse=True)
     G.wgrad(dqkv, st["y1_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
-    dy1 = tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True).to(g.dtype)
+    dy1 = tp.rs_finish(tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True), None, g.dtype)
     dx_ln, _ = F.norm_bwd([dy1], st["x_in"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
                           0.0, 0, rms, need_da=False)
     return [total, dx_ln]
@@ -220,14 +212,14 @@ def tp_postln_forward(L, layer_id: int, x0: torch.Tensor, ctx, st: dict) -> torc
     # ---- self-attention ----
     qkv, x0_full = tp.ag_linear(x0, L.self_attn.in_proj_weight, L.self_attn.in_proj_bias)
     o1, lse1 = F.attention_fwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], ctx.B, Hl, a.causal, None, p, sd(SITE_ATTN1))
-    a1 = _rs_finish(tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x0.dtype)
+    a1 = _rs_finish(tp, tp.linear_rs(o1, L.self_attn.out_proj.weight), L.self_attn.out_proj.bias, x0.dtype)
     z1, x1, mean1, rstd1 = F.add_dropout_norm_fwd(x0, a1, L.norm1.weight, L.norm1.bias, eps, p, sd(SITE_RES1), rms)
     # ---- cross-attention: q from x1, k/v from the layer input ----
     W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
     q2, x1_full = tp.ag_linear(x1, W[:dl], bvec[:dl])
     kv2 = F.linear_fwd(x0_full, W[dl:], bvec[dl:])
     o2, lse2 = F.attention_fwd(q2, kv2[:, :dl], kv2[:, dl:], ctx.B, Hl, False, None, p, sd(SITE_ATTN2))
-    a2 = _rs_finish(tp.linear_rs(o2, L.multihead_attn.out_proj.weight), L.multihead_attn.out_proj.bias, x0.dtype)
+    a2 = _rs_finish(tp, tp.linear_rs(o2, L.multihead_attn.out_proj.weight), L.multihead_attn.out_proj.bias, x0.dtype)
     z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p, sd(SITE_RES2), rms)
     # ---- feed-forward ----
     if a.activation == "relu":
@@ -238,7 +230,7 @@ def tp_postln_forward(L, layer_id: int, x0: torch.Tensor, ctx, st: dict) -> torc
         hpre, x2_full = tp.ag_linear(x2, L.linear1.weight, L.linear1.bias)
         h = F.gelu_fwd(hpre)
         st["hpre"] = hpre
-    a3 = _rs_finish(tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x0.dtype)
+    a3 = _rs_finish(tp, tp.linear_rs(h, L.linear2.weight), L.linear2.bias, x0.dtype)
     z3, x3, mean3, rstd3 = F.add_dropout_norm_fwd(x2, a3, L.norm3.weight, L.norm3.bias, eps, p, sd(SITE_RES3), rms)
     st.update(x0_full=x0_full, qkv=qkv, o1=o1, lse1=lse1, z1=z1, mean1=mean1, rstd1=rstd1, x1_full=x1_full, q2=q2, kv2=kv2,
               o2=o2, lse2=lse2, z2=z2, mean2=mean2, rstd2=rstd2, x2_full=x2_full, h=h, z3=z3, mean3=mean3, rstd3=rstd3)
@@ -255,15 +247,15 @@ def tp_postln_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: d
     dz3, da3 = F.norm_bwd(dys, st["z3"], st["mean3"], st["rstd3"], L.norm3.weight, G(L.norm3.weight), G(L.norm3.bias), p,
                           sd(SITE_RES3), rms)
     dtype = dz3.dtype
-    dh, da3_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True)
+    if a.activation == "relu":   # ReLU (+ hidden dropout) mask and 1/(1-p) in the epilogue of the gather GEMM
+        dh, da3_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True, mask_pos_aux=st["h"],
+                                    alpha=(1.0 / (1.0 - p)) if p > 0 else 1.0)
+    else:
+        dh, da3_full = tp.ag_linear(da3, L.linear2.weight, w_mn_major=True, gelu_aux=st["hpre"])
     G.wgrad(da3_full, st["h"], G(L.linear2.weight), None)
     G.bias_grad(da3, G(L.linear2.bias))
-    if a.activation == "relu":
-        dh = torch.where(st["h"] > 0, dh * (1.0 / (1.0 - p)) if p > 0 else dh, torch.zeros_like(dh))
-    else:
-        dh = _gelu_bwd(dh, st["hpre"])
     G.wgrad(dh, st["x2_full"], G(L.linear1.weight), G(L.linear1.bias))
-    dx2 = tp.linear_rs(dh, L.linear1.weight, w_mn_major=True).to(dtype)
+    dx2 = tp.rs_finish(tp.linear_rs(dh, L.linear1.weight, w_mn_major=True), None, dtype)
     # ---- cross-attention ----
     W = L.multihead_attn.in_proj_weight
     gW, gb = G(W), G(L.multihead_attn.in_proj_bias)
@@ -279,8 +271,8 @@ def tp_postln_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: d
                     out=(dq2, dkv2[:, :dl], dkv2[:, dl:]))
     G.wgrad(dq2, st["x1_full"], gW[:dl], gb[:dl])
     G.wgrad(dkv2, st["x0_full"], gW[dl:], gb[dl:])
-    dx1 = tp.linear_rs(dq2, W[:dl], w_mn_major=True).to(dtype).clone()       # the reduce-scatter buffer is reused two calls on
-    dx0_extra = tp.linear_rs(dkv2, W[dl:], w_mn_major=True).to(dtype).clone()
+    dx1 = tp.rs_finish(tp.linear_rs(dq2, W[:dl], w_mn_major=True), None, dtype)   # (a fresh tensor: the symmetric buffer is reused two calls on)
+    dx0_extra = tp.rs_finish(tp.linear_rs(dkv2, W[dl:], w_mn_major=True), None, dtype)
     # ---- self-attention ----
     dz1, da1 = F.norm_bwd([dz2, dx1], st["z1"], st["mean1"], st["rstd1"], L.norm1.weight, G(L.norm1.weight), G(L.norm1.bias),
                           p, sd(SITE_RES1), rms)
@@ -292,5 +284,5 @@ def tp_postln_backward(L, layer_id: int, dys: Sequence[torch.Tensor], ctx, st: d
     F.attention_bwd(qkv[:, :dl], qkv[:, dl:2 * dl], qkv[:, 2 * dl:], st["o1"], do1, st["lse1"], ctx.B, Hl, a.causal, None, p,
                     sd(SITE_ATTN1), out=(dqkv[:, :dl], dqkv[:, dl:2 * dl], dqkv[:, 2 * dl:]))
     G.wgrad(dqkv, st["x0_full"], G(L.self_attn.in_proj_weight), G(L.self_attn.in_proj_bias))
-    dx0 = tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True).to(dtype)
+    dx0 = tp.rs_finish(tp.linear_rs(dqkv, L.self_attn.in_proj_weight, w_mn_major=True), None, dtype)
     return [dz1, dx0, dx0_extra]

@@ -144,6 +144,10 @@ def _bind_tp(lib) -> None:
     lib.ppb_gemm_allgather_bf16.restype = I
     lib.ppb_gemm_reducescatter_bf16.argtypes = [P, P, P, I, I, I, L, L, L, I, I, P]
     lib.ppb_gemm_reducescatter_bf16.restype = I
+    lib.ppb_gemm_allgather_fused_bf16.argtypes = [P, P, P, ctypes.c_uint, P, P, I, I, I, L, L, I, I, I, I, P, P, L, c_float, P]
+    lib.ppb_gemm_allgather_fused_bf16.restype = I
+    lib.ppb_gemm_allgather_fused_chunks_per_panel.argtypes = [I]
+    lib.ppb_gemm_allgather_fused_chunks_per_panel.restype = I
     lib._ppb_tp_bound = True
 
 
@@ -167,6 +171,67 @@ def allgather_linear(a_shard_ptrs: List[int], rows_per_rank: int, K: int, lda: i
     rc = lib.ppb_gemm_allgather_bf16(arr, w.data_ptr(), out.data_ptr(), M, N, K, lda, w.stride(0), out.stride(0), tp, rank,
                                      int(w_mn_major), epi, _lib.ptr(bias), torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "ppb_gemm_allgather_bf16")
+    _lib.count_launch()
+    return out
+
+
+def _gelu_bwd_ref(dh: torch.Tensor, hpre: torch.Tensor) -> torch.Tensor:
+    a = hpre.float()
+    cdf = 0.5 * (1.0 + torch.erf(a * 0.70710678118))
+    pdf = 0.3989422804 * torch.exp(-0.5 * a * a)
+    return (dh.float() * (cdf + a * pdf)).to(dh.dtype)
+
+
+class GatherFlags:
+    """Panel counters of the fused all-gather GEMM: one uint32 per 128-row panel of the gathered activations, zeroed
+    once and then only ever incremented by the kernels; ``next_target`` is what every counter reaches after the next
+    call (the counters are never reset, so no memset sits between two launches)."""
+
+    def __init__(self, M: int, device: torch.device):
+        self.flags = torch.zeros((M + 127) // 128, dtype=torch.int32, device=device)
+        self.total = 0
+
+    def next_target(self, K: int) -> int:
+        lib = _lib.load(required=True)
+        _bind_tp(lib)
+        self.total += int(lib.ppb_gemm_allgather_fused_chunks_per_panel(K))
+        if self.total >= 2 ** 31:   # ~10^8 calls away; start over rather than wrap
+            torch.cuda.current_stream().synchronize()
+            self.flags.zero_()
+            self.total = int(lib.ppb_gemm_allgather_fused_chunks_per_panel(K))
+        return self.total
+
+
+def fused_allgather_ok(rows_per_rank: int, K: int) -> bool:
+    return rows_per_rank % 128 == 0 and K % 64 == 0
+
+
+def allgather_linear_fused(a_shard_ptrs: List[int], rows_per_rank: int, K: int, full: torch.Tensor, gflags: GatherFlags,
+                           w: torch.Tensor, rank: int, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+                           out: Optional[torch.Tensor] = None, w_mn_major: bool = False,
+                           mask_pos_aux: Optional[torch.Tensor] = None, gelu_aux: Optional[torch.Tensor] = None,
+                           alpha: float = 1.0) -> torch.Tensor:
+    """K12, fused: y[M, N] = act(concat_r(A_r) @ op(w) + bias) in ONE kernel that also gathers: copier warps stream every
+    shard (peers over NVLink, each byte once) into ``full`` [M, K] and release 128-row panels through ``gflags`` while
+    the tiles of the own shard are already being multiplied.  ``full`` holds the gathered activations afterwards."""
+    lib = _lib.load(required=True)
+    _bind_tp(lib)
+    tp = len(a_shard_ptrs)
+    M = rows_per_rank * tp
+    N = w.shape[1] if w_mn_major else w.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.bfloat16, device=w.device)
+    epi, aux = (0 if bias is None else _EPI["bias" if act is None else act]), None
+    if mask_pos_aux is not None:      # activation backward in the epilogue: . * alpha * (aux > 0)
+        epi, aux = 5, mask_pos_aux
+    elif gelu_aux is not None:        # . * gelu'(aux)
+        epi, aux = 6, gelu_aux
+    arr = (c_void_p * tp)(*a_shard_ptrs)
+    rc = lib.ppb_gemm_allgather_fused_bf16(arr, full.data_ptr(), gflags.flags.data_ptr(), gflags.next_target(K), w.data_ptr(),
+                                           out.data_ptr(), M, N, K, w.stride(0), out.stride(0), tp, rank, int(w_mn_major),
+                                           epi, _lib.ptr(bias), _lib.ptr(aux), 0 if aux is None else aux.stride(0),
+                                           float(alpha), torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "ppb_gemm_allgather_fused_bf16")
     _lib.count_launch()
     return out
 
@@ -221,12 +286,19 @@ class TensorParallelMLP:
         self.x_sym = SymmetricBuffer((self.rows, self.d), torch.bfloat16, dev, group)
         self.y_sym = SymmetricBuffer((self.rows, self.d), torch.float32, dev, group)
         self.rank = self.x_sym.rank
+        self.fused_gather = fused_allgather_ok(self.rows, self.d)
+        self.full = torch.empty((T, self.d), dtype=torch.bfloat16, device=dev)
+        self.gflags = GatherFlags(T, dev)
 
     def forward(self, x_shard: torch.Tensor) -> torch.Tensor:
         self.x_sym.tensor.copy_(x_shard)
         self.y_sym.tensor.zero_()
         self.x_sym.barrier(0)                       # every rank's input shard and zeroed output are in place
-        h = allgather_linear(self.x_sym.ptrs, self.rows, self.d, self.d, self.w1, self.rank, self.b1, self.act)
+        if self.fused_gather:
+            h = allgather_linear_fused(self.x_sym.ptrs, self.rows, self.d, self.full, self.gflags, self.w1, self.rank,
+                                       self.b1, self.act)
+        else:
+            h = allgather_linear(self.x_sym.ptrs, self.rows, self.d, self.d, self.w1, self.rank, self.b1, self.act)
         linear_reducescatter(h, self.w2, self.y_sym.ptrs, self.d)
         self.y_sym.barrier(1)                       # all partial sums have landed
         return self.y_sym.tensor
@@ -260,12 +332,17 @@ class TPComm:
             self.kx = self.ky = 0
             import os
             self.direct_peer = os.environ.get("PPB_TP_DIRECT_PEER", "0") == "1"
+            self.fused_gather = fused_allgather_ok(self.rows, self.d) and os.environ.get("PPB_TP_FUSED_GATHER", "1") != "0"
+            self.gflags = GatherFlags(self.rows * self.tp, self.device)
             self.x_sym[0].barrier(0)   # every rank's zeroed reduce-scatter buffers exist before the first push
 
     # ---- all-gather -> GEMM -------------------------------------------------------------------------------------
     def ag_linear(self, x_shard: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
-                  act: Optional[str] = None, w_mn_major: bool = False, need_full: bool = True):
-        """(act(gather(x_shard) @ op(w) + bias), gather(x_shard) or None).  w is [N, d] (or [d, N] when w_mn_major)."""
+                  act: Optional[str] = None, w_mn_major: bool = False, need_full: bool = True,
+                  mask_pos_aux: Optional[torch.Tensor] = None, gelu_aux: Optional[torch.Tensor] = None, alpha: float = 1.0):
+        """(act(gather(x_shard) @ op(w) + bias), gather(x_shard) or None).  w is [N, d] (or [d, N] when w_mn_major).
+        ``mask_pos_aux`` / ``gelu_aux`` (+ ``alpha``) apply an activation derivative in the GEMM epilogue instead
+        (the input-gradient GEMM of a row-parallel layer): y = alpha * (gather(x) @ op(w)) * act'(aux)."""
         import torch.distributed as dist
         if not self.cuda:
             full = torch.empty((self.rows * self.tp, self.d), dtype=x_shard.dtype)
@@ -277,6 +354,10 @@ class TPComm:
                 y = torch.relu(y)
             elif act == "gelu":
                 y = torch.nn.functional.gelu(y)
+            if mask_pos_aux is not None:
+                y = torch.where(mask_pos_aux > 0, y * alpha, torch.zeros_like(y))
+            elif gelu_aux is not None:
+                y = _gelu_bwd_ref(y * alpha, gelu_aux)
             return y, (full if need_full else None)
         buf = self.x_sym[self.kx]
         self.kx ^= 1
@@ -287,15 +368,25 @@ class TPComm:
             # its A tiles and peer memory is not cached in the local L2, so a remote tile crosses NVLink N/256 times
             # (43x at Llama-7B FFN width: measured 5.4 ms vs 1.5 ms of GEMM time per layer) -- only worth it for narrow N
             return allgather_linear(buf.ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major), None
-        # one pass over NVLink: pull the peers' shards next to ours (the weight-gradient GEMM wants the gathered rows
-        # anyway), then run the same kernel with every shard pointer local
         full = torch.empty((self.rows * self.tp, self.d), dtype=torch.bfloat16, device=self.device)
+        if self.fused_gather:
+            # ONE kernel: copier warps bring every shard over NVLink exactly once into `full` (which the weight-gradient
+            # GEMM of the backward pass wants anyway) and release panels to the tiles as they land
+            out = allgather_linear_fused(buf.ptrs, self.rows, self.d, full, self.gflags, w, self.rank, bias, act,
+                                         w_mn_major=w_mn_major, mask_pos_aux=mask_pos_aux, gelu_aux=gelu_aux, alpha=alpha)
+            return out, (full if need_full else None)
+        # shapes the fused kernel does not take (rows per rank not a multiple of 128, K not of 64): pull the peers'
+        # shards next to ours, then run the gather kernel with every shard pointer local
         for r in range(self.tp):
             src = buf.tensor if r == self.rank else buf.hdl.get_buffer(r, (self.rows, self.d), torch.bfloat16)
             full[r * self.rows:(r + 1) * self.rows].copy_(src)
         base = full.data_ptr()
         ptrs = [base + r * self.rows * self.d * 2 for r in range(self.tp)]
         out = allgather_linear(ptrs, self.rows, self.d, self.d, w, self.rank, bias, act, w_mn_major=w_mn_major)
+        if mask_pos_aux is not None:      # unusual shapes only (the fused kernel applies these in its epilogue)
+            out = torch.where(mask_pos_aux > 0, out * alpha, torch.zeros_like(out))
+        elif gelu_aux is not None:
+            out = _gelu_bwd_ref(out * alpha, gelu_aux)
         return out, (full if need_full else None)
 
     # ---- GEMM -> reduce-scatter ---------------------------------------------------------------------------------
@@ -313,6 +404,20 @@ class TPComm:
         linear_reducescatter(x, w, cur.ptrs, self.d, w_mn_major=w_mn_major)
         cur.barrier(1)
         return cur.tensor
+
+    def rs_finish(self, y32: torch.Tensor, bias: Optional[torch.Tensor], dtype: torch.dtype) -> torch.Tensor:
+        """fp32 reduce-scatter result (+ the replicated bias of a row-parallel layer) -> a fresh tensor in the activation
+        dtype, one pass (``ppb_bias_cast_f32_to_bf16``); the symmetric reduce-scatter buffer is free for reuse afterwards."""
+        if not (self.cuda and dtype == torch.bfloat16 and y32.shape[1] % 4 == 0):
+            return ((y32 + bias.float()) if bias is not None else y32).to(dtype).clone()
+        lib = _lib.load(required=True)
+        out = torch.empty(y32.shape, dtype=torch.bfloat16, device=y32.device)
+        lib.ppb_bias_cast_f32_to_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_longlong, c_int, c_void_p]
+        lib.ppb_bias_cast_f32_to_bf16.restype = c_int
+        _lib.check(lib.ppb_bias_cast_f32_to_bf16(y32.data_ptr(), _lib.ptr(bias), out.data_ptr(), y32.shape[0], y32.shape[1],
+                                                 torch.cuda.current_stream().cuda_stream), "ppb_bias_cast_f32_to_bf16")
+        _lib.count_launch()
+        return out
 
     def all_reduce(self, t: torch.Tensor) -> None:
         import torch.distributed as dist

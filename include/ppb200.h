@@ -83,7 +83,8 @@ int ppb_gemm_allgather_bf16(void* const* a_shards, const void* B, void* C, int M
 int ppb_gemm_allgather_fused_chunks_per_panel(int K);
 int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, unsigned int* flags, unsigned int target, const void* B,
                                   void* C, int M, int N, int K, long long ldb, long long ldc, int tp, int rank,
-                                  int b_mn_major, int epi, const void* bias, void* stream);
+                                  int b_mn_major, int epi, const void* bias, const void* aux, long long ld_aux, float alpha,
+                                  void* stream);
 /* ---- K11: GEMM -> reduce-scatter (row-parallel layer under tensor parallelism) -----------------------------------
  * dst_shards[o][M/tp, N] (fp32, zeroed by the caller) += rows [o*M/tp, (o+1)*M/tp) of A[M,K] * op(B)^T, for every
  * owner o: each 32-row slab of the partial product is TMA-reduce-added into its owner's buffer (local or over
@@ -168,6 +169,8 @@ int ppb_add_dropout_fwd(const void* resid, const void* a, void* z, long long n, 
 int ppb_sum_dropout_bwd(const void* dy0, const void* dy1, const void* dy2, void* dz, void* da, long long n,
                         float dropout_p, unsigned long long seed, void* stream);
 int ppb_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+/* y[T, d] (bf16) = x[T, d] (fp32) + bias[d] (bf16, may be NULL): finishes a reduce-scatter in one pass (d % 4 == 0). */
+int ppb_bias_cast_f32_to_bf16(const float* x, const void* bias, void* y, long long T, int d, void* stream);
 
 /* ---- Llama-style block pieces (csrc/llama_ops.cu) -------------------------------------------------------------
  * No counterpart in the reference (its block is nn.TransformerDecoderLayer: ReLU FFN, no positional encoding,

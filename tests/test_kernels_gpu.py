@@ -273,6 +273,76 @@ def test_allgather_gemm_single_gpu(tp, rows, N, K, act):
         assert rel_err(y, ref) < 1e-2
 
 
+@pytest.mark.parametrize("tp,rows,N,K,act", [(2, 256, 512, 256, None), (4, 128, 2048, 1024, "relu"), (2, 1024, 1000, 512, "gelu"),
+                                             (8, 512, 3072, 1024, None)])
+def test_fused_allgather_gemm_single_gpu(tp, rows, N, K, act):
+    """K12, fused form (copier warps + panel counters inside the GEMM kernel), with the tp shards in separate
+    buffers of one GPU: every 'rank' must produce the full product AND leave the gathered activations behind; the
+    counters are never reset between calls."""
+    from ppb200.ops.collective import GatherFlags, allgather_linear_fused
+    torch.manual_seed(15)
+    w = torch.randn(N, K, device=DEV, dtype=torch.bfloat16) * 0.05
+    b = torch.randn(N, device=DEV, dtype=torch.bfloat16)
+    flags = [GatherFlags(rows * tp, torch.device(DEV)) for _ in range(tp)]
+    for it in range(3):   # fresh inputs each round: stale panels from the previous call would show up as an error
+        shards = [torch.randn(rows, K, device=DEV, dtype=torch.bfloat16) for _ in range(tp)]
+        ref = R.linear_fwd(torch.cat(shards), w, b, act)
+        for rank in range(tp):
+            full = torch.full((rows * tp, K), float("nan"), device=DEV, dtype=torch.bfloat16)
+            y = allgather_linear_fused([s.data_ptr() for s in shards], rows, K, full, flags[rank], w, rank, b, act)
+            assert rel_err(y, ref) < 1e-2, (it, rank)
+            assert torch.equal(full, torch.cat(shards)), (it, rank)
+
+
+def test_tp_comm_and_fused_dp_wiring_world_size_one():
+    """The Python side of the fused compute+collective paths (symmetric-memory rendezvous, TPComm buffers and
+    barriers, FusedGradAllReduce arming / coverage bookkeeping / finish) driven end to end on ONE GPU with a
+    single-rank process group, so the driver's 1-GPU test run covers the wiring and not only the raw kernels."""
+    import os
+    import torch.distributed as dist
+    from ppb200.ops.collective import FusedGradAllReduce, TPComm
+    created = False
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(29700 + os.getpid() % 200))
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+        created = True
+    try:
+        torch.manual_seed(16)
+        dev = torch.device("cuda", 0)
+        rows, d, f = 256, 512, 1024
+        tp = TPComm(dist.group.WORLD, rows, d, dev)
+        x = torch.randn(rows, d, device=dev, dtype=torch.bfloat16)
+        w1 = torch.randn(f, d, device=dev, dtype=torch.bfloat16) * 0.05
+        b1 = torch.randn(f, device=dev, dtype=torch.bfloat16)
+        w2 = torch.randn(d, f, device=dev, dtype=torch.bfloat16) * 0.05
+        for _ in range(3):    # the double-buffered symmetric buffers and the panel counters cycle
+            h, full = tp.ag_linear(x, w1, b1, "relu")
+            assert rel_err(h, R.linear_fwd(x, w1, b1, "relu")) < 1e-2 and torch.equal(full, x)
+            y = tp.linear_rs(h, w2)
+            assert rel_err(y, h.float() @ w2.float().t()) < 5e-3
+        # fused DP gradient reduction with one replica: final = sum over replicas = the local gradient
+        n = 512 * 256 + 512
+        grad = torch.zeros(n, device=dev)
+        ar = FusedGradAllReduce(grad, n, dist.group.WORLD, 1.0)
+        dy = torch.randn(1024, 512, device=dev, dtype=torch.bfloat16)
+        xx = torch.randn(1024, 256, device=dev, dtype=torch.bfloat16)
+        gw, gb = grad[:512 * 256].view(512, 256), grad[512 * 256:]
+        gw.add_(1.0)
+        gb.add_(2.0)
+        ar.begin_last_backward()
+        F.linear_wgrad(dy, xx, gw, None, ar=ar)
+        ar.finish()
+        torch.cuda.synchronize()
+        want = 1.0 + dy.float().t() @ xx.float()
+        assert rel_err(ar.final[:512 * 256].view(512, 256), want) < 5e-3
+        assert rel_err(ar.final[512 * 256:n], torch.full((512,), 2.0, device=dev)) < 1e-6
+        ar.after_optimizer()
+    finally:
+        if created:
+            dist.destroy_process_group()
+
+
 @pytest.mark.parametrize("tp,M,N,K", [(2, 512, 768, 256), (4, 1024, 1024, 512), (2, 192, 200, 136)])
 def test_gemm_reducescatter_single_gpu(tp, M, N, K):
     """K11 numerics: tp 'ranks' with different K-slices push into per-owner buffers on one GPU."""
