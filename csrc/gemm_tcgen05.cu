@@ -87,7 +87,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                                           const GemmParams& p, const CUtensorMap* dst_maps,
                                           const CUtensorMap* a_maps = nullptr, const AgCopy* agc = nullptr) {
   using Cfg = GemmCfg<BN, CG, AG2 ? 2 * AG_CHUNK : 0>;
-  static_assert(!AG2 || CG == 1, "the fused all-gather keeps one CTA per tile");
+  // (AG2 with CTA pairs is fine: the tiles read A from THIS GPU's gathered copy; only the copier warps touch peer memory,
+  //  with plain non-multicast bulk loads)
   static_assert(CG == 1 || (OUT != 3 && BN >= 128), "CTA pairs: plain / accumulate outputs, BN >= 128");
   constexpr int TM = BM * CG;          // rows of the (pair) tile
   constexpr int BNH = BN / CG;         // B rows staged by one CTA
@@ -140,7 +141,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const int num_kb_total = (p.K + BK - 1) / BK;
   // all-gather fusion: rotate the row-block order so that every rank starts on its OWN shard (already local)
   // and touches the peers' shards afterwards, spreading the NVLink reads over time
-  const int m_rot = p.ag_rows_per_rank ? (p.ag_rank * (p.ag_rows_per_rank / BM)) : 0;
+  const int m_rot = p.ag_rows_per_rank ? (p.ag_rank * (p.ag_rows_per_rank / TM)) : 0;
   auto m_block_of = [&](int mn) { return (mn % p.tiles_m + m_rot) % p.tiles_m; };
 
   if (warp == 4) {
@@ -530,6 +531,20 @@ gemm_tcgen05_ag_kernel(const __grid_constant__ DstMaps amaps, const __grid_const
 // counter says it has landed, so the transfer hides under the tensor-core work.  amaps.m[0] = own shard, m[1] = the
 // local gathered buffer.  The gathered activations stay behind for the weight-gradient GEMM of the backward pass.
 constexpr int GEMM_AG_THREADS = GEMM_THREADS + 32;
+template <int BN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_AG_THREADS, 1)
+gemm_tcgen05_agfused_pair_kernel(const __grid_constant__ DstMaps amaps, const __grid_constant__ CUtensorMap tmB,
+                                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ AgCopy agc,
+                                 const GemmParams p) {
+  gemm_body<BN, false, B_MN, 0, 2, true>(amaps.m[0], tmB, tmC, p, nullptr, amaps.m + 1, &agc);
+}
+// K11 with CTA pairs (256-row tiles): the epilogue's TMA reduce-adds into the owners' buffers are unchanged.
+template <int BN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tcgen05_rs_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                            const __grid_constant__ DstMaps dst, const GemmParams p) {
+  gemm_body<BN, false, B_MN, 2, 2>(tmA, tmB, dst.m[0], p, dst.m);
+}
 template <int BN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_AG_THREADS, 1)
 gemm_tcgen05_agfused_kernel(const __grid_constant__ DstMaps amaps, const __grid_constant__ CUtensorMap tmB,
@@ -933,20 +948,22 @@ extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, 
     PPB_REQUIRE(aux != nullptr && (ld_aux % 8) == 0, "ppb_gemm_allgather_fused_bf16: epilogue %d needs an aux matrix with ld %% 8 == 0", epi);
   else
     PPB_REQUIRE(epi == PPB_EPI_NONE || bias != nullptr, "ppb_gemm_allgather_fused_bf16: epilogue needs a bias");
-  int bn, splits;
-  choose_config(M, N, K, PPB_OUT_BF16, 0, 0, &bn, &splits);
+  int bn, splits, cg = 1;
+  choose_config(M, N, K, PPB_OUT_BF16, 0, 0, &bn, &splits, &cg);
   const int rows = M / tp;
+  if (cg == 2 && ((rows % (2 * BM)) != 0 || bn != 256)) cg = 1;   // a pair tile must not straddle two shards
   DstMaps am;
   CUtensorMap tmB, tmC;
   bool ok = make_tmap_2d(&am.m[0], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, a_shards[rank], (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, BK, BM) &&
             make_tmap_2d(&am.m[1], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, full, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BK, BM);
   for (int r = 2; ok && r < 8; ++r) am.m[r] = am.m[0];
   ok = ok && (b_mn_major ? make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK)
-                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn));
+                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn / cg));
   ok = ok && make_tmap_2d(&tmC, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, C, (uint64_t)N, (uint64_t)M, (uint64_t)ldc * 2, 64, 32);
   if (!ok) return -3;
   GemmParams p;
   fill_plain_params(p, M, N, K, bn, 1);
+  p.tiles_m = (M + BM * cg - 1) / (BM * cg);
   p.epi = epi;
   p.bias = reinterpret_cast<const bf16*>(bias);
   p.aux = reinterpret_cast<const bf16*>(aux);
@@ -966,7 +983,22 @@ extern "C" int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, 
   agc.rank = rank;
   // every CTA must be resident at once (tiles wait for chunks that other CTAs move): at most one CTA per SM
   const long long total = (long long)p.tiles_m * p.tiles_n;
-  const int grid = (int)(total < sm_count() ? total : sm_count());
+  const int slots = sm_count() / cg;
+  const int grid = (int)(total < slots ? total : slots) * cg;
+  if (cg == 2) {
+    using CfgP = GemmCfg<256, 2, 2 * AG_CHUNK>;
+    if (b_mn_major) {
+      auto kfn = gemm_tcgen05_agfused_pair_kernel<256, true>;
+      PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, CfgP::SMEM_BYTES));
+      kfn<<<grid, GEMM_AG_THREADS, CfgP::SMEM_BYTES, stream>>>(am, tmB, tmC, agc, p);
+    } else {
+      auto kfn = gemm_tcgen05_agfused_pair_kernel<256, false>;
+      PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, CfgP::SMEM_BYTES));
+      kfn<<<grid, GEMM_AG_THREADS, CfgP::SMEM_BYTES, stream>>>(am, tmB, tmC, agc, p);
+    }
+    PPB_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
 #define PPB_LAUNCH_AGF(BN_, BMN_)                                                                                   \
   {                                                                                                                 \
     using CfgF = GemmCfg<BN_, 1, 2 * AG_CHUNK>;                                                                     \
@@ -990,23 +1022,40 @@ extern "C" int ppb_gemm_reducescatter_bf16(const void* A, const void* B, void* c
   PPB_REQUIRE(M > 0 && N > 0 && K > 0 && (M % tp) == 0 && ((M / tp) % 32) == 0,
               "ppb_gemm_reducescatter_bf16: rows per rank (M/tp) must be a multiple of 32");
   PPB_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0 && (ldc % 4) == 0, "ppb_gemm_reducescatter_bf16: misaligned leading dimension");
-  int bn, splits;
-  choose_config(M, N, K, PPB_OUT_F32, 0, 0, &bn, &splits);
+  int bn, splits, cg = 1;
+  choose_config(M, N, K, PPB_OUT_F32, 0, 0, &bn, &splits, &cg);
+  if (bn != 256) cg = 1;
   const int rows = M / tp;
   CUtensorMap tmA, tmB;
   DstMaps dm;
   bool ok = make_tmap_2d(&tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, BM);
   ok = ok && (b_mn_major ? make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb * 2, 64, BK)
-                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn));
+                         : make_tmap_2d(&tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb * 2, BK, bn / cg));
   for (int r = 0; ok && r < tp; ++r)
     ok = make_tmap_2d(&dm.m[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, dst_shards[r], (uint64_t)N, (uint64_t)rows, (uint64_t)ldc * 4, 32, 32);
   for (int r = tp; ok && r < 8; ++r) dm.m[r] = dm.m[0];
   if (!ok) return -3;
   GemmParams p;
   fill_plain_params(p, M, N, K, bn, 1);
+  p.tiles_m = (M + BM * cg - 1) / (BM * cg);
   p.rs_rows_per_rank = rows;
   const long long total = (long long)p.tiles_m * p.tiles_n;
-  const int grid = (int)(total < sm_count() ? total : sm_count());
+  const int slots = sm_count() / cg;
+  const int grid = (int)(total < slots ? total : slots) * cg;
+  if (cg == 2) {
+    using CfgP = GemmCfg<256, 2>;
+    if (b_mn_major) {
+      auto kfn = gemm_tcgen05_rs_pair_kernel<256, true>;
+      PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, CfgP::SMEM_BYTES));
+      kfn<<<grid, GEMM_THREADS, CfgP::SMEM_BYTES, stream>>>(tmA, tmB, dm, p);
+    } else {
+      auto kfn = gemm_tcgen05_rs_pair_kernel<256, false>;
+      PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, CfgP::SMEM_BYTES));
+      kfn<<<grid, GEMM_THREADS, CfgP::SMEM_BYTES, stream>>>(tmA, tmB, dm, p);
+    }
+    PPB_CUDA_OK(cudaGetLastError());
+    return 0;
+  }
 #define PPB_LAUNCH_RS(BN_, BMN_)                                                                                 \
   {                                                                                                              \
     auto kfn = gemm_tcgen05_rs_kernel<BN_, BMN_>;                                                                \

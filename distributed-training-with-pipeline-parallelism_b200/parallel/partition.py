@@ -328,13 +328,15 @@ def measure_unit_costs(args: ModelArgs, micro_batch: int, seq_len: int, device: 
                 best = min(best, e0.elapsed_time(e1))
         return best
 
-    def one_unit_model(part: Optional[str], embed: bool, head: bool) -> Transformer:
+    def one_unit_model(part: Optional[str], embed: bool, head: bool, n_layers: int = 1) -> Transformer:
         with torch.device(dev):
-            m = Transformer(margs)
+            m = Transformer(ModelArgs(**{**margs.__dict__, "n_layers": n_layers}))
         if part is None:
-            del m.layers["0"]
+            for k in list(m.layers.keys()):
+                del m.layers[k]
         else:
-            _apply_part(m.layers["0"], part)
+            for layer in m.layers.values():
+                _apply_part(layer, part)
         if not embed:
             m.tok_embeddings = None
         if not head:
@@ -344,18 +346,31 @@ def measure_unit_costs(args: ModelArgs, micro_batch: int, seq_len: int, device: 
 
     gen = torch.Generator(device="cpu").manual_seed(7)
     tokens = torch.randint(0, args.vocab_size, (micro_batch, seq_len), generator=gen).to(dev)
+    act = lambda rows: torch.randn(rows, seq_len, d, device=dev).to(dt) * 0.5          # noqa: E731
+    grad = lambda rows: torch.randn(rows * seq_len, d, device=dev).to(dt) * 0.01        # noqa: E731
     for u in units:
         st = PipelineStage(one_unit_model(u, False, False), 1, 3, dev)
-        inp = torch.randn(st.in_rows * micro_batch, seq_len, d, device=dev).to(dt) * 0.5
-        dout = torch.randn(st.out_rows * T, d, device=dev).to(dt) * 0.01
-        out[u] = run(st, inp, None, dout)
+        out[u] = run(st, act(st.in_rows * micro_batch), None, grad(st.out_rows * micro_batch))
         del st
     st = PipelineStage(one_unit_model(None, False, True), 2, 3, dev)
-    out["head"] = run(st, torch.randn(micro_batch, seq_len, d, device=dev).to(dt) * 0.5, tokens, None)
+    out["head"] = run(st, act(micro_batch), tokens, None)
     del st
     st = PipelineStage(one_unit_model(None, True, False), 0, 3, dev)
-    out["embed"] = run(st, tokens, None, torch.randn(T, d, device=dev).to(dt) * 0.01)
+    out["embed"] = run(st, tokens, None, grad(micro_batch))
     del st
+    # Every one-unit measurement carries a fixed per-replay cost (two graph launches, the input / gradient copies into
+    # the slot's static buffers) that a real stage pays once, not once per unit: a one-layer and a two-layer stage give
+    # the true marginal cost of a layer and that fixed part, which is taken out of every unit before they are used.
+    t1 = run(PipelineStage(one_unit_model("full", False, False, 1), 1, 3, dev), act(micro_batch), None, grad(micro_batch))
+    t2 = run(PipelineStage(one_unit_model("full", False, False, 2), 1, 3, dev), act(micro_batch), None, grad(micro_batch))
+    layer = max(t2 - t1, 0.25 * t1)
+    fixed = max(0.0, t1 - layer)
+    out["_raw"] = {**{k: v for k, v in out.items()}, "layer1": t1, "layer2": t2, "fixed": fixed}
+    for k in list(units) + ["head", "embed"]:
+        out[k] = max(out[k] - fixed, 0.1 * out[k])
+    scale = layer / max(sum(out[u] for u in units), 1e-9)      # the units of a layer add up to the marginal layer cost
+    for u in units:
+        out[u] *= scale
     torch.cuda.synchronize(dev)
     torch.cuda.empty_cache()
     return out

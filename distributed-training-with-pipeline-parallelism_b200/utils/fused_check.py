@@ -77,16 +77,18 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     x = (torch.randn(T, d, generator=g) * 0.5).to(dev).to(torch.bfloat16)       # same on every rank (same seed)
     w1 = (torch.randn(n_loc, d, generator=g) * 0.02).to(dev).to(torch.bfloat16)
     xs = x[rank * rows:(rank + 1) * rows].contiguous()
-    xsym = SymmetricBuffer((rows, d), torch.bfloat16, dev, group)
+    xsyms = [SymmetricBuffer((rows, d), torch.bfloat16, dev, group) for _ in range(2)]
     full = torch.empty(T, d, dtype=torch.bfloat16, device=dev)
     gfl = GatherFlags(T, dev)
     y = torch.empty(T, n_loc, dtype=torch.bfloat16, device=dev)
+    kx = [0]
 
-    def k12():
+    def k12():   # as TPComm.ag_linear: double-buffered shards, so ONE device barrier per call orders everything
+        xsym = xsyms[kx[0]]
+        kx[0] ^= 1
         xsym.tensor.copy_(xs)
         xsym.barrier(0)
         allgather_linear_fused(xsym.ptrs, rows, d, full, gfl, w1, rank, out=y)
-        xsym.barrier(1)     # nobody rewrites its shard while a peer may still be reading it
 
     xg = torch.empty(T, d, dtype=torch.bfloat16, device=dev)
 
