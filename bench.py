@@ -52,6 +52,8 @@ def parse():
                     help="auto = measure the per-unit costs on the GPU, cut inside layers when that lowers the largest stage")
     ap.add_argument("--dropout", type=float, default=None)
     ap.add_argument("--n-layers", type=int, default=None)
+    ap.add_argument("--extra-warmup", type=int, default=None,
+                    help="1F1B: forwards kept in flight beyond torch's warm-up count (hides stage-to-stage transfer latency)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fused-check", action="store_true",
                     help="skip the K10/K11/K12 parity + roofline check that multi-GPU runs append (ranks 0-1, after the timed regions)")
@@ -156,7 +158,7 @@ def run_ours(a, rank, local_rank, world):
         stages.append(st)
     opt = {"lr": 1e-4, "betas": (0.9, 0.95), "weight_decay": 0.1}
     sched = make_schedule(a.schedule, stages, a.microbatches, None, pp_group=pp_group, pp_group_bwd=pp_group_bwd,
-                          dp_group=dp_group, optimizer=opt)
+                          dp_group=dp_group, optimizer=opt, extra_warmup=a.extra_warmup)
 
     B, S = a.global_batch // a.dp, a.seq_len
     first, last = 0 in sched.local, (num_stages - 1) in sched.local
@@ -252,7 +254,8 @@ def run_ours(a, rank, local_rank, world):
             "config": config_dict(a, {"dim": margs.dim, "n_layers": margs.n_layers, "n_heads": margs.n_heads,
                                       "vocab_size": margs.vocab_size, "ffn_dim": margs.ffn_dim, "dropout": margs.dropout,
                                       **({} if a.model.startswith("ref-") else {"block": a.model})}, par),
-            "impl_notes": {"partition": rule, "partition_requested": a.partition,
+            "impl_notes": {"partition": rule, "partition_requested": a.partition, "extra_warmup": getattr(sched, "extra_warmup", 0),
+                           "nccl_p2p_channels": os.environ.get("NCCL_MAX_P2P_NCHANNELS"), "reserved_sms": os.environ.get("PPB_RESERVED_SMS"),
                            "partition_note": "the one real difference to the reference arm: stage boundaries are balanced on measured per-unit times (and may fall inside a layer); the reference uses helper:70-75 (n_layers // stages, remainder to the last stage)",
                            "unit_costs_ms": ({k: (round(v, 4) if isinstance(v, float) else v) for k, v in unit_ms.items()} if unit_ms else None),
                            "stack": "ppb200: explicit fused fwd/bwd stage program, libppb200.so sm_100a kernels, CUDA graphs per slot, NCCL p2p"},

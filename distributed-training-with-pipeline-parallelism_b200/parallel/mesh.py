@@ -41,14 +41,20 @@ class Mesh:
 
 
 def configure_nccl_for_pipeline() -> None:
-    """Call BEFORE ``init_process_group('nccl')``.  Stage-to-stage transfers are 2-32 MiB NCCL send/recv pairs that
-    overlap with compute; a posted receive spins on its SMs until the sender arrives, and with NCCL's default P2P
-    channel count those CTAs displace CTAs of the persistent tcgen05 GEMMs (measured on 4x B200, 1F1B: middle-rank
-    backward 5.6 ms -> 4.2 ms, step 303 -> 270 ms with <= 2 channels and 4 SMs left free).  User-set values win."""
+    """Call BEFORE ``init_process_group('nccl')``.  Stage-to-stage transfers are 8-16 MiB NCCL send/recv pairs that
+    overlap with compute.  Two opposing needs, both measured on 4x B200 (1F1B, flagship model, 32 micro-batches):
+
+    * a posted receive spins on its SMs until the sender arrives, and every SM NCCL holds pushes one CTA of a
+      persistent tcgen05 GEMM into a second wave -- so the kernels leave ``PPB_RESERVED_SMS`` SMs free;
+    * once the stages are balanced (partition on measured unit times) the steady state of 1F1B has NO slack, so the
+      latency of every transfer lands on the critical path once per micro-batch.  With 2 channels a message takes
+      ~0.2-0.3 ms and the step was 237.3 ms (critical-rank bubble 0.144 against a bound of 0.086); 8 channels / 8 SMs:
+      227.5 ms (0.102); 16 / 16: 225.8 ms (0.094) -- profiles/nccl_p2p_channels_n4.md.
+    User-set values win."""
     import os
-    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", "2")
+    os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", "16")
     os.environ.setdefault("NCCL_MIN_P2P_NCHANNELS", "1")
-    os.environ.setdefault("PPB_RESERVED_SMS", "4")
+    os.environ.setdefault("PPB_RESERVED_SMS", "16")
 
 
 def rank_of(dp: int, pp: int, tp: int, pp_size: int, tp_size: int) -> int:

@@ -35,7 +35,8 @@ class PipelineSchedule:
                  schedule: Optional[str] = None, pp_group=None, pp_group_bwd=None, dp_group=None,
                  optimizer: Optional[dict] = None,
                  scale_grads: bool = True, record_timeline: bool = True, fused_loss: Optional[bool] = None,
-                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2, actions=None, recompute: bool = False):
+                 cuda_graphs: Optional[bool] = None, graph_warmup_steps: int = 2, actions=None, recompute: bool = False,
+                 extra_warmup: Optional[int] = None):
         self.stages: List[PipelineStage] = [stages] if isinstance(stages, PipelineStage) else list(stages)
         if not self.stages:
             raise ValueError("need at least one stage")
@@ -76,8 +77,13 @@ class PipelineSchedule:
             order = self._load_actions(actions, optimizer is not None)
             self.name = "custom" if schedule is None else schedule
         else:
+            import os
+            if extra_warmup is None:   # 1F1B only: forwards kept in flight beyond torch's warm-up count (see one_f_one_b_order)
+                extra_warmup = int(os.environ.get("PPB_1F1B_EXTRA_WARMUP", "0"))
+            self.extra_warmup = int(extra_warmup)
             order = build_schedule(self.name, self.pp_size, self.m, n_virtual=self.n_virtual,
-                                   dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None)
+                                   dp_allreduce=self.dp_size > 1, with_optimizer=optimizer is not None,
+                                   extra_warmup=self.extra_warmup)
         self.full_order = order
         self.order: List[Action] = order[self.pp_rank]
         self._retire_in_order = self._retires_in_forward_order(self.order)

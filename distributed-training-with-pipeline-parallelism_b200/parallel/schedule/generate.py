@@ -37,14 +37,19 @@ def gpipe_order(pp_size: int, n_microbatches: int) -> Order:
     return {r: [Action(r, T.F, i) for i in range(m)] + [Action(r, T.B, i) for i in range(m)] for r in range(pp_size)}
 
 
-def one_f_one_b_order(pp_size: int, n_microbatches: int) -> Order:
-    """Warm-up of min(m, P - rank) forwards, then strictly alternating 1B-1F, then the backward drain."""
+def one_f_one_b_order(pp_size: int, n_microbatches: int, extra_warmup: int = 0) -> Order:
+    """Warm-up of min(m, P - rank) forwards, then strictly alternating 1B-1F, then the backward drain.
+
+    ``extra_warmup`` = additional forwards every rank but the last keeps in flight ("eager" 1F1B).  With perfectly
+    balanced stages the torch warm-up count leaves zero slack in the steady state, so every stage-to-stage transfer
+    latency lands on the critical path once per micro-batch; one more forward in flight gives the neighbours' messages
+    a whole action of slack at the price of one more stashed micro-batch per rank.  0 reproduces torch exactly."""
     m = n_microbatches
     if m < pp_size:
         raise ValueError(f"1F1B needs n_microbatches ({m}) >= number of stages ({pp_size})")
     order: Order = {}
     for r in range(pp_size):
-        warm = min(m, pp_size - r)
+        warm = min(m, pp_size - r + (extra_warmup if r < pp_size - 1 else 0))
         acts = [Action(r, T.F, i) for i in range(warm)]
         f, b = warm, 0
         while b < m:
@@ -461,7 +466,7 @@ def theoretical_bubble(pp_size: int, n_microbatches: int, n_virtual: int = 1) ->
 
 
 def build_schedule(name: str, pp_size: int, n_microbatches: int, n_virtual: int = 1, dp_allreduce: bool = False,
-                   with_optimizer: bool = True, keep_fsdp_slots: bool = False) -> Order:
+                   with_optimizer: bool = True, keep_fsdp_slots: bool = False, extra_warmup: int = 0) -> Order:
     """Full lowering for one of 'GPipe' | '1F1B' | 'Interleaved1F1B' (names of helper:215-219)."""
     if name == "GPipe":
         if n_virtual != 1:
@@ -470,7 +475,7 @@ def build_schedule(name: str, pp_size: int, n_microbatches: int, n_virtual: int 
     elif name == "1F1B":
         if n_virtual != 1:
             raise ValueError("1F1B runs one stage per rank")
-        order = one_f_one_b_order(pp_size, n_microbatches)
+        order = one_f_one_b_order(pp_size, n_microbatches, extra_warmup)
     elif name == "Interleaved1F1B":
         order = interleaved_order(pp_size, n_virtual, n_microbatches)
     elif name == "ZeroBubble1F1B":
