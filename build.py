@@ -134,6 +134,66 @@ def dump_sass() -> None:
             tot = sum(hist.values())
             f.write(f"| `{k[:110]}` | {tot} | " + " | ".join(str(hist.get(x, 0)) for x in keys) + " |\n")
     print(f"wrote {out_dir}/summary.md ({len(kernels)} kernels)")
+    dump_listings(out_dir)
+
+
+# one representative instantiation per kernel family: full `cuobjdump -sass` listing, committed under docs/sass/
+LISTINGS = {
+    "gemm_fwd_bn256": "gemm_tcgen05_kernelILi256ELb0ELb0ELi0EE",
+    "gemm_wgrad_bn256_accum": "gemm_tcgen05_kernelILi256ELb1ELb1ELi2EE",
+    "gemm_pair_fwd_bn256": "gemm_tcgen05_pair_kernelILi256ELb0ELb0ELi0EE",
+    "gemm_pair_dgrad_bn256": "gemm_tcgen05_pair_kernelILi256ELb0ELb1ELi0EE",
+    "k10_gemm_allreduce_bn256": "gemm_tcgen05_allreduce_kernelILi256EE",
+    "k11_gemm_reducescatter_bn256": "gemm_tcgen05_rs_kernelILi256ELb0EE",
+    "k11_gemm_reducescatter_pair_bn256": "gemm_tcgen05_rs_pair_kernelILi256ELb0EE",
+    "k12_allgather_fused_bn256": "gemm_tcgen05_agfused_kernelILi256ELb0EE",
+    "k12_allgather_fused_pair_bn256": "gemm_tcgen05_agfused_pair_kernelILi256ELb0EE",
+    "attn_fwd_dh64": "attn_fwd_kernelILi64ELi64ELi2ELi1EE",
+    "attn_bwd_dh64": "attn_bwd_kernelILi64ELi64EE",
+    "ln_bwd_d1024": "ln_bwd_kernelILi128EE",
+    "ln_fwd_d1024": "ln_fwd_kernelILi4EE",
+    "xent": "xent_fwd_bwd_kernelILb1EE",
+    "adamw": "adamw_kernel",
+}
+
+
+def dump_listings(out_dir: str) -> None:
+    names = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True).stdout
+    funcs = [l.split(":", 1)[1].strip() for l in names.splitlines() if l.strip().startswith("Function :")]
+    index = ["# Full SASS listings (cuobjdump -sass), one representative instantiation per kernel family\n",
+             "Regenerate with `python build.py --sass`.  `UTCHMMA` = tcgen05.mma (`.2CTA` = cta_group::2), `UTMALDG` / `UTMASTG` /",
+             "`UTMAREDG` = TMA load / store / reduce, `UBLKCP` = 1-D bulk copy (the all-gather copier), `LDTM` / `STTM` = tcgen05.ld / st,",
+             "`UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier.\n", "| listing | kernel | instructions | UTCHMMA | UTMALDG | UTMASTG | UTMAREDG | UBLKCP | LDTM | HMMA |", "|---|---|---|---|---|---|---|---|---|---|"]
+    for short, pat in LISTINGS.items():
+        match = [f for f in funcs if pat in f]
+        if not match:
+            continue
+        r = subprocess.run(["cuobjdump", "-sass", "-fun", match[0], LIB], capture_output=True, text=True)
+        # keep the function's instruction stream only: address + instruction, without the encoding words and fatbin headers
+        import re
+        lines, on = [], False
+        for l in r.stdout.splitlines():
+            if "Function :" in l:
+                on = True
+                lines.append(l.strip())
+                continue
+            if not on:
+                continue
+            mm = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);\s*/\*", l)
+            if mm:
+                lines.append(f"/*{mm.group(1)}*/  {mm.group(2)} ;")
+            elif l.strip().startswith(".") and ":" in l:
+                lines.append(l.strip())
+        with open(os.path.join(out_dir, short + ".sass"), "w") as f:
+            f.write("\n".join(lines) + "\n")
+        ops = [re.sub(r"^@!?U?P\d+\s+", "", l.split("*/", 1)[1].strip()).split()[0] for l in lines[1:] if l.startswith("/*")]
+        cnt = lambda op: sum(1 for o in ops if o.startswith(op))   # noqa: E731
+        n_instr = len(ops)
+        index.append(f"| [{short}.sass]({short}.sass) | `{match[0][:70]}` | {n_instr} | {cnt('UTCHMMA')} | {cnt('UTMALDG')} | "
+                     f"{cnt('UTMASTG')} | {cnt('UTMAREDG')} | {cnt('UBLKCP')} | {cnt('LDTM')} | {cnt('HMMA')} |")
+    with open(os.path.join(out_dir, "README.md"), "w") as f:
+        f.write("\n".join(index) + "\n")
+    print(f"wrote {len(LISTINGS)} listings to {out_dir}")
 
 
 if __name__ == "__main__":

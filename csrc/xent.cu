@@ -46,6 +46,9 @@ __device__ __forceinline__ float block_reduce_sum(float v, float* red) {
 }
 
 // USE_SMEM: the row is cached in shared memory; otherwise it is re-read from global/L2.
+// Two sweeps over the row instead of three: the first one loads it, keeps a per-thread ONLINE (max, sum-exp) pair --
+// one rescale per 8-element chunk, no bounds checks except in the last chunk -- and the block combines the pairs;
+// the second one turns the cached row into the gradient.  exp2 on log2(e)-prescaled logits: one FFMA + one MUFU.
 template <bool USE_SMEM>
 __global__ void __launch_bounds__(XE_THREADS) xent_fwd_bwd_kernel(bf16* __restrict__ logits, long long ld,
                                                                    const long long* __restrict__ targets,
@@ -58,60 +61,75 @@ __global__ void __launch_bounds__(XE_THREADS) xent_fwd_bwd_kernel(bf16* __restri
   if (row >= T) return;
   bf16* grow = logits + (long long)row * ld;
   const int nchunks = (V + 7) >> 3;  // ld is a multiple of 8, so reading the padded tail chunk is in-bounds
+  const int tail_valid = V - (nchunks - 1) * 8;   // valid elements of the last chunk (1..8)
   const float LOG2E = 1.4426950408889634f;
 
-  float mx = -INFINITY;
+  float m_t = -INFINITY, s_t = 0.f;   // running max (log2 domain) and sum of exp2(y - m_t) of this thread's chunks
   for (int c = threadIdx.x; c < nchunks; c += XE_THREADS) {
     const uint4 u = *reinterpret_cast<const uint4*>(grow + c * 8);
     if (USE_SMEM) *reinterpret_cast<uint4*>(srow + c * 8) = u;
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+    float y[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float2 f = unpack_bf16(w[q]);
-      const int e = c * 8 + 2 * q;
-      if (e < V) mx = fmaxf(mx, f.x);
-      if (e + 1 < V) mx = fmaxf(mx, f.y);
+      y[2 * q] = f.x * LOG2E;
+      y[2 * q + 1] = f.y * LOG2E;
     }
+    if (c == nchunks - 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j >= tail_valid) y[j] = -INFINITY;
+    }
+    const float cm = fmaxf(fmaxf(fmaxf(y[0], y[1]), fmaxf(y[2], y[3])), fmaxf(fmaxf(y[4], y[5]), fmaxf(y[6], y[7])));
+    if (cm > m_t) {                    // rare after the first few chunks
+      s_t *= exp2f(m_t - cm);          // m_t = -inf on the first chunk: exp2(-inf) = 0, s_t stays 0
+      m_t = cm;
+    }
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) {
+      a0 += exp2f(y[j] - m_t);
+      a1 += exp2f(y[j + 1] - m_t);
+    }
+    s_t += a0 + a1;
   }
-  mx = block_reduce_max(mx, red);  // (contains the __syncthreads that publishes srow)
+  const float mx2 = block_reduce_max(m_t, red);  // (contains the __syncthreads that publishes srow)
+  const float se = block_reduce_sum(m_t == -INFINITY ? 0.f : s_t * exp2f(m_t - mx2), red);
   const bf16* src = USE_SMEM ? srow : grow;
-  float se = 0.f;
-  for (int c = threadIdx.x; c < nchunks; c += XE_THREADS) {
-    const uint4 u = *reinterpret_cast<const uint4*>(src + c * 8);
-    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float2 f = unpack_bf16(w[q]);
-      const int e = c * 8 + 2 * q;
-      if (e < V) se += exp2f((f.x - mx) * LOG2E);
-      if (e + 1 < V) se += exp2f((f.y - mx) * LOG2E);
-    }
-  }
-  se = block_reduce_sum(se, red);
   const long long tgt = targets[row];
+  const bool has_tgt = tgt >= 0 && tgt < V;
   if (threadIdx.x == 0) {
-    const float lt = (tgt >= 0 && tgt < V) ? __bfloat162float(src[tgt]) : mx;
-    row_loss[row] = (tgt >= 0 && tgt < V) ? (logf(se) + mx - lt) : 0.f;
+    const float lt2 = has_tgt ? __bfloat162float(src[tgt]) * LOG2E : mx2;
+    row_loss[row] = has_tgt ? (log2f(se) + mx2 - lt2) * 0.6931471805599453f : 0.f;
   }
   if (!write_grad) return;
   if (!USE_SMEM) __syncthreads();  // thread 0 has read the target logit before the row is overwritten in place
-  const float inv = (tgt >= 0 && tgt < V) ? grad_scale / se : 0.f;  // ignored rows get zero gradient
-  const float gs = (tgt >= 0 && tgt < V) ? grad_scale : 0.f;
+  const float inv = has_tgt ? grad_scale / se : 0.f;  // ignored rows get zero gradient
+  const float gs = has_tgt ? grad_scale : 0.f;
+  const int tgt_chunk = has_tgt ? (int)(tgt >> 3) : -1;
   for (int c = threadIdx.x; c < nchunks; c += XE_THREADS) {
     const uint4 u = *reinterpret_cast<const uint4*>(src + c * 8);
     const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-    uint32_t o[4];
+    float g[8];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const float2 f = unpack_bf16(w[q]);
-      const int e = c * 8 + 2 * q;
-      float gx = (e < V) ? exp2f((f.x - mx) * LOG2E) * inv : 0.f;
-      float gy = (e + 1 < V) ? exp2f((f.y - mx) * LOG2E) * inv : 0.f;
-      if (e == tgt) gx -= gs;
-      if (e + 1 == tgt) gy -= gs;
-      o[q] = pack_bf16(gx, gy);
+      g[2 * q] = exp2f(fmaf(f.x, LOG2E, -mx2)) * inv;
+      g[2 * q + 1] = exp2f(fmaf(f.y, LOG2E, -mx2)) * inv;
     }
-    *reinterpret_cast<uint4*>(grow + c * 8) = make_uint4(o[0], o[1], o[2], o[3]);
+    if (c == tgt_chunk) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j == (int)(tgt & 7)) g[j] -= gs;
+    }
+    if (c == nchunks - 1) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (j >= tail_valid) g[j] = 0.f;
+    }
+    *reinterpret_cast<uint4*>(grow + c * 8) =
+        make_uint4(pack_bf16(g[0], g[1]), pack_bf16(g[2], g[3]), pack_bf16(g[4], g[5]), pack_bf16(g[6], g[7]));
   }
 }
 
