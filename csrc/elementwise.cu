@@ -204,6 +204,19 @@ __global__ void __launch_bounds__(256) push_add_kernel(const float* __restrict__
   }
 }
 
+// NVLS variant: ONE multimem.red per 16 bytes adds the value into every replica's buffer inside the NVSwitch (the
+// destination is the multicast address of the replicas' symmetric buffers), so each GPU sends its gradient once
+// instead of once per peer.  Used for data-parallel degrees >= 4, where the per-peer pushes would multiply the bytes.
+__global__ void __launch_bounds__(256) push_add_multimem_kernel(const float* __restrict__ src, float* mc_dst, long long n4,
+                                                                float scale) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = reinterpret_cast<const float4*>(src)[i];
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_dst + 4 * i),
+                 "f"(v.x * scale), "f"(v.y * scale), "f"(v.z * scale), "f"(v.w * scale)
+                 : "memory");
+  }
+}
+
 static int ew_grid(long long work_items) {
   long long b = (work_items + 255) / 256;
   const long long cap = (long long)sm_count() * 8;
@@ -312,6 +325,16 @@ extern "C" int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_d
   return 0;
 }
 
+
+extern "C" int ppb_push_add_multimem_f32(const float* src, void* mc_dst, long long n, float scale, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  PPB_REQUIRE(mc_dst != nullptr && (reinterpret_cast<uintptr_t>(mc_dst) % 16) == 0, "ppb_push_add_multimem_f32: need a 16-byte aligned multicast address");
+  PPB_REQUIRE(n >= 0 && (n % 4) == 0, "ppb_push_add_multimem_f32: element count must be a multiple of 4");
+  if (n == 0) return 0;
+  push_add_multimem_kernel<<<ew_grid(n / 4), 256, 0, stream>>>(src, reinterpret_cast<float*>(mc_dst), n / 4, scale);
+  PPB_CUDA_OK(cudaGetLastError());
+  return 0;
+}
 
 extern "C" int ppb_add_dropout_fwd(const void* resid, const void* a, void* z, long long n, float dropout_p,
                                    unsigned long long seed, void* stream_) {

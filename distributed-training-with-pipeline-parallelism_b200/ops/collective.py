@@ -29,6 +29,8 @@ def _bind(lib) -> None:
     lib.ppb_gemm_allreduce_bf16.restype = I
     lib.ppb_push_add_f32.argtypes = [P, P, I, L, F, P]
     lib.ppb_push_add_f32.restype = I
+    lib.ppb_push_add_multimem_f32.argtypes = [P, P, L, F, P]
+    lib.ppb_push_add_multimem_f32.restype = I
     lib._ppb_collective_bound = True
 
 
@@ -69,6 +71,16 @@ def push_add(src: torch.Tensor, dst_ptrs: List[int], scale: float) -> None:
     _lib.count_launch()
 
 
+def push_add_multimem(src: torch.Tensor, mc_ptr: int, scale: float) -> None:
+    """NVLS push: every replica's buffer behind the multicast address ``mc_ptr`` += scale * src (fp32, numel % 4 == 0),
+    reduced inside the NVSwitch (``multimem.red``)."""
+    lib = _lib.load(required=True)
+    _bind(lib)
+    rc = lib.ppb_push_add_multimem_f32(src.data_ptr(), mc_ptr, src.numel(), float(scale), torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "ppb_push_add_multimem_f32")
+    _lib.count_launch()
+
+
 class FusedGradAllReduce:
     """Per-stage state of the fused DP gradient reduction.
 
@@ -96,6 +108,12 @@ class FusedGradAllReduce:
         self.world = self.hdl.world_size
         self.rank = self.hdl.rank
         self.base_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        # NVLS: with >= 4 replicas the non-GEMM gradients go through ONE multimem.red stream (in-switch reduction) instead of
+        # one push per peer; PPB_FUSED_DP_NVLS=1 / 0 forces it on / off (needs the multicast mapping of the symmetric buffer)
+        import os
+        mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+        want = os.environ.get("PPB_FUSED_DP_NVLS")
+        self.mc_ptr = mc if (mc and (want == "1" or (want is None and self.world >= 4))) else 0
         self.armed = False
         self.covered: List[Tuple[int, int]] = []
         torch.cuda.synchronize(dev)
@@ -125,7 +143,10 @@ class FusedGradAllReduce:
                 lo, hi = pos, off
                 hi = min(self.n_total, (hi + 3) // 4 * 4)
                 if hi > lo:
-                    push_add(self.grad[lo:hi], [p + 4 * lo for p in self.base_ptrs], 1.0)
+                    if self.mc_ptr and lo % 4 == 0:
+                        push_add_multimem(self.grad[lo:hi], self.mc_ptr + 4 * lo, 1.0)
+                    else:
+                        push_add(self.grad[lo:hi], [p + 4 * lo for p in self.base_ptrs], 1.0)
             pos = max(pos, off + n)
         self.hdl.barrier(channel=0)
 

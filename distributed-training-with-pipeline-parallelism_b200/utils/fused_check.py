@@ -176,5 +176,34 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     out["k10_wgrad_allreduce"] = {"ms": round(ms, 4), "nccl_ms": round(base, 4), "frac_roofline": round(roof / ms, 3),
                                   "max_rel_err": round(_max_over(group, dev, err), 5), "params": total, "tokens": T, "dp": tp,
                                   "baseline": "cuBLAS matmul + add into the fp32 gradient, then ncclAllReduce of the bucket"}
+    # NVLS form of the same reduction: plain accumulating weight-gradient GEMMs, then ONE multimem.red stream over the bucket
+    # (every GPU sends each gradient byte once; the NVSwitch adds it into every replica) -- the dp >= 4 path of the non-GEMM
+    # gradients, timed here over the whole bucket
+    mc = int(getattr(fin.hdl, "multicast_ptr", 0) or 0)
+    if mc:
+        from ..ops.collective import push_add_multimem
+
+        def k10_nvls():
+            off = 0
+            for o, i in shapes:
+                F.linear_wgrad(dys[o], xin[i], accum[off:off + o * i].view(o, i))
+                off += o * i
+            push_add_multimem(accum, mc, 1.0)
+            fin.barrier(0)
+
+        accum.zero_()
+        fin.tensor.zero_()
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group, device_ids=[dev.index])
+        k10_nvls()
+        torch.cuda.synchronize(dev)
+        err = ((fin.tensor[:o0 * i0].view(o0, i0) - ref).norm() / ref.norm()).item()
+        ms = _timed(k10_nvls, group, dev)
+        roof_nvls = max(2.0 * T * total / peak, total * 4 / link) * 1e3
+        out["k10_nvls_multimem_push"] = {"ms": round(ms, 4), "nccl_ms": round(base, 4), "frac_roofline": round(roof_nvls / ms, 3),
+                                         "max_rel_err": round(_max_over(group, dev, err), 5), "dp": tp,
+                                         "note": "accumulating wgrad GEMMs + one multimem.red pass over the bucket (in-switch reduction)"}
+    else:
+        out["k10_nvls_multimem_push"] = {"unavailable": "the symmetric-memory handle exposes no multicast address on this box"}
     out["denominators"] = {"bf16_tflops_measured": round(peak / 1e12, 1), "nvlink_gbs_per_direction": NVLINK_GBS}
     return out

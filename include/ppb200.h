@@ -93,6 +93,10 @@ int ppb_gemm_allgather_fused_bf16(void* const* a_shards, void* full, unsigned in
 int ppb_gemm_reducescatter_bf16(const void* A, const void* B, void* const* dst_shards, int M, int N, int K,
                                 long long lda, long long ldb, long long ldc, int tp, int b_mn_major, void* stream);
 int ppb_push_add_f32(const float* src, void* const* dst_ptrs, int n_dst, long long n, float scale, void* stream);
+/* NVLS form of the push: mc_dst is the MULTICAST address of the replicas' symmetric buffers; one multimem.red per 16
+ * bytes adds scale * src into every replica inside the NVSwitch, so a GPU sends each gradient byte once whatever the
+ * data-parallel degree (the per-peer push sends it dp-1 times).  n % 4 == 0. */
+int ppb_push_add_multimem_f32(const float* src, void* mc_dst, long long n, float scale, void* stream);
 
 /* ---- K5: fused residual-add + dropout + LayerNorm / RMSNorm ------------------------------------------------
  * fwd: z = resid + dropout(a); y = norm(z)*gamma(+beta).  Either of resid / a may be NULL; z, mean may be NULL.

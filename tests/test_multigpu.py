@@ -58,3 +58,15 @@ def test_tensor_parallel_stage_matches_single_gpu(act):
     assert abs(res["loss_tp"] - res["loss_ref"]) < 5e-3 * abs(res["loss_ref"]), res
     assert res["grad_rel_err_max"] < 3e-2, res          # bf16 activations, different GEMM tilings / summation orders
     assert res["train_tp"][-1] < res["train_tp"][0] and abs(res["train_tp"][-1] - res["train_ref"][-1]) < 0.05, res
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_fused_collective_kernels_over_nvlink_with_sentinels():
+    """K10 / K11 / K12 against torch + NCCL over real peers, and the NaN-sentinel / changing-input check of the fused
+    all-gather's panel counters (a missed signal or a stale epoch cannot pass)."""
+    out = _torchrun(2, [os.path.join(ROOT, "tests", "_mgpu_fused_check.py")])
+    res = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+    assert res["k12_allgather_gemm"]["max_rel_err"] < 1e-2 and res["k12_allgather_gemm"]["gathered_copy_exact"], res
+    assert res["k11_gemm_reducescatter"]["max_rel_err"] < 1e-2, res
+    assert res["k10_wgrad_allreduce"]["max_rel_err"] < 1e-2, res
+    assert res["sentinel"]["max_rel_err"] < 1e-2 and res["sentinel"]["gathered_exact_and_finite_on_all_ranks"], res
