@@ -300,23 +300,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           ls2 += pr[i + 2];
           ls3 += pr[i + 3];
         }
+        // bf16 pairs first, then probability dropout as ONE half2 compare + ONE AND per pair (drop_pair_mask); kept
+        // probabilities are NOT rescaled here: the constant 1/(1-p) is folded into the final 1/l
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pk[i] = pack_bf16(pr[2 * i], pr[2 * i + 1]);
         if (p.drop_thresh) {
-          // kept probabilities are NOT rescaled here: the constant 1/(1-p) is folded into the final 1/l
           const DropoutStream ds(seed_eff, (drop_row + (unsigned long long)(kv0 + c * 32)) >> 1);
           if (ds.nowrap(16)) {
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const DropPair hsh = ds.bits_nowrap(i >> 1);
-              pr[i] = (hsh.a >= p.drop_thresh) ? pr[i] : 0.f;
-              pr[i + 1] = (hsh.b >= p.drop_thresh) ? pr[i + 1] : 0.f;
-            }
+            for (int i = 0; i < 16; ++i) pk[i] &= drop_pair_mask(ds.word_nowrap(i), p.drop_thresh);
           } else {
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const DropPair hsh = ds.bits(i >> 1);
-              pr[i] = (hsh.a >= p.drop_thresh) ? pr[i] : 0.f;
-              pr[i + 1] = (hsh.b >= p.drop_thresh) ? pr[i + 1] : 0.f;
-            }
+            for (int i = 0; i < 16; ++i) pk[i] &= drop_pair_mask(ds.word(i), p.drop_thresh);
           }
         }
         const int col = half * COLS + c * 32;   // first kv column (within the 128-wide tile) of this chunk
@@ -325,9 +321,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int q = 0; q < 4; ++q) {
           const uint32_t cc = ((col & 63) >> 3) + q;
           const uint32_t dst = atom + ((cc ^ (row & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack_bf16(pr[8 * q], pr[8 * q + 1])),
-                       "r"(pack_bf16(pr[8 * q + 2], pr[8 * q + 3])), "r"(pack_bf16(pr[8 * q + 4], pr[8 * q + 5])),
-                       "r"(pack_bf16(pr[8 * q + 6], pr[8 * q + 7]))
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                       "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
                        : "memory");
         }
       }

@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -348,51 +349,77 @@ __host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
   x ^= x >> 16;
   return x;
 }
-// One hash per PAIR of elements.  The pair index is folded with the seed (the high word goes through a full mix32,
-// which callers hoist out of inner loops), scrambled with a multiply-xorshift round, and two different odd
-// multipliers produce one 32-bit word per element; element e of the pair is kept iff its word >= thr32, where
-// thr32 = round(p * 65536) << 16 (the decision only looks at the top 16 bits, i.e. a 2^-16 resolution of p).
+// One hash per PAIR of elements, built so that a run of consecutive pairs costs four integer instructions per pair:
+//   x = (lo + K) * C1      K = k0 ^ mix32(hi ^ k1 ^ golden): constant while the high word of the pair index is; for a
+//                          run lo0, lo0+1, ... this is base + i*C1 with i*C1 a compile-time constant (a Weyl sequence)
+//   x ^= x >> 15 ;  y = x * C2                                  (one xorshift-multiply round on top of it)
+// The even element of the pair uses the LOW 16 bits of y, the odd element the HIGH 16 bits.  From each half 13 bits
+// survive: 0x3BFF clears bit 15 and bit 10, OR 0x4000 sets bit 14, which makes every half the bit pattern of a
+// POSITIVE, NORMAL fp16 number whose order as a float equals its order as an integer.  An element is kept iff its
+// pattern >= the threshold pattern (resolution 2^-13 of p).  Kernels that hold values in fp32 compare the two patterns
+// as 32-bit integers (DropPair); kernels that hold packed bf16x2 / fp16x2 values get both decisions of a pair from ONE
+// half2 compare and apply them with ONE bitwise AND (drop_pair_mask).  The python reference in ops/reference.py
+// implements the same integer function bit-for-bit.
+constexpr uint32_t DROP_C1 = 0x9E3779B1U, DROP_C2 = 0x85EBCA77U;
+constexpr uint32_t DROP_KEEP_BITS = 0x3BFF3BFFU, DROP_SET_BITS = 0x40004000U;
 struct DropPair {
-  uint32_t a, b;  // word for the even / odd element of the pair
+  uint32_t a, b;  // pattern (in the top 16 bits) for the even / odd element of the pair
 };
-__host__ __device__ __forceinline__ DropPair drop_pair_from(uint32_t x) {
-  x *= 0x9E3779B1U;
+__host__ __device__ __forceinline__ uint32_t drop_pair_word(uint32_t x) {   // x = (lo + K) * C1
   x ^= x >> 15;
+  return ((x * DROP_C2) & DROP_KEEP_BITS) | DROP_SET_BITS;
+}
+__host__ __device__ __forceinline__ DropPair drop_pair_from(uint32_t x) {
+  const uint32_t w = drop_pair_word(x);
   DropPair r;
-  r.a = x * 0x85EBCA77U;
-  r.b = x * 0xC2B2AE3DU;
+  r.a = w << 16;
+  r.b = w & 0xFFFF0000U;
   return r;
 }
-__host__ __device__ __forceinline__ DropPair dropout_pair_bits(uint64_t seed, uint64_t pair_idx) {
-  uint32_t lo = uint32_t(pair_idx), hi = uint32_t(pair_idx >> 32);
-  uint32_t k0 = uint32_t(seed), k1 = uint32_t(seed >> 32);
-  return drop_pair_from((lo ^ k0) + mix32(hi ^ k1 ^ 0x9e3779b9U));
+__host__ __device__ __forceinline__ uint32_t drop_pair_key(uint64_t seed, uint32_t hi) {
+  return uint32_t(seed) ^ mix32(hi ^ uint32_t(seed >> 32) ^ 0x9e3779b9U);
 }
-// Fast path for runs of consecutive pair indices: the mixing of the high word is hoisted out of the inner loop.
+__host__ __device__ __forceinline__ DropPair dropout_pair_bits(uint64_t seed, uint64_t pair_idx) {
+  return drop_pair_from((uint32_t(pair_idx) + drop_pair_key(seed, uint32_t(pair_idx >> 32))) * DROP_C1);
+}
+// Fast path for runs of consecutive pair indices: the keyed base is hoisted out of the inner loop.
 // bits(i) == dropout_pair_bits(seed, pair0 + i) for every i < 2^32, including across a low-word wrap.
 struct DropoutStream {
-  uint32_t k0, lo0, inner, inner_next;
+  uint32_t lo0, base, base_next;
   __device__ __forceinline__ DropoutStream(uint64_t seed, uint64_t pair0) {
-    k0 = uint32_t(seed);
     lo0 = uint32_t(pair0);
-    const uint32_t k1 = uint32_t(seed >> 32), hi = uint32_t(pair0 >> 32);
-    inner = mix32(hi ^ k1 ^ 0x9e3779b9U);
-    inner_next = mix32((hi + 1u) ^ k1 ^ 0x9e3779b9U);
+    const uint32_t hi = uint32_t(pair0 >> 32);
+    base = (lo0 + drop_pair_key(seed, hi)) * DROP_C1;
+    base_next = (lo0 + drop_pair_key(seed, hi + 1u)) * DROP_C1;
   }
   __device__ __forceinline__ DropPair bits(uint32_t i) const {
-    const uint32_t lo = lo0 + i;
-    return drop_pair_from((lo ^ k0) + (lo < lo0 ? inner_next : inner));
+    return drop_pair_from(((lo0 + i) < lo0 ? base_next : base) + i * DROP_C1);
   }
-  // true when indices [0, n) stay inside one value of the high word, so bits_nowrap() may be used
+  // true when indices [0, n) stay inside one value of the high word, so the *_nowrap() forms may be used
   __device__ __forceinline__ bool nowrap(uint32_t n) const { return lo0 + (n - 1u) >= lo0; }
-  __device__ __forceinline__ DropPair bits_nowrap(uint32_t i) const { return drop_pair_from(((lo0 + i) ^ k0) + inner); }
+  __device__ __forceinline__ DropPair bits_nowrap(uint32_t i) const { return drop_pair_from(base + i * DROP_C1); }
+  // both patterns of pair i in one word (low half = even element): input of drop_pair_mask
+  __device__ __forceinline__ uint32_t word_nowrap(uint32_t i) const { return drop_pair_word(base + i * DROP_C1); }
+  __device__ __forceinline__ uint32_t word(uint32_t i) const {
+    return drop_pair_word(((lo0 + i) < lo0 ? base_next : base) + i * DROP_C1);
+  }
 };
 
-__host__ __device__ __forceinline__ uint32_t dropout_thresh16(float p) {
-  float t = p * 65536.0f + 0.5f;
-  return t <= 0.f ? 0u : (t >= 65535.f ? 65535u : uint32_t(t));
+// threshold: keep iff 13-bit value >= T13 = round(p * 8192); as a pattern, with the same bit placement as the words
+__host__ __device__ __forceinline__ uint32_t dropout_thresh13(float p) {
+  float t = p * 8192.0f + 0.5f;
+  return t <= 0.f ? 0u : (t >= 8191.f ? 8191u : uint32_t(t));
 }
-__host__ __device__ __forceinline__ uint32_t dropout_thr32(float p) { return dropout_thresh16(p) << 16; }
+__host__ __device__ __forceinline__ uint32_t dropout_thr_pattern(float p) {
+  const uint32_t t = dropout_thresh13(p);
+  return 0x4000u | ((t >> 10) << 11) | (t & 0x3FFu);
+}
+__host__ __device__ __forceinline__ uint32_t dropout_thr32(float p) { return dropout_thr_pattern(p) << 16; }
+// 0xFFFF in each half of the result whose element is KEPT; `word` from DropoutStream::word*, thr32 from dropout_thr32
+__device__ __forceinline__ uint32_t drop_pair_mask(uint32_t word, uint32_t thr32) {
+  const uint32_t t2 = (thr32 >> 16) * 0x00010001u;
+  return __hge2_mask(*reinterpret_cast<const __half2*>(&word), *reinterpret_cast<const __half2*>(&t2));
+}
 // keep flag of element idx (idx even/odd selects low/high half of the pair hash)
 __host__ __device__ __forceinline__ bool dropout_keep(uint64_t seed, uint64_t idx, uint32_t thr32) {
   const DropPair h = dropout_pair_bits(seed, idx >> 1);

@@ -24,26 +24,33 @@ def _mix32(x: torch.Tensor) -> torch.Tensor:
     return x
 
 
-def dropout_thresh16(p: float) -> int:
-    t = p * 65536.0 + 0.5
-    return 0 if t <= 0 else (65535 if t >= 65535 else int(t))
+def dropout_thresh13(p: float) -> int:
+    t = p * 8192.0 + 0.5
+    return 0 if t <= 0 else (8191 if t >= 8191 else int(t))
+
+
+def dropout_thr_pattern(p: float) -> int:
+    """Threshold as the 16-bit pattern the kernels compare against (csrc/common.cuh: bit 14 set, bits 15 and 10 clear)."""
+    t = dropout_thresh13(p)
+    return 0x4000 | ((t >> 10) << 11) | (t & 0x3FF)
 
 
 def dropout_keep_mask(seed: int, start: int, numel: int, p: float, device=None) -> torch.Tensor:
-    """keep[i] for flat element indices start .. start+numel-1 (bool); bit-identical to ppb::dropout_keep."""
-    thresh = dropout_thresh16(p)
+    """keep[i] for flat element indices start .. start+numel-1 (bool); bit-identical to ppb::dropout_keep:
+    one hash per pair of elements, x = (lo + (k0 ^ mix32(hi ^ k1 ^ golden))) * C1, x ^= x >> 15, y = x * C2; the even
+    element takes the low 16 bits of y, the odd one the high 16 bits; 13 bits of each half are compared with the
+    threshold (effective dropout probability round(p * 8192) / 8192)."""
+    thr = dropout_thr_pattern(p)
     idx = torch.arange(start, start + numel, dtype=torch.int64, device=device)
     pair = idx >> 1
     lo, hi = pair & _M32, (pair >> 32) & _M32
     k0, k1 = seed & _M32, (seed >> 32) & _M32
-    inner = _mix32(hi ^ ((k1 ^ 0x9E3779B9) & _M32))
-    x = ((lo ^ k0) + inner) & _M32
-    x = (x * 0x9E3779B1) & _M32
+    key = k0 ^ _mix32(hi ^ ((k1 ^ 0x9E3779B9) & _M32))
+    x = ((lo + key) & _M32) * 0x9E3779B1 & _M32
     x = x ^ (x >> 15)
-    a = (x * 0x85EBCA77) & _M32
-    b = (x * 0xC2B2AE3D) & _M32
-    word = torch.where((idx & 1) == 1, b, a)
-    return (word >> 16) >= thresh
+    y = (x * 0x85EBCA77) & _M32
+    half = torch.where((idx & 1) == 1, y >> 16, y & 0xFFFF)
+    return ((half & 0x3BFF) | 0x4000) >= thr
 
 
 def dropout(x: torch.Tensor, p: float, seed: int, index_offset: int = 0) -> torch.Tensor:

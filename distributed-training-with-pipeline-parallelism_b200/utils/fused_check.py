@@ -67,6 +67,12 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     peak = _peak_tflops() * 1e12
     link = NVLINK_GBS * 1e9
     out: Dict[str, dict] = {}
+    verbose = os.environ.get("PPB_FUSED_CHECK_VERBOSE", "0") == "1"
+
+    def note(msg: str) -> None:
+        if verbose and rank == 0:
+            print(f"[fused_check tp={tp}] {msg}", flush=True)
+
     g = torch.Generator(device="cpu").manual_seed(1234)
     T = tokens if not small else 512
     rows = T // tp
@@ -96,8 +102,10 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
         dist.all_gather_into_tensor(xg, xs, group=group)
         return torch.matmul(xg, w1.t())
 
+    note("k12 first call")
     k12()
     torch.cuda.synchronize(dev)
+    note("k12 done once")
     ref = x[:256].float() @ w1.float().t()
     err = ((y[:256].float() - ref).norm() / ref.norm()).item()
     gathered_ok = bool(torch.equal(full, x))
@@ -124,8 +132,10 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     def k11_base():
         dist.reduce_scatter_tensor(yo, torch.matmul(h, w2.t()), group=group)
 
+    note("k11 first call")
     k11()
     torch.cuda.synchronize(dev)
+    note("k11 done once")
     part = (h.float() @ w2.float().t())
     dist.all_reduce(part, group=group)
     ref = part[rank * rows:(rank + 1) * rows]
@@ -165,8 +175,10 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     fin.tensor.zero_()
     torch.cuda.synchronize(dev)
     dist.barrier(group=group, device_ids=[dev.index])
+    note("k10 first call")
     k10()
     torch.cuda.synchronize(dev)
+    note("k10 done once")
     o0, i0 = shapes[0]
     ref = dys[o0].float().t() @ xin[i0].float()
     dist.all_reduce(ref, group=group)
@@ -195,8 +207,10 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
         fin.tensor.zero_()
         torch.cuda.synchronize(dev)
         dist.barrier(group=group, device_ids=[dev.index])
+        note("k10 nvls first call")
         k10_nvls()
         torch.cuda.synchronize(dev)
+        note("k10 nvls done once")
         err = ((fin.tensor[:o0 * i0].view(o0, i0) - ref).norm() / ref.norm()).item()
         ms = _timed(k10_nvls, group, dev)
         roof_nvls = max(2.0 * T * total / peak, total * 4 / link) * 1e3

@@ -326,7 +326,9 @@ def test_tensor_parallel_with_dropout_backward_matches_finite_differences(postln
     assert "error" not in res, res
     for r in res["ranks"]:
         assert r["reproducible"], r
-        assert abs(r["fd"] - r["pred"]) < 3e-2 * abs(r["pred"]) + 1e-4, r
+        # central differences with eps = 1e-3 cross a few ReLU kinks in the post-LN block (which masks are drawn decides how
+        # many): 3 % for the smooth pre-LN GELU block, 5 % for the ReLU block; mismatched forward / backward masks are >= 20 %
+        assert abs(r["fd"] - r["pred"]) < (5e-2 if postln else 3e-2) * abs(r["pred"]) + 1e-4, r
 
 
 @pytest.mark.parametrize("world,act", [(2, "relu"), (4, "gelu")])
