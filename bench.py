@@ -227,25 +227,15 @@ def run_ours(a, rank, local_rank, world):
     fused_paths = None
     if world > 1 and not a.no_fused_check and not a.small:
         pair = dist.new_group([0, 1])
-        quad = dist.new_group([0, 1, 2, 3]) if world >= 4 else None
         if rank < 2:
             try:
                 from ppb200.utils import fused_check
-                fused_paths = fused_check.run(pair, dev)
+                # (the NVLS multimem variant and the degree-4 run live in benchmarks/fused_paths_bench.py -> profiles/: inside
+                # a larger world the sub-group multicast set-up stalled once, and this check must never cost the bench line)
+                fused_paths = fused_check.run(pair, dev, nvls=False)
             except Exception as e:  # noqa: BLE001
                 fused_paths = {"error": f"{type(e).__name__}: {e}"[:300]}
         dist.barrier()
-        if quad is not None:      # the same three kernels at degree 4 (tp = 4 / dp = 4) on ranks 0-3
-            r4 = None
-            if rank < 4:
-                try:
-                    from ppb200.utils import fused_check
-                    r4 = fused_check.run(quad, dev)
-                except Exception as e:  # noqa: BLE001
-                    r4 = {"error": f"{type(e).__name__}: {e}"[:300]}
-            if rank == 0 and fused_paths is not None:
-                fused_paths["degree4"] = r4
-            dist.barrier()
     summ = {k: round(v, 3) for k, v in sched.summary().items()}
     summ["layers"] = [[f"{k}:{getattr(l, 'part', 'full')}" if getattr(l, 'part', 'full') != 'full' else k
                        for k, l in st.submod.layers.items()] for st in stages]

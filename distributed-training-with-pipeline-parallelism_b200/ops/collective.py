@@ -108,12 +108,12 @@ class FusedGradAllReduce:
         self.world = self.hdl.world_size
         self.rank = self.hdl.rank
         self.base_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
-        # NVLS: with >= 4 replicas the non-GEMM gradients go through ONE multimem.red stream (in-switch reduction) instead of
-        # one push per peer; PPB_FUSED_DP_NVLS=1 / 0 forces it on / off (needs the multicast mapping of the symmetric buffer)
+        # NVLS (opt-in, PPB_FUSED_DP_NVLS=1): the non-GEMM gradients go through ONE multimem.red stream (in-switch reduction)
+        # instead of one push per peer.  Measured standalone at dp = 4 (profiles/fused_paths_n4.json); not the default because
+        # a multicast mapping over a SUB-group of a larger job stalled once on this pool.
         import os
         mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
-        want = os.environ.get("PPB_FUSED_DP_NVLS")
-        self.mc_ptr = mc if (mc and (want == "1" or (want is None and self.world >= 4))) else 0
+        self.mc_ptr = mc if (mc and os.environ.get("PPB_FUSED_DP_NVLS") == "1") else 0
         self.armed = False
         self.covered: List[Tuple[int, int]] = []
         torch.cuda.synchronize(dev)

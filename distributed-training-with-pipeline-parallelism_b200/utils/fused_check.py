@@ -57,7 +57,7 @@ def _max_over(group, dev, v: float) -> float:
     return float(t.item())
 
 
-def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dict]:
+def run(group, device, tokens: int = 4096, small: bool = False, nvls: bool = True) -> Dict[str, dict]:
     from ..ops import functional as F
     from ..ops.collective import (GatherFlags, SymmetricBuffer, allgather_linear_fused, gemm_allreduce,
                                   linear_reducescatter)
@@ -192,7 +192,9 @@ def run(group, device, tokens: int = 4096, small: bool = False) -> Dict[str, dic
     # (every GPU sends each gradient byte once; the NVSwitch adds it into every replica) -- the dp >= 4 path of the non-GEMM
     # gradients, timed here over the whole bucket
     mc = int(getattr(fin.hdl, "multicast_ptr", 0) or 0)
-    if mc:
+    if not nvls:
+        pass
+    elif mc:
         from ..ops.collective import push_add_multimem
 
         def k10_nvls():
