@@ -121,7 +121,8 @@ def run_ours(a, rank, local_rank, world):
         # serialise every send/recv with every other op of the group)
         from ppb200.parallel.mesh import configure_nccl_for_pipeline
         configure_nccl_for_pipeline()
-        dist.init_process_group("nccl")
+        if not dist.is_initialized():    # (benchmarks/sweep_vs_reference.py runs many cells on one process group)
+            dist.init_process_group("nccl")
         mesh = init_mesh(dp_size=a.dp, pp_size=world // (a.dp * a.tp), tp_size=a.tp)
         pp_group, dp_group, pp_idx, dp_idx, P = mesh.pp_group, mesh.dp_group, mesh.pp_idx, mesh.dp_idx, mesh.pp_size
         pp_group_bwd = mesh.pp_group_bwd
@@ -270,7 +271,8 @@ def run_ours(a, rank, local_rank, world):
         })
     if world > 1:
         dist.barrier()
-        dist.destroy_process_group()
+        if not getattr(a, "keep_process_group", False):
+            dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------------------------------------------------------
@@ -313,7 +315,8 @@ def run_reference(a, rank, local_rank, world):
         os.environ.setdefault("MASTER_PORT", "29533")
         os.environ.setdefault("RANK", "0")
         os.environ.setdefault("WORLD_SIZE", "1")
-    dist.init_process_group("nccl", device_id=dev)
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
     # data parallelism is not in the helper (helper:178 creates a group it never uses): the DP baseline is the stock
     # torch composition SURVEY.md 6.4 names -- the helper's pruned stage module wrapped in DistributedDataParallel
     # (torch's PipelineStage drives no_sync for all but the last micro-batch), NCCL all-reduce of the gradients
@@ -451,7 +454,8 @@ def run_reference(a, rank, local_rank, world):
     finally:
         try:
             dist.barrier()
-            dist.destroy_process_group()
+            if not getattr(a, "keep_process_group", False):
+                dist.destroy_process_group()
         except Exception:  # noqa: BLE001
             pass
 

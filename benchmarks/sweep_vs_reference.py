@@ -4,6 +4,7 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
         benchmarks/sweep_vs_reference.py --out gpurun_out/sweep_nN.json [--microbatches 4,8,16,32,64] [--steps 3]
 
+One arm per launch (`--impl ours` / `--impl reference`; `benchmarks/sweep_merge.py` joins the two files into the table).
 For every schedule the reference selects (GPipe, 1F1B, Interleaved1F1B -- helper:215-220, nb:346-349) and every
 micro-batch count it runs `bench.run_ours` and `bench.run_reference` (the UNMODIFIED helper on NCCL + cuBLAS) with the
 same flags on the flagship model (BASELINE.json config 5) and records tokens/s of both, their ratio, the measured bubble
@@ -32,12 +33,24 @@ def main():
     ap.add_argument("--schedules", default="GPipe,1F1B,Interleaved1F1B")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--skip-reference", action="store_true")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"],
+                    help="one arm per launch: the process group is created once (lazily for ours, eagerly with device_id for the "
+                         "reference arm, exactly as bench.py does) and shared by all cells; merge the two JSON files afterwards")
     sa = ap.parse_args()
     rank, local_rank, world = bench.env_rank()
     sys.argv = [sys.argv[0]]
     base = bench.parse()
     base.gpus, base.steps, base.warmup, base.no_e2e, base.no_fused_check = world, sa.steps, sa.warmup, True, True
+    base.keep_process_group = True
+    import torch.distributed as dist
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    if sa.impl == "ours":
+        from ppb200.parallel.mesh import configure_nccl_for_pipeline
+        configure_nccl_for_pipeline()
+        dist.init_process_group("nccl")
+    else:
+        dist.init_process_group("nccl", device_id=dev)
     rows = []
     captured = []
     bench.emit = lambda obj: captured.append(obj)
@@ -50,7 +63,7 @@ def main():
             if sched == "Interleaved1F1B" and (m % world or m < world):
                 continue
             row = {"n_gpus": world, "schedule": sched, "n_microbatches": m}
-            for impl in (["ours"] if sa.skip_reference else ["ours", "reference"]):
+            for impl in [sa.impl]:
                 a = copy.copy(base)
                 a.schedule, a.microbatches, a.impl = sched, m, impl
                 a.virtual_stages = 2 if sched == "Interleaved1F1B" else 1
@@ -61,12 +74,8 @@ def main():
                     (bench.run_ours if impl == "ours" else bench.run_reference)(a, rank, local_rank, world)
                 except Exception as e:  # noqa: BLE001
                     row[impl + "_error"] = f"{type(e).__name__}: {e}"[:300]
-                    try:
-                        import torch.distributed as dist
-                        if dist.is_initialized():
-                            dist.destroy_process_group()
-                    except Exception:  # noqa: BLE001
-                        pass
+                    import traceback
+                    traceback.print_exc()
                 if rank == 0 and captured:
                     r = captured[-1]
                     if "value" in r:
@@ -84,8 +93,6 @@ def main():
                 gc.collect()
                 torch.cuda.empty_cache()
             if rank == 0:
-                if "ours_tok_s" in row and "reference_tok_s" in row:
-                    row["ratio"] = round(row["ours_tok_s"] / row["reference_tok_s"], 3)
                 rows.append(row)
                 print(json.dumps(row), flush=True)
                 os.makedirs(os.path.dirname(sa.out), exist_ok=True)
