@@ -23,7 +23,7 @@ import torch.distributed as dist
 
 from .models.tp import shard_model_for_tp
 from .parallel.mesh import configure_nccl_for_pipeline, init_mesh
-from .parallel.partition import build_stage_model
+from .parallel.partition import build_stage_model, calibrate, resolve_rule
 from .parallel.runner import make_schedule
 from .parallel.stage import PipelineStage
 from .utils import checkpoint
@@ -97,9 +97,14 @@ def main(argv: Optional[List[str]] = None) -> dict:
     v = cfg.virtual_stages if "Interleaved" in cfg.schedule else 1
     num_stages = cfg.pp * v
     stages = []
+    rule = cfg.partition
+    if rule in ("auto", "balanced", "fine") and use_cuda and num_stages > 1 and cfg.tp == 1:
+        # stage boundaries from unit times measured on this GPU (rank 0's numbers are used by every rank)
+        calibrate(margs, max(1, cfg.global_batch // cfg.dp // cfg.n_microbatches), cfg.seq_len, dev)
+    rule = resolve_rule(rule, margs.n_layers, num_stages, margs, cfg.seq_len, tp=cfg.tp)
     for i in range(v):
         sidx = pp_idx + cfg.pp * i
-        model = build_stage_model(margs, sidx, num_stages, rule=cfg.partition, seq_len=cfg.seq_len, device=dev, seed=cfg.seed)
+        model = build_stage_model(margs, sidx, num_stages, rule=rule, seq_len=cfg.seq_len, device=dev, seed=cfg.seed)
         if cfg.tp > 1:
             shard_model_for_tp(model, tp_idx, cfg.tp)
         st = PipelineStage(model, sidx, num_stages, dev, dp_group=groups.get("dp_group"), tp_group=tp_group)

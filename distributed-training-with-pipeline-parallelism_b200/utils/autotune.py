@@ -16,7 +16,7 @@ from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence
 
 from ..models import ModelArgs, preset
-from ..parallel.partition import stage_layer_parts
+from ..parallel.partition import layer_units, part_units, stage_layer_parts, unit_costs
 from ..parallel.schedule import ActionType as T, build_schedule, simulate, theoretical_bubble
 
 
@@ -58,11 +58,14 @@ def predict(args: ModelArgs, pp: int, schedule: str, n_microbatches: int, global
     """Simulated step of one configuration: {'ms', 'idle_critical', 'idle_max', 'theory', 'tokens_per_s'}."""
     c = costs or UnitCosts.from_model(args, seq_len)
     S = pp * n_virtual
+    # layer-equivalents per stage: unit shares from the partitioner's cost table (measured when calibrated, else its model)
+    uc, units = unit_costs(args, seq_len), layer_units(args)
+    layer_total = sum(uc[u] for u in units)
     weights = []
     for s in range(S):
         w = 0.0
         for _, part in stage_layer_parts(args.n_layers, S, s, rule, args, seq_len):
-            w += 1.0 if part == "full" else (c.attn_share if part == "attn" else 1.0 - c.attn_share)
+            w += sum(uc[u] for u in part_units(part, units)) / layer_total
         weights.append(w)
     scale = (global_batch / n_microbatches) * seq_len / 4096.0
 

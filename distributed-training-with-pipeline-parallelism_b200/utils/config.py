@@ -29,7 +29,7 @@ class RunConfig:
     backend: Optional[str] = None         # default: nccl on CUDA, gloo on CPU
     device: Optional[str] = None          # 'cuda' | 'cpu'
     dtype: str = "bf16"                   # 'bf16' (CUDA) | 'fp32'
-    partition: str = "reference"          # 'reference' (helper:70-75) | 'balanced'
+    partition: str = "reference"          # 'reference' (helper:70-75) | 'balanced' | 'fine' (sub-layer cuts) | 'auto' (measured unit times)
     lr: float = 1e-4
     weight_decay: float = 0.1
     beta1: float = 0.9

@@ -265,3 +265,27 @@ def test_zero_bubble_interleaved_is_valid_and_beats_both_parents(p, v, m):
     zb = simulate(build_schedule("ZeroBubble1F1B", p, m), p).makespan
     assert zbi < inter and zbi <= zb
     assert zbi <= 3 * m + (p - 1) / v + 1e-9 + 1.0 / v          # bubble of ZB-H1 divided by the number of chunks (+ one slot)
+
+
+def test_eager_1f1b_extra_warmup_is_valid_and_keeps_more_in_flight():
+    """`extra_warmup` forwards beyond torch's warm-up count: same actions, still deadlock-free, one more micro-batch in
+    flight on every rank but the last; 0 reproduces the torch order exactly."""
+    from ppb200.parallel.schedule import build_schedule, simulate
+    from ppb200.parallel.schedule.generate import one_f_one_b_order
+    from ppb200.parallel.schedule.ir import ActionType as T
+    assert one_f_one_b_order(4, 8, 0) == one_f_one_b_order(4, 8)
+    base, eager = build_schedule("1F1B", 4, 8), build_schedule("1F1B", 4, 8, extra_warmup=1)
+    for r in range(4):
+        assert sorted(map(str, base[r])) == sorted(map(str, eager[r]))
+
+        def peak(order):
+            live = best = 0
+            for a in order:
+                if a.type == T.F:
+                    live += 1
+                    best = max(best, live)
+                elif a.type == T.B:
+                    live -= 1
+            return best
+        assert peak(eager[r]) == peak(base[r]) + (1 if r < 3 else 0)
+    assert simulate(eager, 4).makespan <= simulate(base, 4).makespan

@@ -319,3 +319,31 @@ def test_token_file_data_gives_next_token_targets(tmp_path):
     assert RunConfig(lr=1.0, lr_warmup_steps=4).lr_at(1) == 0.5
     c = RunConfig(lr=1.0, lr_warmup_steps=0, lr_decay_steps=10, lr_min_ratio=0.1)
     assert c.lr_at(0) == 1.0 and abs(c.lr_at(10) - 0.1) < 1e-9 and abs(c.lr_at(5) - 0.55) < 1e-9
+
+
+def test_partition_units_parts_and_auto_rule():
+    """Unit-granular cuts: part names, which parameters a part keeps, measured costs steering the cut positions, and the
+    'auto' rule (sub-layer cuts only when they lower the most expensive stage by more than 2 %)."""
+    import copy
+    args = ModelArgs(dim=32, n_layers=6, n_heads=4, vocab_size=50, ffn_dim=64, dropout=0.0)
+    assert Pn.layer_units(args) == ("self", "cross", "ffn")
+    assert Pn.layer_units(ModelArgs(dim=32, n_layers=2, n_heads=4, cross_attn=False, norm_first=True, causal=True)) == ("attn", "ffn")
+    assert Pn.part_name(0, 3, ("self", "cross", "ffn")) == "full" and Pn.part_name(0, 2, ("self", "cross", "ffn")) == "attn"
+    assert Pn.part_name(1, 3, ("self", "cross", "ffn")) == "cross+ffn" and Pn.part_units("cross+ffn", ("self", "cross", "ffn")) == ("cross", "ffn")
+    full = Transformer(args)
+    layer = copy.deepcopy(full.layers["0"])
+    Pn._apply_part(layer, "cross+ffn")
+    kept = {n.split(".")[0] for n, _ in layer.named_parameters()}
+    assert kept == {"multihead_attn", "norm2", "linear1", "linear2", "norm3"}
+    try:
+        Pn.set_measured_costs(args, 16, {"self": 1.0, "cross": 1.0, "ffn": 1.0, "head": 2.0, "embed": 0.0})
+        assert Pn.unit_costs(args, 16)["source"] == "measured"
+        costs = Pn._stage_costs(6, 4, "fine", args, 16)
+        assert max(costs) == 5.0 and abs(sum(costs) - 20.0) < 1e-9          # 18 units + head 2 over 4 stages: 5 each
+        assert Pn.resolve_rule("auto", 6, 4, args, 16) == "fine"            # whole layers: max 6 (two layers) vs 5 with cuts
+        Pn.set_measured_costs(args, 16, {"self": 1.0, "cross": 1.0, "ffn": 1.0, "head": 0.0, "embed": 0.0})
+        assert Pn.resolve_rule("auto", 6, 3, args, 16) == "balanced"        # 2 layers per stage is already perfect
+        assert Pn.resolve_rule("auto", 6, 4, args, 16, tp=2) == "balanced"  # tensor-parallel stages keep whole layers
+    finally:
+        Pn.clear_measured_costs()
+    assert Pn.unit_costs(args, 16)["source"] == "model"
