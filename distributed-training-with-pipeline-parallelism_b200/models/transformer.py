@@ -106,12 +106,54 @@ class GradSink:
         self._g: Dict[int, torch.Tensor] = {}
         self.fused_ar = None   # ops.collective.FusedGradAllReduce while the stage's LAST backward runs
         self.deferred: Optional[list] = None   # a list while an input-gradient-only pass (IR action I) runs
+        # Weight-gradient work on a SIDE stream: nothing downstream of a backward needs dW / db before the optimizer, so the
+        # wgrad GEMMs and bias column sums of a fused backward are forked off the input-gradient chain.  The persistent
+        # kernels of the two streams cannot share an SM, but whenever the chain's kernel leaves SMs idle (the last partial
+        # wave of an attention / GEMM launch) the side stream's CTAs fill them.  Works inside CUDA-graph capture (the fork
+        # and the join become graph edges).  Operands are kept alive until the join.
+        self.side_stream = None   # set by the stage (ops.functional.side_stream(device)); None = everything on one stream
+        self._side_live: list = []
+        self._side_prev = None
+
+    def _on_side(self) -> bool:
+        return self.side_stream is not None and self.fused_ar is None and self.deferred is None
+
+    def _fork(self):
+        ev = torch.cuda.Event()
+        ev.record()
+        self.side_stream.wait_event(ev)
+        return torch.cuda.stream(self.side_stream)
+
+    def side_layer_done(self) -> None:
+        """End of a layer's backward: the main stream waits for the side work of the PREVIOUS layer (one layer of lag keeps
+        the fork busy across the layer boundary) and drops the operands that work was reading."""
+        if self.side_stream is None or not self._side_live:
+            return
+        ev = torch.cuda.Event()
+        ev.record(self.side_stream)
+        if self._side_prev is not None:
+            torch.cuda.current_stream().wait_event(self._side_prev[0])
+        self._side_prev = (ev, self._side_live)
+        self._side_live = []
+
+    def side_join(self) -> None:
+        """End of a stage backward: everything forked so far is complete before the caller goes on (and before a graph
+        capture ends)."""
+        if self.side_stream is None:
+            return
+        if self._side_live or self._side_prev is not None:
+            torch.cuda.current_stream().wait_stream(self.side_stream)
+        self._side_live, self._side_prev = [], None
 
     def wgrad(self, dy: torch.Tensor, x: torch.Tensor, gw: torch.Tensor, gb: Optional[torch.Tensor]) -> None:
         """gw += dy^T x, gb += colsum(dy): now (action B) or recorded for the matching W action (torch's
         stage_backward_input / stage_backward_weight split, _backward.py:165/:283)."""
         if self.deferred is not None:
             self.deferred.append(("linear", dy, x, gw, gb))
+        elif self._on_side() and dy.is_cuda:
+            self._side_live.append((dy, x))
+            with self._fork():
+                F.linear_wgrad(dy, x, gw, gb)
         else:
             F.linear_wgrad(dy, x, gw, gb, ar=self.fused_ar)
 
@@ -119,6 +161,10 @@ class GradSink:
         """gb += colsum(dy) for a bias whose weight gradient is computed elsewhere (tensor-parallel row-parallel layers)."""
         if self.deferred is not None:
             self.deferred.append(("bias", dy, None, None, gb))
+        elif self._on_side() and dy.is_cuda:
+            self._side_live.append((dy,))
+            with self._fork():
+                F.colsum_accum(dy, gb)
         else:
             F.colsum_accum(dy, gb)
 
@@ -291,13 +337,18 @@ def _postln_self_forward(L: DecoderLayer, layer_id: int, x0: torch.Tensor, ctx: 
     return x1
 
 
-def _postln_cross_forward(L: DecoderLayer, layer_id: int, x1: torch.Tensor, x0: torch.Tensor, ctx: Ctx, st: dict) -> torch.Tensor:
-    """Cross-attention over the layer input (memory = x0)."""
+def _postln_cross_forward(L: DecoderLayer, layer_id: int, x1: torch.Tensor, x0: torch.Tensor, ctx: Ctx, st: dict,
+                          kv2: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Cross-attention over the layer input (memory = x0).  ``kv2``: the K/V projection when the caller already forked it
+    onto the side stream (joined here)."""
     a, d, H, p = ctx.args, ctx.args.dim, ctx.args.n_heads, ctx.p
     rms, eps = a.norm == "rmsnorm", a.layer_norm_eps
     W, bvec = L.multihead_attn.in_proj_weight, L.multihead_attn.in_proj_bias
     q2 = F.linear_fwd(x1, W[:d], bvec[:d])
-    kv2 = F.linear_fwd(x0, W[d:], bvec[d:])
+    if kv2 is None:
+        kv2 = F.linear_fwd(x0, W[d:], bvec[d:])
+    else:
+        F.join(x0.device)
     o2, lse2 = F.attention_fwd(q2, kv2[:, :d], kv2[:, d:], ctx.B, H, False, None, p, ctx.seed(layer_id, SITE_ATTN2))
     a2 = F.linear_fwd(o2, L.multihead_attn.out_proj.weight, L.multihead_attn.out_proj.bias)
     z2, x2, mean2, rstd2 = F.add_dropout_norm_fwd(x1, a2, L.norm2.weight, L.norm2.bias, eps, p,
@@ -321,6 +372,8 @@ def layer_forward(L: DecoderLayer, layer_id: int, x_in: torch.Tensor, ctx: Ctx, 
     units = _PARTS[part] if a.cross_attn else tuple(u for u in _PARTS[part] if u != "cross")
     T = ctx.B * ctx.S if ctx.tp is None else x_in.shape[0]
     h = x_in
+    # (forking the cross-attention K/V projection onto the side stream in FORWARD was measured and dropped: 8.08 -> 8.17 ms
+    #  per micro-batch -- the forward chain has no long partial waves for it to fill, it only delays the chain's CTAs)
     if "self" in units:
         h = _postln_self_forward(L, layer_id, x_in, ctx, st, packed_out=(a.cross_attn and units[-1] == "self"))
         if units[-1] == "self":
@@ -491,12 +544,14 @@ def stage_backward(model: "Transformer", douts: Sequence[torch.Tensor], ctx: Ctx
         dys = [dz]
     for name in reversed(list(model.layers.keys())):
         dys = layer_backward(model.layers[name], int(name), dys, ctx, st["layers"][name], G)
+        G.side_layer_done()
     if model.tok_embeddings is not None:
         G.embedding_wgrad(st["tokens"].reshape(-1), dys, G(model.tok_embeddings.weight))
+        G.side_join()
         return None
-    if not need_input_grad:
-        return None
-    return F.add_n(dys)
+    out = F.add_n(dys) if need_input_grad else None
+    G.side_join()
+    return out
 
 
 # ------------------------------------------------------------------------------------------------------------

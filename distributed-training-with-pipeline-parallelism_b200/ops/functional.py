@@ -42,6 +42,57 @@ def pad8(n: int) -> int:
 
 
 # ------------------------------------------------------------------------------------------------------------
+# side stream: independent branches of the stage program (weight gradients, the cross-attention K/V projection) are
+# forked off the critical chain so that their CTAs fill the SMs the chain's kernels leave idle in their last partial wave
+# (persistent tcgen05 kernels hold a whole SM, so two launches overlap exactly where one of them runs out of tiles).
+# Fork and join are event edges, which CUDA-graph capture records as graph dependencies.  PPB_SIDE_STREAM=0 turns it off.
+# ------------------------------------------------------------------------------------------------------------
+_side_streams: dict = {}
+SIDE_STREAM = __import__("os").environ.get("PPB_SIDE_STREAM", "1") != "0"
+
+
+def side_stream(device: torch.device):
+    """The per-device side stream (None on CPU or when disabled)."""
+    if not SIDE_STREAM or device.type != "cuda":
+        return None
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    st = _side_streams.get(key)
+    if st is None:
+        st = _side_streams[key] = torch.cuda.Stream(device)
+    return st
+
+
+class fork:
+    """``with fork(device) as on_side:`` -- work issued inside runs on the side stream, ordered after everything issued so
+    far on the current stream (no-op context when there is no side stream).  ``join(device)`` orders the current stream
+    after everything forked so far."""
+
+    def __init__(self, device: torch.device):
+        self.side = side_stream(device)
+        self.ctx = None
+
+    def __enter__(self):
+        if self.side is not None:
+            ev = torch.cuda.Event()
+            ev.record()
+            self.side.wait_event(ev)
+            self.ctx = torch.cuda.stream(self.side)
+            self.ctx.__enter__()
+        return self.side is not None
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
+
+
+def join(device: torch.device) -> None:
+    st = side_stream(device)
+    if st is not None:
+        torch.cuda.current_stream().wait_stream(st)
+
+
+# ------------------------------------------------------------------------------------------------------------
 # GEMM family
 # ------------------------------------------------------------------------------------------------------------
 def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, a_mn: bool, b_mn: bool,

@@ -92,6 +92,8 @@ class PipelineStage:
         self.exp_avg = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(max(total, 8), dtype=torch.float32, device=dev)
         self.sink = GradSink()
+        if dev.type == "cuda" and self.tp_size == 1:
+            self.sink.side_stream = F.side_stream(dev)   # weight-gradient work forked off the input-gradient chain
         self.param_names = []
         self.tp_replicated: List[tuple] = []   # (offset, numel) of parameters every tp rank holds in full
         with torch.no_grad():
