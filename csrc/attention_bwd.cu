@@ -70,7 +70,8 @@ __global__ void __launch_bounds__(AttnBwdCfg<DQK, DV>::THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                 const __grid_constant__ CUtensorMap tmDQacc, const __grid_constant__ CUtensorMap tmDK,
-                const __grid_constant__ CUtensorMap tmDV, const AttnBwdParams p) {
+                const __grid_constant__ CUtensorMap tmDV, const __grid_constant__ CUtensorMap tmDQ32,
+                const AttnBwdParams p) {
   using Cfg = AttnBwdCfg<DQK, DV>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
@@ -248,6 +249,47 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // dQ tile of iteration it_prev: TMEM -> fp32 staging -> TMA reduce-add into the accumulator
       mbar_wait(dq_full, it_prev & 1);
       tc_fence_after();
+      if constexpr (!Cfg::ALIAS_STG) {
+        // Warp-local drain (dedicated staging): every warp owns the 32 rows x (DQK/2) columns it reads from TMEM, stages
+        // them in its own 4 KB slices and issues its own TMA reduce-add (32-row boxes), so no CTA-wide barrier sits between
+        // the eight compute warps in the steady state.
+        if (lane == 0) tma_wait_group_read<0>();   // this warp's previous reduce has read its slices
+        __syncwarp();
+#pragma unroll
+        for (int c = 0; c < DQK / 64; ++c) {
+          uint32_t r[32];
+          tmem_ld_x32(t_dq + c * 32, r);
+          tmem_ld_wait();
+          const int chunk = hf * (DQK / 64) + c;
+          const uint32_t dst_row = stg_smem + chunk * Cfg::CHUNK + row * 128;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((q ^ (row & 7)) << 4)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 1]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 2]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 3]) * p.scale))
+                         : "memory");
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(dq_empty);
+          const int qrow = (i_start + it_prev) * 128 + (warp & 3) * 32;
+          if (qrow < p.Sq) {
+#pragma unroll
+            for (int c = 0; c < DQK / 64; ++c) {
+              const int chunk = hf * (DQK / 64) + c;
+              if (chunk * 32 < p.dh)
+                tma_reduce_add_4d(&tmDQ32, stg_smem + chunk * Cfg::CHUNK + (warp & 3) * 4096, chunk * 32, h, qrow, b);
+            }
+          }
+          tma_commit_group();
+        }
+        return;
+      }
       if (warp == 0 && lane == 0) tma_wait_group_read<0>();  // previous reduce has finished reading the staging
       named_bar_sync(1, 256);
 #pragma unroll
@@ -282,12 +324,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (Cfg::ALIAS_STG) named_bar_sync(1, 256);  // staging aliases the P/dS tiles that are written next
     };
 
+    // lse / delta of the NEXT query tile are fetched while the current one is processed (two dependent global loads per
+    // tile would otherwise sit at the head of every iteration)
+    const long long lbase = ((long long)(b * p.H + h)) * p.Sq;
+    float lse_nxt = p.lse[lbase + min(i_start * 128 + row, p.Sq - 1)];
+    float dlt_nxt = p.delta[lbase + min(i_start * 128 + row, p.Sq - 1)];
     for (int it = 0; it < n_it; ++it) {
       const int q_idx = (i_start + it) * 128 + row;
       const bool row_ok = q_idx < p.Sq;
-      const long long lidx = ((long long)(b * p.H + h)) * p.Sq + min(q_idx, p.Sq - 1);
-      const float lse2 = p.lse[lidx] * LOG2E;
-      const float dlt = p.delta[lidx];
+      const float lse2 = lse_nxt * LOG2E;
+      const float dlt = dlt_nxt;
+      if (it + 1 < n_it) {
+        const long long nidx = lbase + min(q_idx + 128, p.Sq - 1);
+        lse_nxt = p.lse[nidx];
+        dlt_nxt = p.delta[nidx];
+      }
       const int causal_lim = q_idx + off;
       constexpr bool PIPELINED = !(Cfg::ALIAS_DQ || STAGES < 2);   // must match the MMA issuer's ordering
       if (!PIPELINED && it > 0) drain_dq(it - 1);
@@ -371,7 +422,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // ---- dV, dK: TMEM -> bf16 -> swizzled staging (the P / dS tiles are free now) -> TMA store ----
     mbar_wait(fin_full, 0);
     tc_fence_after();
-    if (warp == 0 && lane == 0) tma_wait_group_read<0>();
+    if (lane == 0) tma_wait_group_read<0>();   // (every warp issued its own dQ reduces)
     named_bar_sync(1, 256);
     auto stage_out = [&](uint32_t tcol, int ncols, uint32_t dst_base, float sc) {
       // this thread owns columns [hf*ncols/2, (hf+1)*ncols/2) of its kv row
@@ -465,13 +516,13 @@ __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const float* __res
 
 template <int DQK, int DV>
 static int launch_attn_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
-                           const CUtensorMap& tdq, const CUtensorMap& tdk, const CUtensorMap& tdv, const AttnBwdParams& p,
-                           cudaStream_t stream) {
+                           const CUtensorMap& tdq, const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq32,
+                           const AttnBwdParams& p, cudaStream_t stream) {
   using Cfg = AttnBwdCfg<DQK, DV>;
   auto kfn = attn_bwd_kernel<DQK, DV>;
   PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   const int kv_tiles = (p.Skv + 127) / 128;
-  kfn<<<p.B * p.H * kv_tiles, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdq, tdk, tdv, p);
+  kfn<<<p.B * p.H * kv_tiles, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p);
   PPB_CUDA_OK(cudaGetLastError());
   return 0;
 }
@@ -523,7 +574,7 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
     PPB_CUDA_OK(cudaGetLastError());
   }
 
-  CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv;
+  CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv, tdq32;
   if (!make_head_tmap(&tq, q, dh, H, Sq, B, ldq, 128) || !make_head_tmap(&tk, k, dh, H, Skv, B, ldk, 128) ||
       !make_head_tmap(&tv, v, dh, H, Skv, B, ldv, 128) || !make_head_tmap(&tdo, dO, dh, H, Sq, B, ldo, 128) ||
       !make_head_tmap(&tdk, dk, dh, H, Skv, B, ldk, 128) || !make_head_tmap(&tdv, dv, dh, H, Skv, B, ldv, 128))
@@ -533,6 +584,8 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
     uint64_t strides[3] = {(uint64_t)dh * 4, (uint64_t)D * 4, (uint64_t)Sq * (uint64_t)D * 4};
     uint32_t box[4] = {32, 1, 128, 1};
     if (!make_tmap(&tdq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -3;
+    uint32_t box32[4] = {32, 1, 32, 1};   // one warp's 32 query rows
+    if (!make_tmap(&tdq32, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, strides, box32, CU_TENSOR_MAP_SWIZZLE_128B)) return -3;
   }
   AttnBwdParams p;
   p.B = B;
@@ -549,8 +602,8 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;
   p.delta = delta;
-  int rc = (dh <= 64) ? launch_attn_bwd<64, 64>(tq, tk, tv, tdo, tdq, tdk, tdv, p, stream)
-                      : launch_attn_bwd<128, 128>(tq, tk, tv, tdo, tdq, tdk, tdv, p, stream);
+  int rc = (dh <= 64) ? launch_attn_bwd<64, 64>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream)
+                      : launch_attn_bwd<128, 128>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
   if (rc) return rc;
   {
     const long long n8 = (long long)B * Sq * (D / 8);
