@@ -116,10 +116,16 @@ def bench_bandwidth(rows):
     print(rows[-1], flush=True)
 
 
-def bench_attention(rows):
+ATTN_SHAPES = [(4, 16, 1024, 64, False, 0.0), (4, 16, 1024, 64, False, 0.1), (4, 16, 1024, 64, True, 0.0),
+               (2, 32, 2048, 128, True, 0.0), (8, 8, 128, 96, False, 0.1)]
+# head dim 192 = the 4-head rows of the reference grid (dim 768; one micro-batch there is 8 x 128 tokens); run once as is and
+# once with PPB_ATTN_TC_MAX_DH=128 (CUDA-core path) for the A/B
+ATTN_WIDE_SHAPES = [(8, 4, 128, 192, False, 0.1), (4, 4, 1024, 192, False, 0.1), (4, 4, 1024, 192, True, 0.0)]
+
+
+def bench_attention(rows, shapes=ATTN_SHAPES):
     hbm, tf, tag = peaks()
-    for (B, H, S, dh, causal, p) in [(4, 16, 1024, 64, False, 0.0), (4, 16, 1024, 64, False, 0.1), (4, 16, 1024, 64, True, 0.0),
-                                     (2, 32, 2048, 128, True, 0.0), (8, 8, 128, 96, False, 0.1)]:
+    for (B, H, S, dh, causal, p) in shapes:
         D = H * dh
         qkv = torch.randn(B * S, 3 * D, device="cuda", dtype=torch.bfloat16)
         q, k, v = qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:]
@@ -149,11 +155,13 @@ if __name__ == "__main__":
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "kernel_bench.json"))
     a = ap.parse_args()
     rows = []
-    if "gemm" in a.what:
+    if "gemm" in a.what.split(","):
         bench_gemm(rows)
-    if "bw" in a.what:
+    if "bw" in a.what.split(","):
         bench_bandwidth(rows)
-    if "attn" in a.what:
+    if "attn" in a.what.split(","):
         bench_attention(rows)
+    if "attnwide" in a.what.split(","):
+        bench_attention(rows, ATTN_WIDE_SHAPES)
     os.makedirs(os.path.dirname(a.out), exist_ok=True)
     json.dump(rows, open(a.out, "w"), indent=1)

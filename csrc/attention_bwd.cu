@@ -15,6 +15,13 @@
 //   3. finish : dQ accumulator fp32 -> bf16 in the layout of q.
 // dK / dV stay in TMEM for the whole CTA lifetime and are written once with TMA stores.
 //
+// Head dims 129..192 (the reference grid's 4-head rows: 768 / 4): S | dP | dV | dK would need 640 TMEM columns and all
+// seven tiles 256 KB of shared memory, so the main step runs as TWO specialisations of the same kernel (PART):
+//   PART 1: S -> P, dV += P^T dO                 (no V, no dP, no dS: 176 KB, 448 columns)
+//   PART 2: S, dP -> dS, dK += dS^T Q, dQ = dS K (no P tile; dQ re-uses the S | dP columns and leaves through the dS
+//           tile in three 64-column passes: 224 KB, 448 columns)
+// Both recompute S (six tile GEMMs instead of five); dV / dK leave through the Q stage, which is free by then.
+//
 // Replaces the autograd backward of aten.bmm x2 + _softmax_backward_data + dropout backward
 //  for the reference's attention blocks (/root/reference/LLMsDistributedTrainingHelper.py:40-44).
 #include "common.cuh"
@@ -24,6 +31,7 @@
 namespace ppb {
 
 bool make_head_tmap(CUtensorMap* tm, const void* ptr, int dh, int H, int S, int B, long long ld, int box_rows);
+int attn_tc_max_head_dim();
 
 struct AttnBwdParams {
   int B, H, Sq, Skv, dh;
@@ -38,23 +46,29 @@ struct AttnBwdParams {
   const float* delta;  // [B, H, Sq]
 };
 
-template <int DQK, int DV>
+template <int DQK, int DV, int PART>
 struct AttnBwdCfg {
   static constexpr int NQK = DQK / 64, NV = DV / 64;
   static constexpr int CHUNK = 128 * 128;  // bytes of a [128 rows x 128 B] swizzled chunk
-  static constexpr int K_BYTES = NQK * CHUNK, V_BYTES = NV * CHUNK;
+  static constexpr bool WIDE = (DQK > 128) || (DV > 128);
+  static constexpr bool HAS_P = PART != 2;    // P tile (dV) wanted
+  static constexpr bool HAS_DS = PART != 1;   // dP, dS tile (dK, dQ) wanted; V is only read for dP
+  static_assert(WIDE == (PART != 0), "wide heads run as PART 1 + PART 2, the others as one kernel");
+  static constexpr int K_BYTES = NQK * CHUNK, V_BYTES = HAS_DS ? NV * CHUNK : 0;
   static constexpr int Q_BYTES = NQK * CHUNK, DO_BYTES = NV * CHUNK;
-  static constexpr int PD_BYTES = 2 * CHUNK, DS_BYTES = 2 * CHUNK;
+  static constexpr int PD_BYTES = HAS_P ? 2 * CHUNK : 0, DS_BYTES = HAS_DS ? 2 * CHUNK : 0;
   static constexpr int STG_BYTES = (DQK / 32) * CHUNK;  // fp32 dQ staging: DQK/32 chunks of [128 x 32 fp32]
   static constexpr bool BIG = (DQK > 64) || (DV > 64);
   static constexpr int STAGES = BIG ? 1 : 2;
   static constexpr bool ALIAS_STG = BIG;  // big heads: the dQ staging re-uses the P/dS tiles
   static constexpr int SMEM_BYTES =
       K_BYTES + V_BYTES + STAGES * (Q_BYTES + DO_BYTES) + PD_BYTES + DS_BYTES + (ALIAS_STG ? 0 : STG_BYTES) + 512 + 1024;
-  // TMEM columns: S | dP | dV | dK | dQ  (dQ aliases dP when the budget would exceed 512)
-  static constexpr int S_COL = 0, DP_COL = 128, DV_COL = 256, DK_COL = 256 + DV;
-  static constexpr bool ALIAS_DQ = (256 + DV + DQK + DQK) > 512;
-  static constexpr int DQ_COL = ALIAS_DQ ? DP_COL : (256 + DV + DQK);
+  static_assert(SMEM_BYTES <= 232448, "shared memory budget of one CTA");
+  // TMEM columns: S | dP | dV | dK | dQ  (dQ aliases dP -- or, 192 wide, S | dP -- when the budget would exceed 512)
+  static constexpr int S_COL = 0, DP_COL = 128, DV_COL = 256, DK_COL = (PART == 2) ? 256 : 256 + DV;
+  static constexpr bool ALIAS_DQ = WIDE || (256 + DV + DQK + DQK) > 512;
+  static constexpr int DQ_COL = ALIAS_DQ ? (DQK > 128 ? S_COL : DP_COL) : (256 + DV + DQK);
+  static_assert((!HAS_DS || DK_COL + DQK <= 512) && (!HAS_P || DV_COL + DV <= 512) && (!ALIAS_DQ || DQ_COL + DQK <= 256), "TMEM budget");
   static constexpr int TMEM_COLS = 512;
   static constexpr int THREADS = 10 * 32;
 };
@@ -65,15 +79,16 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
-template <int DQK, int DV>
-__global__ void __launch_bounds__(AttnBwdCfg<DQK, DV>::THREADS, 1)
+template <int DQK, int DV, int PART>
+__global__ void __launch_bounds__(AttnBwdCfg<DQK, DV, PART>::THREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                 const __grid_constant__ CUtensorMap tmDQacc, const __grid_constant__ CUtensorMap tmDK,
                 const __grid_constant__ CUtensorMap tmDV, const __grid_constant__ CUtensorMap tmDQ32,
                 const AttnBwdParams p) {
-  using Cfg = AttnBwdCfg<DQK, DV>;
+  using Cfg = AttnBwdCfg<DQK, DV, PART>;
   constexpr int STAGES = Cfg::STAGES;
+  constexpr bool HAS_P = Cfg::HAS_P, HAS_DS = Cfg::HAS_DS;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -139,7 +154,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     if (lane == 0) {
       mbar_expect_tx(kv_full, Cfg::K_BYTES + Cfg::V_BYTES);
       for (int c = 0; c < Cfg::NQK; ++c) tma_load_4d(k_smem + c * Cfg::CHUNK, &tmK, kv_full, c * 64, h, kv0, b);
-      for (int c = 0; c < Cfg::NV; ++c) tma_load_4d(v_smem + c * Cfg::CHUNK, &tmV, kv_full, c * 64, h, kv0, b);
+      if constexpr (HAS_DS)
+        for (int c = 0; c < Cfg::NV; ++c) tma_load_4d(v_smem + c * Cfg::CHUNK, &tmV, kv_full, c * 64, h, kv0, b);
       for (int it = 0; it < n_it; ++it) {
         const int st = it % STAGES;
         const int qrow = (i_start + it) * 128;
@@ -167,11 +183,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           umma_f16_ss(tmem_base + Cfg::S_COL, make_smem_desc_sw128(qa + o, 16, 1024),
                       make_smem_desc_sw128(k_smem + o, 16, 1024), id_s, kk > 0 ? 1u : 0u);
         }
+        if constexpr (HAS_DS) {
 #pragma unroll
-        for (int kk = 0; kk < DV / 16; ++kk) {
-          const uint32_t o = (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32;
-          umma_f16_ss(tmem_base + Cfg::DP_COL, make_smem_desc_sw128(da + o, 16, 1024),
-                      make_smem_desc_sw128(v_smem + o, 16, 1024), id_s, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < DV / 16; ++kk) {
+            const uint32_t o = (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32;
+            umma_f16_ss(tmem_base + Cfg::DP_COL, make_smem_desc_sw128(da + o, 16, 1024),
+                        make_smem_desc_sw128(v_smem + o, 16, 1024), id_s, kk > 0 ? 1u : 0u);
+          }
         }
         umma_commit(sdp_full);
       };
@@ -179,21 +197,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const int st = it % STAGES;
         const uint32_t qa = q_smem + st * Cfg::Q_BYTES;
         const uint32_t da = do_smem + st * Cfg::DO_BYTES;
+        if constexpr (HAS_P) {
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // K = 128 query rows; A: P tile MN-major (M = kv), B: dO tile MN-major (N = dv)
-          umma_f16_ss(tmem_base + Cfg::DV_COL, make_smem_desc_sw128(pd_smem + kk * 2048, Cfg::CHUNK, 1024),
-                      make_smem_desc_sw128(da + kk * 2048, Cfg::CHUNK, 1024), id_dv, (it > 0 || kk > 0) ? 1u : 0u);
+          for (int kk = 0; kk < 8; ++kk) {  // K = 128 query rows; A: P tile MN-major (M = kv), B: dO tile MN-major (N = dv)
+            umma_f16_ss(tmem_base + Cfg::DV_COL, make_smem_desc_sw128(pd_smem + kk * 2048, Cfg::CHUNK, 1024),
+                        make_smem_desc_sw128(da + kk * 2048, Cfg::CHUNK, 1024), id_dv, (it > 0 || kk > 0) ? 1u : 0u);
+          }
         }
+        if constexpr (HAS_DS) {
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // A: dS tile MN-major, B: Q tile MN-major (N = dqk)
-          umma_f16_ss(tmem_base + Cfg::DK_COL, make_smem_desc_sw128(ds_smem + kk * 2048, Cfg::CHUNK, 1024),
-                      make_smem_desc_sw128(qa + kk * 2048, Cfg::CHUNK, 1024), id_dk, (it > 0 || kk > 0) ? 1u : 0u);
-        }
+          for (int kk = 0; kk < 8; ++kk) {  // A: dS tile MN-major, B: Q tile MN-major (N = dqk)
+            umma_f16_ss(tmem_base + Cfg::DK_COL, make_smem_desc_sw128(ds_smem + kk * 2048, Cfg::CHUNK, 1024),
+                        make_smem_desc_sw128(qa + kk * 2048, Cfg::CHUNK, 1024), id_dk, (it > 0 || kk > 0) ? 1u : 0u);
+          }
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // K = 128 kv rows; A: dS tile K-major (M = q), B: K tile MN-major (N = dqk)
-          umma_f16_ss(tmem_base + Cfg::DQ_COL,
-                      make_smem_desc_sw128(ds_smem + (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32, 16, 1024),
-                      make_smem_desc_sw128(k_smem + kk * 2048, Cfg::CHUNK, 1024), id_dq, kk > 0 ? 1u : 0u);
+          for (int kk = 0; kk < 8; ++kk) {  // K = 128 kv rows; A: dS tile K-major (M = q), B: K tile MN-major (N = dqk)
+            umma_f16_ss(tmem_base + Cfg::DQ_COL,
+                        make_smem_desc_sw128(ds_smem + (kk >> 2) * Cfg::CHUNK + (kk & 3) * 32, 16, 1024),
+                        make_smem_desc_sw128(k_smem + kk * 2048, Cfg::CHUNK, 1024), id_dq, kk > 0 ? 1u : 0u);
+          }
         }
         umma_commit(dq_full);
         umma_commit(qdo_empty(st));
@@ -249,6 +271,49 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // dQ tile of iteration it_prev: TMEM -> fp32 staging -> TMA reduce-add into the accumulator
       mbar_wait(dq_full, it_prev & 1);
       tc_fence_after();
+      if constexpr (!HAS_DS) {   // PART 1 has no dQ: the barrier pair only says "the dV GEMM has read the P tile"
+        __syncwarp();
+        if (lane == 0) mbar_arrive(dq_empty);
+        return;
+      }
+      if constexpr (DQK > 128) {
+        // 192 columns of dQ through the 32 KB dS tile (free: its readers, the GEMMs of this tile, are done), 64 columns
+        // per pass: thread (row, hf) stages columns [64 * pass + 32 * hf, + 32) into chunk hf
+        const int qrow = (i_start + it_prev) * 128;
+#pragma unroll 1
+        for (int pass = 0; pass < DQK / 64; ++pass) {
+          if (warp == 0 && lane == 0) tma_wait_group_read<0>();   // the previous reduce has read the staging
+          named_bar_sync(1, 256);
+          uint32_t r[32];
+          tmem_ld_x32(tmem_base + lane_off + Cfg::DQ_COL + pass * 64 + hf * 32, r);
+          tmem_ld_wait();
+          const uint32_t dst_row = stg_smem + hf * Cfg::CHUNK + row * 128;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((q ^ (row & 7)) << 4)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 1]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 2]) * p.scale)),
+                         "r"(__float_as_uint(__uint_as_float(r[4 * q + 3]) * p.scale))
+                         : "memory");
+          }
+          if (pass == DQK / 64 - 1) {   // last read of the dQ columns: the next tile's S / dP may overwrite them
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dq_empty);
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, 256);
+          if (warp == 0 && lane == 0) {
+            for (int c = 0; c < 2; ++c)
+              if (pass * 64 + c * 32 < p.dh) tma_reduce_add_4d(&tmDQacc, stg_smem + c * Cfg::CHUNK, pass * 64 + c * 32, h, qrow, b);
+            tma_commit_group();
+          }
+        }
+        if (warp == 0 && lane == 0) tma_wait_group_read<0>();
+        named_bar_sync(1, 256);   // the staging is the dS tile that is written next
+        return;
+      }
       if constexpr (!Cfg::ALIAS_STG) {
         // Warp-local drain (dedicated staging): every warp owns the 32 rows x (DQK/2) columns it reads from TMEM, stages
         // them in its own 4 KB slices and issues its own TMA reduce-add (32-row boxes), so no CTA-wide barrier sits between
@@ -350,8 +415,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t rs[64], rd[64];
       tmem_ld_x32(t_s, rs);
       tmem_ld_x32(t_s + 32, rs + 32);
-      tmem_ld_x32(t_dp, rd);
-      tmem_ld_x32(t_dp + 32, rd + 32);
+      if constexpr (HAS_DS) {
+        tmem_ld_x32(t_dp, rd);
+        tmem_ld_x32(t_dp + 32, rd + 32);
+      }
       tmem_ld_wait();
       if (PIPELINED) {   // S/dP may be overwritten by the next tile's GEMMs while we do the math below
         tc_fence_before();
@@ -383,12 +450,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const float k0 = (hsh.a >= p.drop_thresh) ? p.drop_scale : 0.f;
             const float k1 = (hsh.b >= p.drop_thresh) ? p.drop_scale : 0.f;
             const int e = c * 32 + i;
-            dsv[e] = pv[e] * fmaf(dsv[e], k0, -dlt);        // softmax scale is applied when dQ / dK leave TMEM
-            dsv[e + 1] = pv[e + 1] * fmaf(dsv[e + 1], k1, -dlt);
+            if constexpr (HAS_DS) {
+              dsv[e] = pv[e] * fmaf(dsv[e], k0, -dlt);        // softmax scale is applied when dQ / dK leave TMEM
+              dsv[e + 1] = pv[e + 1] * fmaf(dsv[e + 1], k1, -dlt);
+            }
             pv[e] *= k0;
             pv[e + 1] *= k1;
           }
-        } else {
+        } else if constexpr (HAS_DS) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) dsv[c * 32 + i] = pv[c * 32 + i] * (dsv[c * 32 + i] - dlt);
         }
@@ -401,14 +470,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         const uint32_t sw = (((uint32_t)q) ^ (row & 7)) << 4;
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + sw), "r"(pack_bf16(pv[8 * q], pv[8 * q + 1])),
-                     "r"(pack_bf16(pv[8 * q + 2], pv[8 * q + 3])), "r"(pack_bf16(pv[8 * q + 4], pv[8 * q + 5])),
-                     "r"(pack_bf16(pv[8 * q + 6], pv[8 * q + 7]))
-                     : "memory");
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + sw), "r"(pack_bf16(dsv[8 * q], dsv[8 * q + 1])),
-                     "r"(pack_bf16(dsv[8 * q + 2], dsv[8 * q + 3])), "r"(pack_bf16(dsv[8 * q + 4], dsv[8 * q + 5])),
-                     "r"(pack_bf16(dsv[8 * q + 6], dsv[8 * q + 7]))
-                     : "memory");
+        if constexpr (HAS_P)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(prow + sw), "r"(pack_bf16(pv[8 * q], pv[8 * q + 1])),
+                       "r"(pack_bf16(pv[8 * q + 2], pv[8 * q + 3])), "r"(pack_bf16(pv[8 * q + 4], pv[8 * q + 5])),
+                       "r"(pack_bf16(pv[8 * q + 6], pv[8 * q + 7]))
+                       : "memory");
+        if constexpr (HAS_DS)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(drow + sw), "r"(pack_bf16(dsv[8 * q], dsv[8 * q + 1])),
+                       "r"(pack_bf16(dsv[8 * q + 2], dsv[8 * q + 3])), "r"(pack_bf16(dsv[8 * q + 4], dsv[8 * q + 5])),
+                       "r"(pack_bf16(dsv[8 * q + 6], dsv[8 * q + 7]))
+                       : "memory");
       }
       tc_fence_before();
       fence_proxy_async_smem();
@@ -445,15 +516,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       }
     };
-    stage_out(Cfg::DV_COL, DV, pd_smem, 1.f);
-    stage_out(Cfg::DK_COL, DQK, ds_smem, p.scale);
+    // wide heads (three 16 KB chunks per output) leave through the Q stage: every GEMM that read it has completed
+    const uint32_t dv_out = Cfg::WIDE ? q_smem : pd_smem, dk_out = Cfg::WIDE ? q_smem : ds_smem;
+    if constexpr (HAS_P) stage_out(Cfg::DV_COL, DV, dv_out, 1.f);
+    if constexpr (HAS_DS) stage_out(Cfg::DK_COL, DQK, dk_out, p.scale);
     fence_proxy_async_smem();
     named_bar_sync(1, 256);
     if (warp == 0 && lane == 0) {
-      for (int c = 0; c < Cfg::NV; ++c)
-        if (c * 64 < p.dh) tma_store_4d(&tmDV, pd_smem + c * Cfg::CHUNK, c * 64, h, kv0, b);
-      for (int c = 0; c < Cfg::NQK; ++c)
-        if (c * 64 < p.dh) tma_store_4d(&tmDK, ds_smem + c * Cfg::CHUNK, c * 64, h, kv0, b);
+      if constexpr (HAS_P)
+        for (int c = 0; c < Cfg::NV; ++c)
+          if (c * 64 < p.dh) tma_store_4d(&tmDV, dv_out + c * Cfg::CHUNK, c * 64, h, kv0, b);
+      if constexpr (HAS_DS)
+        for (int c = 0; c < Cfg::NQK; ++c)
+          if (c * 64 < p.dh) tma_store_4d(&tmDK, dk_out + c * Cfg::CHUNK, c * 64, h, kv0, b);
       tma_commit_group();
       tma_wait_group<0>();
     }
@@ -514,12 +589,12 @@ __global__ void __launch_bounds__(256) attn_bwd_finish_kernel(const float* __res
   }
 }
 
-template <int DQK, int DV>
+template <int DQK, int DV, int PART>
 static int launch_attn_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                            const CUtensorMap& tdq, const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq32,
                            const AttnBwdParams& p, cudaStream_t stream) {
-  using Cfg = AttnBwdCfg<DQK, DV>;
-  auto kfn = attn_bwd_kernel<DQK, DV>;
+  using Cfg = AttnBwdCfg<DQK, DV, PART>;
+  auto kfn = attn_bwd_kernel<DQK, DV, PART>;
   PPB_CUDA_OK(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
   const int kv_tiles = (p.Skv + 127) / 128;
   kfn<<<p.B * p.H * kv_tiles, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p);
@@ -536,7 +611,8 @@ int attn_bwd_generic(const void* q, const void* k, const void* v, const void* o,
 
 using namespace ppb;
 
-// `S` = max(Sq, Skv).  tcgen05 path: delta + fp32 dQ accumulator; generic path (dh > 128): fp32 dK and dV accumulators.
+// `S` = max(Sq, Skv).  tcgen05 path: delta + fp32 dQ accumulator; generic path: fp32 dK and dV accumulators (sized for
+// either path when dh > 128, so the switch below never changes a caller's buffer).
 extern "C" long long ppb_attn_bwd_scratch_bytes(int B, int H, int S, int dh) {
   const long long delta = ((long long)B * H * S * 4 + 255) / 256 * 256;
   return delta + (long long)B * S * H * dh * 4 * (dh > 128 ? 2 : 1) + 256;
@@ -557,7 +633,7 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   PPB_REQUIRE(!causal || Skv >= Sq, "ppb_attn_bwd: causal attention needs Skv >= Sq");
   PPB_REQUIRE(dropout_p <= 0.f || (Skv % 2) == 0, "ppb_attn_bwd: dropout needs an even Skv");
   PPB_REQUIRE(scratch != nullptr && (reinterpret_cast<uintptr_t>(scratch) % 256) == 0, "ppb_attn_bwd: scratch must be 256-byte aligned");
-  if (dh > 128)
+  if (dh > attn_tc_max_head_dim())   // CUDA-core path (attention_generic.cu)
     return attn_bwd_generic(q, k, v, o, dO, lse, dq, dk, dv, scratch, B, H, Sq, Skv, dh, ldq, ldk, ldv, ldo, causal, scale,
                             dropout_p, seed, stream);
   float* delta = reinterpret_cast<float*>(scratch);
@@ -602,8 +678,15 @@ extern "C" int ppb_attn_bwd(const void* q, const void* k, const void* v, const v
   p.drop_scale = dropout_p < 1.f ? 1.f / (1.f - dropout_p) : 0.f;
   p.lse = lse;
   p.delta = delta;
-  int rc = (dh <= 64) ? launch_attn_bwd<64, 64>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream)
-                      : launch_attn_bwd<128, 128>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
+  int rc;
+  if (dh <= 64) {
+    rc = launch_attn_bwd<64, 64, 0>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
+  } else if (dh <= 128) {
+    rc = launch_attn_bwd<128, 128, 0>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
+  } else {   // 129..192: dV, then dK + dQ (see the header comment)
+    rc = launch_attn_bwd<192, 192, 1>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
+    if (rc == 0) rc = launch_attn_bwd<192, 192, 2>(tq, tk, tv, tdo, tdq, tdk, tdv, tdq32, p, stream);
+  }
   if (rc) return rc;
   {
     const long long n8 = (long long)B * Sq * (D / 8);

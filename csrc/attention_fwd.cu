@@ -13,11 +13,16 @@
 //     works on one query tile while the other one is in its exp2 phase.
 // Inputs are column-sliced views of the packed QKV activation ([tokens, 3*d]); heads are addressed through 4-D
 // TMA tensor maps (dh, head, seq, batch), so no split/transposes/.contiguous() copies exist.  Head dims that are
-// not multiples of 64 (96, 192 in the reference sweep) are zero-padded by TMA out-of-bounds fill.
+// not multiples of 64 (96 in the reference sweep) are zero-padded by TMA out-of-bounds fill.  Head dims 129..192 (the
+// sweep's 4-head rows, 768 / 4) run one query tile per CTA with TWO threads per query row (96 output columns each,
+// so the fp32 accumulator still lives in registers), single-stage K / V tiles of three 64-column chunks, 320 TMEM
+// columns; O leaves through the Q tile (three chunks), which is dead after the last Q K^T.
 //
 // Replaces aten.bmm x2 + mul.Scalar + _safe_softmax + dropout of the reference's attention blocks
 // (self- and cross-attention of nn.TransformerDecoderLayer,
 // /root/reference/LLMsDistributedTrainingHelper.py:40-44, :52).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "host_common.h"
 #include "ppb200.h"
@@ -37,6 +42,7 @@ struct AttnParams {
 
 template <int DQK, int DV, int MT, int SPLIT>
 struct AttnFwdCfg {
+  static_assert(DV <= 128 || (MT == 1 && SPLIT == 2 && DQK >= DV), "wide heads: one query tile, two threads per row, O staged in Q");
   static constexpr int NQK = DQK / 64, NV = DV / 64;
   static constexpr int CHUNK_BYTES = 128 * 128;  // 128 rows x 64 bf16 (one 128B-swizzled column chunk)
   static constexpr int Q_BYTES = NQK * CHUNK_BYTES;
@@ -354,11 +360,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float inv_l = (l_run > 0.f ? 1.f / l_run : 0.f) * (p.drop_thresh ? p.drop_scale : 1.f);
     if (half == 0 && q_idx < p.Sq)
       p.lse[((long long)(b * p.H + h)) * p.Sq + q_idx] = (m_run + log2f(l_run)) * 0.6931471805599453f;
-    // stage O (bf16) through the (now free) P region of this query tile: NV chunks of [128 rows x 128 B]
+    // stage O (bf16) through the (now free) P region of this query tile: NV chunks of [128 rows x 128 B]; three chunks
+    // do not fit there, they go through the Q tile (every Q K^T of this CTA has completed: its last S was consumed)
+    const uint32_t o_stage = (Cfg::NV > 2) ? q_smem + t * Cfg::Q_BYTES : p_smem + t * Cfg::P_BYTES;
 #pragma unroll
     for (int g = 0; g < OD / 8; ++g) {
       const int col = half * OD + g * 8;
-      const uint32_t dst = p_smem + t * Cfg::P_BYTES + (col >> 6) * Cfg::CHUNK_BYTES + row * 128 +
+      const uint32_t dst = o_stage + (col >> 6) * Cfg::CHUNK_BYTES + row * 128 +
                            (((uint32_t)((col & 63) >> 3) ^ (row & 7)) << 4);
       const float* sp = &o[g * 8];
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pack_bf16(sp[0] * inv_l, sp[1] * inv_l)),
@@ -370,7 +378,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     named_bar_sync(1 + t, 128 * SPLIT);
     if (wl == 0 && lane == 0 && q0 + t * 128 < p.Sq) {
       for (int c = 0; c < DV / 64; ++c)
-        if (c * 64 < p.dh) tma_store_4d(&tmO, p_smem + t * Cfg::P_BYTES + c * Cfg::CHUNK_BYTES, c * 64, h, q0 + t * 128, b);
+        if (c * 64 < p.dh) tma_store_4d(&tmO, o_stage + c * Cfg::CHUNK_BYTES, c * 64, h, q0 + t * 128, b);
       tma_commit_group();
       tma_wait_group<0>();
     }
@@ -400,6 +408,17 @@ static int launch_attn_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const C
   return 0;
 }
 
+// Largest head dim that takes the tcgen05 kernels (forward and backward); larger ones (up to 256) run on CUDA cores.
+// PPB_ATTN_TC_MAX_DH=128 sends 129..192 back to the CUDA-core path (A/B measurements).
+int attn_tc_max_head_dim() {
+  static const int v = [] {
+    const char* e = getenv("PPB_ATTN_TC_MAX_DH");
+    const int x = e ? atoi(e) : 192;
+    return x >= 192 ? 192 : 128;
+  }();
+  return v;
+}
+
 int attn_fwd_generic(const void* q, const void* k, const void* v, void* o, float* lse, int B, int H, int Sq, int Skv,
                      int dh, long long ldq, long long ldk, long long ldv, long long ldo, int causal, float scale,
                      float dropout_p, unsigned long long seed, cudaStream_t stream);
@@ -420,7 +439,7 @@ extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o
   PPB_REQUIRE((ldq % 8) == 0 && (ldk % 8) == 0 && (ldv % 8) == 0 && (ldo % 8) == 0, "ppb_attn_fwd: row strides must be multiples of 8");
   PPB_REQUIRE(!causal || Skv >= Sq, "ppb_attn_fwd: causal attention needs Skv >= Sq");
   PPB_REQUIRE(dropout_p <= 0.f || (Skv % 2) == 0, "ppb_attn_fwd: dropout needs an even Skv");
-  if (dh > 128)  // CUDA-core fallback (attention_generic.cu); the tcgen05 path covers head dims up to 128
+  if (dh > attn_tc_max_head_dim())  // CUDA-core fallback (attention_generic.cu); the tcgen05 path covers head dims up to 192
     return attn_fwd_generic(q, k, v, o, lse, B, H, Sq, Skv, dh, ldq, ldk, ldv, ldo, causal, scale, dropout_p, seed, stream);
   CUtensorMap tq, tk, tv, to;
   if (!make_head_tmap(&tq, q, dh, H, Sq, B, ldq, 128) || !make_head_tmap(&tk, k, dh, H, Skv, B, ldk, 128) ||
@@ -443,6 +462,7 @@ extern "C" int ppb_attn_fwd(const void* q, const void* k, const void* v, void* o
   // SPLIT (threads per query row) = 1: measured on B200 (B=4,H=16,S=1024,dh=64) two threads per row are SLOWER
   // (66.6 vs 59.4 us without dropout, 81.9 vs 73.7 us with): the softmax is bound by FMA/ALU pipe throughput, not
   // by latency, so extra warps only add the row-max exchange barrier and register spills.
+  if (dh > 128) return launch_attn_fwd<192, 192, 1, 2>(tq, tk, tv, to, p, stream);
   if (dh <= 64) return two ? launch_attn_fwd<64, 64, 2, 1>(tq, tk, tv, to, p, stream) : launch_attn_fwd<64, 64, 1, 1>(tq, tk, tv, to, p, stream);
   return two ? launch_attn_fwd<128, 128, 2, 1>(tq, tk, tv, to, p, stream) : launch_attn_fwd<128, 128, 1, 1>(tq, tk, tv, to, p, stream);
 }

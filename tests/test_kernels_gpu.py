@@ -197,9 +197,11 @@ ATTN_CASES = [
     (2, 3, 200, 200, 64, False, 0.0),
     (2, 3, 136, 328, 64, False, 0.0),
     (1, 4, 128, 128, 32, False, 0.0),
-    (2, 4, 128, 128, 192, False, 0.1),   # the reference sweep's 4-head case (CUDA-core fallback path)
+    (2, 4, 128, 128, 192, False, 0.1),   # the reference sweep's 4-head case: wide-head tcgen05 kernels (two-part backward)
     (1, 2, 96, 160, 192, False, 0.0),
-    (1, 2, 128, 128, 256, True, 0.0),
+    (1, 2, 384, 384, 192, True, 0.1),    # several query / kv tiles per head, causal, dropout
+    (1, 3, 200, 328, 160, False, 0.0),   # 129..192 zero-padded to three 64-column chunks, ragged tiles
+    (1, 2, 128, 128, 256, True, 0.0),    # CUDA-core path (head dims above 192)
 ]
 
 
