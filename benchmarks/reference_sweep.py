@@ -38,7 +38,14 @@ if a.report:
     sp = analysis.compute_speedup_and_efficiency(df)
     out = os.path.join(ROOT, "profiles")
     with open(os.path.join(out, "reference_sweep_report.md"), "w") as f:
-        f.write("# Reference experiment grid on B200 (ours)\n\n## Throughput (tokens/s)\n\n```\n" + analysis.throughput_pivot(df).round(0).to_string() +
+        note = ""
+        if "measured_in_round" in df.columns and df["measured_in_round"].nunique() > 1:
+            r2 = df[df["measured_in_round"] == 2]
+            note = ("Rows re-measured in round 2 (head dim 192 on the tcgen05 attention kernels; everything else of round 2 too): "
+                    f"{len(r2)} cells -- num_processes {sorted(r2['num_processes'].unique().tolist())}, n_heads "
+                    f"{sorted(r2['n_heads'].unique().tolist())}.  The other cells are the round-1 measurements (their 4-head rows "
+                    "still ran attention on CUDA cores).\n\n")
+        f.write("# Reference experiment grid on B200 (ours)\n\n" + note + "## Throughput (tokens/s)\n\n```\n" + analysis.throughput_pivot(df).round(0).to_string() +
                 "\n```\n\n## Speedup vs GPipe / efficiency (nb:405-435)\n\n```\n" + sp.round(4).to_string(index=False) +
                 "\n```\n\n## Measured vs theoretical bubble\n\n```\n" + analysis.bubble_table(df).round(4).to_string(index=False) + "\n```\n")
     analysis.plot_speedup_and_efficiency(sp, os.path.join(out, "reference_sweep_speedup.svg"))
