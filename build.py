@@ -149,7 +149,10 @@ LISTINGS = {
     "k12_allgather_fused_bn256": "gemm_tcgen05_agfused_kernelILi256ELb0EE",
     "k12_allgather_fused_pair_bn256": "gemm_tcgen05_agfused_pair_kernelILi256ELb0EE",
     "attn_fwd_dh64": "attn_fwd_kernelILi64ELi64ELi2ELi1EE",
-    "attn_bwd_dh64": "attn_bwd_kernelILi64ELi64EE",
+    "attn_bwd_dh64": "attn_bwd_kernelILi64ELi64ELi0EE",
+    "attn_fwd_dh192": "attn_fwd_kernelILi192ELi192ELi1ELi2EE",
+    "attn_bwd_dh192_dv": "attn_bwd_kernelILi192ELi192ELi1EE",
+    "attn_bwd_dh192_dk_dq": "attn_bwd_kernelILi192ELi192ELi2EE",
     "ln_bwd_d1024": "ln_bwd_kernelILi128EE",
     "ln_fwd_d1024": "ln_fwd_kernelILi4EE",
     "xent": "xent_fwd_bwd_kernelILb1EE",
