@@ -411,24 +411,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_after();
       const unsigned long long drop_row = ((unsigned long long)(b * p.H + h) * p.Sq + (unsigned long long)min(q_idx, p.Sq - 1)) *
                                           (unsigned long long)p.Skv;
-      // this thread's 64 columns of S and dP, pulled into registers in one go
+      // this thread's 64 columns of S and dP in two 32-column halves: the second half is in flight (TMEM reads are
+      // bandwidth-bound, all compute warps ask at the same moment) while the arithmetic of the first one runs
       uint32_t rs[64], rd[64];
       tmem_ld_x32(t_s, rs);
-      tmem_ld_x32(t_s + 32, rs + 32);
-      if constexpr (HAS_DS) {
-        tmem_ld_x32(t_dp, rd);
-        tmem_ld_x32(t_dp + 32, rd + 32);
-      }
+      if constexpr (HAS_DS) tmem_ld_x32(t_dp, rd);
       tmem_ld_wait();
-      if (PIPELINED) {   // S/dP may be overwritten by the next tile's GEMMs while we do the math below
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(sdp_empty);
-      }
+      tmem_ld_x32(t_s + 32, rs + 32);
+      if constexpr (HAS_DS) tmem_ld_x32(t_dp + 32, rd + 32);
       float* pv = reinterpret_cast<float*>(rs);    // P (then dropped-out P) in place of S
       float* dsv = reinterpret_cast<float*>(rd);   // dS in place of dP
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
+        if (c == 1) {
+          tmem_ld_wait();
+          if (PIPELINED) {   // S/dP may be overwritten by the next tile's GEMMs while we do the rest of the math
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(sdp_empty);
+          }
+        }
         const int kvb = kv0 + hf * 64 + c * 32;
         const bool need_mask = !row_ok || (kvb + 32 > p.Skv) || (p.causal && (kvb + 31 > causal_lim));
 #pragma unroll

@@ -56,6 +56,12 @@ struct AttnFwdCfg {
   static constexpr int TMEM_COLS = TMEM_NEED <= 128 ? 128 : (TMEM_NEED <= 256 ? 256 : 512);
   static constexpr int SWARPS = 4 * MT * SPLIT;   // softmax warps: SPLIT threads share one query row (column halves)
   static constexpr int THREADS = (SWARPS + 2) * 32;
+  // RESIDENT (head dims up to 64, one thread per row): O stays in TMEM for the whole kv loop (every P V accumulates onto
+  // it) and the row's 128 scores are read from TMEM ONCE and kept in registers for both the max and the exp2 pass.  TMEM
+  // reads (64 B/clk per SM) are this kernel's scarcest resource: scores twice + the P V read-back were 160 KB per tile,
+  // now 64 KB.  The exponent reference of a row only moves when the running maximum grew by more than 8 (factor 256, safe
+  // in bf16 / fp32), so the in-TMEM rescale (tcgen05.ld, multiply, tcgen05.st) runs on the first tiles only.
+  static constexpr bool RESIDENT = (SPLIT == 1 && DQK == 64 && DV == 64);
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -180,16 +186,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (j + 1 < n_kv) mbar_wait(k_full((j + 1) % STAGES), ((j + 1) / STAGES) & 1);
         for (int t = 0; t < MT; ++t) {
           mbar_wait(p_full(t), j & 1);
-          mbar_wait(pv_empty(t), (j & 1) ^ 1);
+          if constexpr (!Cfg::RESIDENT) mbar_wait(pv_empty(t), (j & 1) ^ 1);
           tc_fence_after();
           const uint32_t pa = p_smem + t * Cfg::P_BYTES;
           const uint32_t vb = v_smem + st * Cfg::V_BYTES;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t acc = (kk > 0 || (Cfg::RESIDENT && j > 0)) ? 1u : 0u;   // RESIDENT: O accumulates over all kv tiles
             umma_f16_ss(pv_tmem(t), make_smem_desc_sw128(pa + (kk >> 2) * Cfg::CHUNK_BYTES + (kk & 3) * 32, 16, 1024),
-                        make_smem_desc_sw128(vb + kk * 2048, Cfg::CHUNK_BYTES, 1024), idesc_pv, kk > 0 ? 1u : 0u);
+                        make_smem_desc_sw128(vb + kk * 2048, Cfg::CHUNK_BYTES, 1024), idesc_pv, acc);
           }
-          umma_commit(pv_full(t));
+          // RESIDENT: pv_full is a one-shot "O of this query tile is final" barrier
+          if (!Cfg::RESIDENT || j == n_kv - 1) umma_commit(pv_full(t));
           if (t == MT - 1) umma_commit(v_empty(st));
           if (j + 1 < n_kv) {
             mbar_wait(s_empty(t), j & 1);
@@ -223,6 +231,103 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t s_cols = s_tmem(t) + lane_off + half * COLS;
     const uint32_t pv_cols = pv_tmem(t) + lane_off + half * OD;
 
+    if constexpr (Cfg::RESIDENT) {
+      float m_ref = -INFINITY;   // exponent reference of this row (log2 domain): a lagging upper-ish bound of the running maximum
+      for (int j = 0; j < n_kv; ++j) {
+        mbar_wait(s_full(t), j & 1);
+        tc_fence_after();
+        uint32_t sc[128];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld_x32(s_cols + c * 32, sc + c * 32);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_empty(t));   // S_t may be overwritten by the next Q K^T
+        const int kv0 = j * 128;
+        if ((kv0 + 128 > p.Skv) || (p.causal && (kv0 + 127 > causal_lim))) {   // sequence tail / causal diagonal
+#pragma unroll
+          for (int i = 0; i < 128; ++i) {
+            const int kv = kv0 + i;
+            if (!((kv < p.Skv) && (!p.causal || kv <= causal_lim))) sc[i] = 0xff800000u;   // exp2(-inf) == 0
+          }
+        }
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 128; i += 4) {
+          m0 = fmaxf(m0, __uint_as_float(sc[i]));
+          m1 = fmaxf(m1, __uint_as_float(sc[i + 1]));
+          m2 = fmaxf(m2, __uint_as_float(sc[i + 2]));
+          m3 = fmaxf(m3, __uint_as_float(sc[i + 3]));
+        }
+        const float mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)) * p.sl2;
+        const bool grow = mx > m_ref + 8.f;   // (first tile: m_ref == -inf)
+        const float m_new = grow ? mx : m_ref;
+        if (j > 0 && __any_sync(0xffffffffu, grow)) {
+          // move the reference: O row *= 2^(m_ref - m_new) in TMEM.  P V of tile j-1 has completed: S of tile j, which this
+          // thread has just read, was issued after it and tcgen05 operations of one thread complete in order.
+          const float alpha = grow ? fast_exp2(m_ref - m_new) : 1.f;
+          tc_fence_after();
+#pragma unroll
+          for (int c = 0; c < OD / 16; ++c) {
+            uint32_t r[16];
+            tmem_ld_x16(pv_cols + c * 16, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st_x16(pv_cols + c * 16, r);
+          }
+          tmem_st_wait();
+          l_run *= alpha;
+        }
+        m_ref = m_new;
+        const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+        // ---- probabilities (in place of the scores) -> bf16 P tile in swizzled smem ----
+        float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float* pr = reinterpret_cast<float*>(sc + c * 32);
+#pragma unroll
+          for (int i = 0; i < 32; i += 4) {
+            pr[i] = fast_exp2(fmaf(pr[i], p.sl2, -m_use));
+            pr[i + 1] = fast_exp2(fmaf(pr[i + 1], p.sl2, -m_use));
+            pr[i + 2] = fast_exp2(fmaf(pr[i + 2], p.sl2, -m_use));
+            pr[i + 3] = fast_exp2(fmaf(pr[i + 3], p.sl2, -m_use));
+            ls0 += pr[i];
+            ls1 += pr[i + 1];
+            ls2 += pr[i + 2];
+            ls3 += pr[i + 3];
+          }
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pk[i] = pack_bf16(pr[2 * i], pr[2 * i + 1]);
+          if (p.drop_thresh) {   // mask convention: see the two-pass loop below
+            const DropoutStream ds(seed_eff, (drop_row + (unsigned long long)(kv0 + c * 32)) >> 1);
+            if (ds.nowrap(16)) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) pk[i] &= drop_pair_mask(ds.word_nowrap(i), p.drop_thresh);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) pk[i] &= drop_pair_mask(ds.word(i), p.drop_thresh);
+            }
+          }
+          const uint32_t atom = p_row + (c >> 1) * Cfg::CHUNK_BYTES;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t cc = (c & 1) * 4 + q;
+            const uint32_t dst = atom + ((cc ^ (row & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(pk[4 * q]), "r"(pk[4 * q + 1]),
+                         "r"(pk[4 * q + 2]), "r"(pk[4 * q + 3])
+                         : "memory");
+          }
+        }
+        l_run += (ls0 + ls1) + (ls2 + ls3);
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full(t));   // P_t is visible to the tensor core, the O row carries the current reference
+      }
+      m_run = m_ref;
+    } else
     for (int j = 0; j < n_kv; ++j) {
       mbar_wait(s_full(t), j & 1);
       tc_fence_after();
@@ -341,8 +446,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         mbar_arrive(p_full(t));   // P_t is visible to the tensor core
       }
     }
-    // ---- last P*V, normalise, store ----
-    mbar_wait(pv_full(t), (n_kv - 1) & 1);
+    // ---- last P*V (RESIDENT: the one-shot "O is final" phase), normalise, store ----
+    mbar_wait(pv_full(t), Cfg::RESIDENT ? 0 : ((n_kv - 1) & 1));
     tc_fence_after();
 #pragma unroll
     for (int c = 0; c < OD / 32; ++c) {
