@@ -57,6 +57,8 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-fused-check", action="store_true",
                     help="skip the K10/K11/K12 parity + roofline check that multi-GPU runs append (ranks 0-1, after the timed regions)")
+    ap.add_argument("--fused-check-timeout", type=float, default=150.0,
+                    help="seconds the appended K10/K11/K12 check may take before the line is printed without it")
     ap.add_argument("--trace", default=None, help="write a chrome trace of the measured timeline here")
     ap.add_argument("--small", action="store_true", help="tiny config for smoke tests")
     return ap.parse_args()
@@ -222,21 +224,6 @@ def run_ours(a, rank, local_rank, world):
             write_chrome_trace(evs, a.trace)
     peak_mem = max_over_ranks(torch.cuda.max_memory_allocated(dev) / 2**30, dev)
     loss_t = torch.tensor([loss_val if loss_val is not None else -1.0], dtype=torch.float64, device=dev)
-    # The fused compute+collective kernels (K10 wgrad+all-reduce, K11 GEMM->reduce-scatter, K12 all-gather->GEMM) are not
-    # on the pipeline-only headline path, so every multi-GPU run appends their parity + roofline check over the real
-    # NVLink peers (ranks 0 and 1, outside every timed region): the evidence travels with the driver's own records.
-    fused_paths = None
-    if world > 1 and not a.no_fused_check and not a.small:
-        pair = dist.new_group([0, 1])
-        if rank < 2:
-            try:
-                from ppb200.utils import fused_check
-                # (the NVLS multimem variant and the degree-4 run live in benchmarks/fused_paths_bench.py -> profiles/: inside
-                # a larger world the sub-group multicast set-up stalled once, and this check must never cost the bench line)
-                fused_paths = fused_check.run(pair, dev, nvls=False)
-            except Exception as e:  # noqa: BLE001
-                fused_paths = {"error": f"{type(e).__name__}: {e}"[:300]}
-        dist.barrier()
     summ = {k: round(v, 3) for k, v in sched.summary().items()}
     summ["layers"] = [[f"{k}:{getattr(l, 'part', 'full')}" if getattr(l, 'part', 'full') != 'full' else k
                        for k, l in st.submod.layers.items()] for st in stages]
@@ -245,11 +232,12 @@ def run_ours(a, rank, local_rank, world):
         dist.all_reduce(loss_t, op=dist.ReduceOp.MAX)
         per_rank = [None] * world
         dist.all_gather_object(per_rank, summ)
-    if rank == 0:
+    result = None
+    if rank == 0:   # the whole line is assembled BEFORE the appended check below: nothing that follows can cost it
         tokens = a.global_batch * S
         ms_step = ms_total / a.steps
         par = f"pp{P}" + (f"xdp{a.dp}" if a.dp > 1 else "") + (f"xtp{a.tp}" if a.tp > 1 else "") + (f"xv{v}" if v > 1 else "")
-        emit({
+        result = {
             "metric": "tokens/sec (1F1B pipeline training step, max over ranks)" if a.schedule == "1F1B" else f"tokens/sec ({a.schedule})",
             "value": tokens / (ms_step / 1e3), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
@@ -266,9 +254,42 @@ def run_ours(a, rank, local_rank, world):
             "bubble_fraction_theory": sched.theory_bubble,
             "loss": float(loss_t.item()), "peak_mem_gib": peak_mem, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
             "model_tflops_per_gpu": margs.flops_per_token(S) * tokens / (ms_step / 1e3) / 1e12 / world,
-            "fused_paths": fused_paths,
+            "fused_paths": None,
             "per_rank": per_rank,
-        })
+        }
+    # The fused compute+collective kernels (K10 wgrad+all-reduce, K11 GEMM->reduce-scatter, K12 all-gather->GEMM) are not
+    # on the pipeline-only headline path, so every multi-GPU run appends their parity + roofline check over the real
+    # NVLink peers (ranks 0 and 1, outside every timed region): the evidence travels with the driver's own records.
+    # It runs under a deadline: if it has not come back in time, rank 0 prints the line it already holds (with the
+    # time-out noted under `fused_paths`) and every rank leaves, so a stalled peer can never cost the measurement.
+    if world > 1 and not a.no_fused_check and not a.small:
+        from ppb200.utils.deadline import Deadline
+
+        def on_timeout():
+            if rank == 0:
+                result["fused_paths"] = {"error": f"check did not finish within {a.fused_check_timeout:.0f} s; the headline numbers above were complete before it started"}
+                emit(result)
+            sys.stdout.flush()
+            os._exit(0)
+
+        with Deadline(a.fused_check_timeout, on_timeout) as dl:
+            pair = dist.new_group([0, 1])
+            fused_paths = None
+            if rank < 2:
+                try:
+                    from ppb200.utils import fused_check
+                    # (the NVLS multimem variant and the degree-4 run live in benchmarks/fused_paths_bench.py -> profiles/)
+                    fused_paths = fused_check.run(pair, dev, nvls=False)
+                except Exception as e:  # noqa: BLE001
+                    fused_paths = {"error": f"{type(e).__name__}: {e}"[:300]}
+            dist.barrier()
+        if not dl.completed:   # the time-out handler owns the output from here (it ends the process)
+            import time
+            time.sleep(3600)
+        if rank == 0:
+            result["fused_paths"] = fused_paths
+    if rank == 0:
+        emit(result)
     if world > 1:
         dist.barrier()
         if not getattr(a, "keep_process_group", False):

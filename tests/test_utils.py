@@ -347,3 +347,25 @@ def test_partition_units_parts_and_auto_rule():
     finally:
         Pn.clear_measured_costs()
     assert Pn.unit_costs(args, 16)["source"] == "model"
+
+
+def test_deadline_lets_a_fast_block_finish_and_fires_on_a_slow_one():
+    """bench.py bounds its appended fused-kernel check with this: exactly one side (block / handler) wins."""
+    import time
+    from ppb200.utils.deadline import Deadline
+    fired = []
+    with Deadline(5.0, lambda: fired.append("late")) as dl:
+        x = 1 + 1
+    assert dl.completed and x == 2
+    time.sleep(0.05)
+    assert fired == []
+    with Deadline(0.05, lambda: fired.append("timeout")) as dl:
+        time.sleep(0.4)
+    assert not dl.completed and fired == ["timeout"]
+    try:   # an exception inside the block disarms the watchdog and propagates
+        with Deadline(0.05, lambda: fired.append("after-exception")) as dl:
+            raise ValueError("boom")
+    except ValueError:
+        pass
+    time.sleep(0.15)
+    assert fired == ["timeout"] and dl.completed
