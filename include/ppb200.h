@@ -129,8 +129,10 @@ int ppb_norm_bwd_noalloc(const void* dy0, const void* dy1, const void* dy2, cons
  * q [B*Sq, ldq], k / v [B*Skv, ldk / ldv], o [B*Sq, ldo]: bf16 rows of H heads x dh columns (column-sliced views of a
  * packed QKV activation are fine; heads are addressed through 4-D TMA maps, nothing is transposed or copied).
  * lse [B, H, Sq] fp32 (natural log).  causal needs Skv >= Sq; dropout (probability dropout, counter-based mask from
- * (seed, element index), regenerated in backward) needs an even Skv.  dh: multiple of 8, 8..256 (tcgen05 tiles of
- * 64 / 128 / 192 / 256 columns, zero-padded by TMA).  reserved* arguments must be 0 / NULL.
+ * (seed, element index), regenerated in backward) needs an even Skv.  dh: multiple of 8, 8..256; 8..192 run on the tcgen05
+ * kernels (tiles of 64 / 128 / 192 columns, zero-padded by TMA; 129..192: two threads per query row in the forward, the
+ * backward as a dV launch and a dK + dQ launch), 193..256 on a CUDA-core path.  PPB_ATTN_TC_MAX_DH=128 in the
+ * environment sends 129..192 to the CUDA-core path as well (A/B measurements).  reserved* arguments must be 0 / NULL.
  * Backward writes dq / dk / dv with the row strides of q / k / v; `scratch` = ppb_attn_bwd_scratch_bytes(B, H,
  * max(Sq, Skv), dh) bytes, 256-byte aligned, no initialisation needed (delta rows + the fp32 dQ accumulator).
  * Replaces aten.bmm x2 + mul.Scalar + _safe_softmax + dropout and their backwards -- torch transformer.py:1158-1194,
