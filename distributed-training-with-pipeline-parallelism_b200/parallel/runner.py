@@ -73,6 +73,7 @@ class PipelineSchedule:
         self.local: Dict[int, PipelineStage] = {st.stage_index: st for st in self.stages}
         self.device = self.stages[0].device
         self.cuda = self.device.type == "cuda"
+        self.extra_warmup = 0
         if actions is not None:
             order = self._load_actions(actions, optimizer is not None)
             self.name = "custom" if schedule is None else schedule
