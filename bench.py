@@ -317,6 +317,14 @@ def run_reference(a, rank, local_rank, world):
     # what the helper cannot express is reported, not emulated: it has one block (post-LN, ReLU, FFN 2048), no data or
     # tensor parallelism (helper:178 creates an unused group) and only torch's three schedules (helper:215-220)
     why = None
+    if a.tp > 1 and a.dp == 1 and a.schedule in ("GPipe", "1F1B") and not a.model.startswith("ref-"):
+        # tensor parallelism is not in the helper (helper:178 creates a group it never uses) and its fixed block cannot be
+        # sharded: the baseline for the tensor-parallel configurations is the composition a torch user would write --
+        # a Megatron-style tensor + sequence parallel pre-LN block from torch modules (ncclAllGather / ncclReduceScatter,
+        # cuBLAS, SDPA) inside torch.distributed.pipelining, benchmarks/tp_baseline.py (parity-tested on CPU)
+        from benchmarks import tp_baseline
+        tp_baseline.run(a, rank, local_rank, world, emit, config_dict, max_over_ranks)
+        return
     if a.model not in ("ref-gpt2-medium", "ref-gpt2-xl", "ref-small"):
         why = f"the helper's Transformer cannot express model preset {a.model!r} (fixed nn.TransformerDecoderLayer block)"
     elif a.tp > 1:
