@@ -297,6 +297,32 @@ def run_ours(a, rank, local_rank, world):
 
 
 # ---------------------------------------------------------------------------------------------------------------
+def reference_stage_with_replicas(ref, model, stage_index: int, num_stages: int, dev, pp_group, dp_group):
+    """The helper's own `manual_model_split` (its partition rule and pruning, helper:60-94) for a pipeline that has
+    data-parallel replicas.  The helper builds its PipelineStage on the WORLD group (helper:93), which torch rejects as
+    soon as the world is larger than the pipeline ("group size cannot be larger than number of stages"), so for the call
+    the `PipelineStage` name inside the helper module is bound to the stock composition SURVEY.md 6.4 names: the pruned
+    module moved to its device, wrapped in DistributedDataParallel over the replica group (torch's stage runtime drives
+    `no_sync` for all but the last micro-batch), torch's PipelineStage on the pipeline group.  The file on disk is
+    untouched; tests/test_reference_arm.py runs this on CPU (gloo, 2 stages x 2 replicas)."""
+    from torch.distributed.pipelining import PipelineStage as TorchStage
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    def stage_on_pipeline_group(module, idx, n_stages, device):
+        module.to(device)
+        if any(True for _ in module.parameters()):
+            module = DDP(module, device_ids=[device.index] if device.type == "cuda" else None, process_group=dp_group,
+                         gradient_as_bucket_view=True)
+        return TorchStage(module, idx, n_stages, device, group=pp_group)
+
+    saved = ref.PipelineStage
+    ref.PipelineStage = stage_on_pipeline_group
+    try:
+        return ref.manual_model_split(model, stage_index, num_stages, dev)
+    finally:
+        ref.PipelineStage = saved
+
+
 def run_reference(a, rank, local_rank, world):
     """The unmodified helper (baseline/_ref/LLMsDistributedTrainingHelper.py) through its own public API:
     ``Transformer`` + ``manual_model_split`` + the torch.distributed.pipelining schedule classes it uses
@@ -390,16 +416,7 @@ def run_reference(a, rank, local_rank, world):
             stage = ref.manual_model_split(model, rank + world * i, num_stages, dev)
             model.to(dev)
         else:
-            # the helper's split binds the stage to the WORLD group (helper:93); with replicas the stage must live on its
-            # pipeline group, so the helper prunes the model (its partition rule, helper:60-91) and torch's own
-            # PipelineStage is rebuilt over the DDP-wrapped module
-            from torch.distributed.pipelining import PipelineStage as TorchStage
-            from torch.nn.parallel import DistributedDataParallel as DDP
-            ref.manual_model_split(model, pp_rank + pp_world * i, num_stages, dev)
-            model.to(dev)
-            has_params = any(True for _ in model.parameters())
-            mod = DDP(model, device_ids=[dev.index], process_group=dp_group, gradient_as_bucket_view=True) if has_params else model
-            stage = TorchStage(mod, pp_rank + pp_world * i, num_stages, dev, group=pp_group)
+            stage = reference_stage_with_replicas(ref, model, pp_rank + pp_world * i, num_stages, dev, pp_group, dp_group)
         stages.append(stage)
         params += list(model.parameters())
     if a.schedule == "GPipe":
