@@ -369,3 +369,32 @@ def test_deadline_lets_a_fast_block_finish_and_fires_on_a_slow_one():
         pass
     time.sleep(0.15)
     assert fired == ["timeout"] and dl.completed
+
+
+def test_min_max_partition_is_optimal_against_brute_force():
+    """The stage cutter (parallel/partition.py: _min_max_partition) against exhaustive search on random unit costs,
+    with the embedding charged to the first group and the head to the last (hypothesis-driven)."""
+    import itertools
+    from hypothesis import given, settings, strategies as st
+    from ppb200.parallel.partition import _min_max_partition
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.lists(st.floats(0.05, 3.0), min_size=2, max_size=9), st.integers(1, 5), st.floats(0.0, 2.5), st.floats(0.0, 0.5))
+    def check(costs, S, tail, head):
+        S = min(S, len(costs))
+        got = _min_max_partition(costs, S, tail, head)
+        assert got[0][0] == 0 and got[-1][1] == len(costs) and all(a < b for a, b in got)
+        assert all(got[i][1] == got[i + 1][0] for i in range(S - 1))
+
+        def worst(cuts):
+            b = [0, *cuts, len(costs)]
+            loads = [sum(costs[b[i]:b[i + 1]]) for i in range(S)]
+            loads[0] += head
+            loads[-1] += tail
+            return max(loads)
+
+        best = min(worst(c) for c in itertools.combinations(range(1, len(costs)), S - 1))
+        mine = worst([b for _, b in got[:-1]])
+        assert mine <= best * (1 + 1e-9) + 1e-12, (costs, S, tail, head, got, mine, best)
+
+    check()
