@@ -24,3 +24,20 @@ def test_reference_arm_with_data_parallel_replicas():
     assert len(res["losses"]) == 2                     # the last stage of each replica
     for h in res["losses"]:
         assert len(h) == 3 and h[-1] < h[0], res
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="baseline/_ref not installed (DESIGN.md: reference arm)")
+@pytest.mark.parametrize("sched", ["GPipe", "1F1B"])
+def test_pipeline_losses_match_the_unmodified_helper(sched):
+    """Oracle vs. reference at the PIPELINE level: same weights, same batch, two ranks."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29800 + (os.getpid() + len(sched)) % 90), os.path.join(ROOT, "tests", "_ref_oracle_worker.py"), sched]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    ranks = json.loads([l for l in r.stdout.splitlines() if l.startswith("[")][-1])
+    last = ranks[-1]
+    assert len(last["ref_losses"]) == len(last["our_losses"]) == 4
+    for a, b in zip(last["our_losses"], last["ref_losses"]):
+        assert abs(a - b) < 1e-4 * abs(b), last
+    for rk in ranks:
+        assert rk["n_grads"] > 0 and rk["grad_rel_err"] < 1e-3, rk
