@@ -44,25 +44,35 @@ def loss_fn(out, tgt):                               # helper:197-201
     return torch.nn.CrossEntropyLoss()(out.reshape(-1, V), tgt.reshape(-1))
 
 
-# ---- the helper's pipeline ----
-stage = ref.manual_model_split(ref_model, rank, world, dev)
-rs = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B}[sched_name](stage, n_microbatches=m, loss_fn=loss_fn)
+# ---- the helper's pipeline (its worker builds one pruned copy per virtual stage, helper:186-194) ----
+from torch.distributed.pipelining import ScheduleInterleaved1F1B  # noqa: E402
+v = 2 if sched_name == "Interleaved1F1B" else 1
+ref_models = [ref_model] + [copy.deepcopy(ref_model) for _ in range(v - 1)]
+ref_stages = [ref.manual_model_split(mdl, rank + world * i, world * v, dev) for i, mdl in enumerate(ref_models)]
+if v == 1:
+    rs = {"GPipe": ScheduleGPipe, "1F1B": Schedule1F1B}[sched_name](ref_stages[0], n_microbatches=m, loss_fn=loss_fn)
+else:
+    rs = ScheduleInterleaved1F1B(ref_stages, n_microbatches=m, loss_fn=loss_fn)
 ref_losses = []
 if rank == 0:
     rs.step(x)
 else:
     rs.step(target=y, losses=ref_losses)
-ref_grads = {n: p.grad.clone() for n, p in ref_model.named_parameters() if p.grad is not None}
+ref_grads = {n: p.grad.clone() for mdl in ref_models for n, p in mdl.named_parameters() if p.grad is not None}
 
 # ---- this framework, same weights ----
-ours = Transformer(ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=V, dropout=0.0))
-ours.load_state_dict(full_sd)
-st = manual_model_split(ours, rank, world, dev)
-sched = make_schedule(sched_name, st, m, None, optimizer=None)
+sts = []
+for i in range(v):
+    ours = Transformer(ModelArgs(dim=64, n_layers=4, n_heads=4, vocab_size=V, dropout=0.0))
+    ours.load_state_dict(full_sd)
+    sts.append(manual_model_split(ours, rank + world * i, world * v, dev))
+sched = make_schedule(sched_name, sts if v > 1 else sts[0], m, None, optimizer=None)
 our_losses = []
 sched.step(*((x,) if rank == 0 else ()), target=y if rank == world - 1 else None, losses=our_losses if rank == world - 1 else None)
+views = {}
+for st in sts:
+    views.update(st.grad_views())
 grad_err = 0.0
-views = st.grad_views()
 for n, gr in ref_grads.items():
     # torch's runtime scales the accumulated gradients by 1 / n_microbatches, like this runner does without an optimizer
     grad_err = max(grad_err, ((views[n] - gr).abs().max() / (gr.abs().max() + 1e-8)).item())

@@ -27,7 +27,7 @@ def test_reference_arm_with_data_parallel_replicas():
 
 
 @pytest.mark.skipif(not os.path.exists(REF), reason="baseline/_ref not installed (DESIGN.md: reference arm)")
-@pytest.mark.parametrize("sched", ["GPipe", "1F1B"])
+@pytest.mark.parametrize("sched", ["GPipe", "1F1B", "Interleaved1F1B"])
 def test_pipeline_losses_match_the_unmodified_helper(sched):
     """Oracle vs. reference at the PIPELINE level: same weights, same batch, two ranks."""
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
