@@ -114,6 +114,12 @@ def worker_process(rank, world_size, n_layers, n_heads, schedule_type, batch_siz
             dev = torch.device("cuda", rank % torch.cuda.device_count())
         else:
             dev = torch.device("cpu")
+            # One intra-op thread pool per rank, sized so that the ranks together do not oversubscribe the host.  The
+            # helper leaves torch's default (every rank spins up a pool as large as the machine, helper:150-235), which
+            # on an 8-core host makes a 2-rank step of a small model 20-30x slower than it has to be; an explicit
+            # OMP_NUM_THREADS from the user wins.
+            if "OMP_NUM_THREADS" not in os.environ:
+                torch.set_num_threads(max(1, (os.cpu_count() or 1) // world_size))
         if backend == "nccl":
             from .parallel.mesh import configure_nccl_for_pipeline
             configure_nccl_for_pipeline()

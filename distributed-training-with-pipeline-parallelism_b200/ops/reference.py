@@ -24,6 +24,16 @@ def _mix32(x: torch.Tensor) -> torch.Tensor:
     return x
 
 
+def _mix32_int(x: int) -> int:
+    x &= _M32
+    x ^= x >> 16
+    x = (x * 0x7FEB352D) & _M32
+    x ^= x >> 15
+    x = (x * 0x846CA68B) & _M32
+    x ^= x >> 16
+    return x
+
+
 def dropout_thresh13(p: float) -> int:
     t = p * 8192.0 + 0.5
     return 0 if t <= 0 else (8191 if t >= 8191 else int(t))
@@ -41,15 +51,21 @@ def dropout_keep_mask(seed: int, start: int, numel: int, p: float, device=None) 
     element takes the low 16 bits of y, the odd one the high 16 bits; 13 bits of each half are compared with the
     threshold (effective dropout probability round(p * 8192) / 8192)."""
     thr = dropout_thr_pattern(p)
-    idx = torch.arange(start, start + numel, dtype=torch.int64, device=device)
-    pair = idx >> 1
-    lo, hi = pair & _M32, (pair >> 32) & _M32
+    if numel <= 0:
+        return torch.zeros(0, dtype=torch.bool, device=device)
+    p0, p1 = start >> 1, (start + numel - 1) >> 1
+    pair = torch.arange(p0, p1 + 1, dtype=torch.int64, device=device)      # one hash per PAIR, like the kernels
     k0, k1 = seed & _M32, (seed >> 32) & _M32
-    key = k0 ^ _mix32(hi ^ ((k1 ^ 0x9E3779B9) & _M32))
-    x = ((lo + key) & _M32) * 0x9E3779B1 & _M32
+    if (p0 >> 32) == (p1 >> 32):      # the usual case: the high word of the pair index is one constant -> scalar key
+        key = k0 ^ _mix32_int(((p0 >> 32) & _M32) ^ ((k1 ^ 0x9E3779B9) & _M32))
+    else:
+        key = k0 ^ _mix32(((pair >> 32) & _M32) ^ ((k1 ^ 0x9E3779B9) & _M32))
+    x = ((((pair & _M32) + key) & _M32) * 0x9E3779B1) & _M32
     x = x ^ (x >> 15)
     y = (x * 0x85EBCA77) & _M32
-    half = torch.where((idx & 1) == 1, y >> 16, y & 0xFFFF)
+    halves = torch.stack((y & 0xFFFF, y >> 16), dim=1).reshape(-1)          # element order: even, odd, even, odd, ...
+    off = start & 1
+    half = halves[off:off + numel]
     return ((half & 0x3BFF) | 0x4000) >= thr
 
 

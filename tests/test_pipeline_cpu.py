@@ -1,6 +1,8 @@
 """Multi-process CPU (gloo) end-to-end tests: the parity oracle of SURVEY.md section 4 -- pipelined loss and
 per-parameter gradients == single-process full-model loss/gradients, for all three schedules, world sizes 2 and 4,
 virtual stages, and a (dp=2, pp=2) mesh; plus the reference-compatible experiment API."""
+import os
+
 import pytest
 
 from ppb200.parallel.launch import launch_workers
@@ -341,3 +343,16 @@ def test_tensor_parallel_reference_block_matches_single_process(world, act):
         assert r["max_rel_grad_err"] < 2e-4, r
         if "loss_err" in r:
             assert r["loss_err"] < 1e-5, r
+
+
+def test_notebook_flow_example_runs_end_to_end(tmp_path):
+    """examples/notebook_flow.py = the reference notebook's cells on this API (experiments -> tables -> figures)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "notebook_flow.py"), "--out", str(tmp_path), "--iterations", "1"],
+                       capture_output=True, text=True, timeout=900, cwd=root)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    assert "speedup vs GPipe" in r.stdout and "measured vs theoretical bubble" in r.stdout
+    for f in ("report.md", "speedup_efficiency.svg", "throughput.svg", os.path.join("figures", "1f1b.svg")):
+        assert os.path.getsize(os.path.join(tmp_path, f)) > 200, f
