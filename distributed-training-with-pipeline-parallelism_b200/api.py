@@ -95,7 +95,7 @@ def worker_process(rank, world_size, n_layers, n_heads, schedule_type, batch_siz
                    n_microbatches: int = 4, master_port: Optional[int] = None, master_addr: str = "127.0.0.1",
                    dim: int = 768, vocab_size: int = 10000, dropout: float = 0.1, optimizer: Optional[dict] = None,
                    seed: Optional[int] = None, virtual_stages: Optional[int] = None, model_kwargs: Optional[dict] = None,
-                   warmup: int = 2, all_ranks_report: bool = False):
+                   warmup: int = 2, all_ranks_report: bool = False, collective_timeout_s: Optional[float] = None):
     """Individual worker process for distributed training (same positional signature as helper:150-151).
 
     Keyword-only extras expose what the helper hard-codes: backend ('gloo' on CPU, 'nccl' on CUDA), device,
@@ -123,7 +123,11 @@ def worker_process(rank, world_size, n_layers, n_heads, schedule_type, batch_siz
         if backend == "nccl":
             from .parallel.mesh import configure_nccl_for_pipeline
             configure_nccl_for_pipeline()
-        dist.init_process_group(backend=backend, rank=rank, world_size=world_size)
+        pg_kw = {}
+        if collective_timeout_s:   # a peer that never shows up raises here instead of blocking forever (helper: no timeout)
+            from datetime import timedelta
+            pg_kw["timeout"] = timedelta(seconds=float(collective_timeout_s))
+        dist.init_process_group(backend=backend, rank=rank, world_size=world_size, **pg_kw)
 
         # virtual-stage rule of helper:181-185 (silent fallback to one chunk per rank)
         stages_per_w = 1

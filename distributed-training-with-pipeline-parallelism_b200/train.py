@@ -81,7 +81,11 @@ def main(argv: Optional[List[str]] = None) -> dict:
         os.environ.setdefault("MASTER_ADDR", cfg.master_addr)
         if cfg.master_port:
             os.environ.setdefault("MASTER_PORT", str(cfg.master_port))
-        dist.init_process_group(backend, rank=rank, world_size=world)
+        kw = {}
+        if cfg.collective_timeout_s:   # dead-peer detection: the reference blocks forever in recv (nb:324-325)
+            from datetime import timedelta
+            kw["timeout"] = timedelta(seconds=float(cfg.collective_timeout_s))
+        dist.init_process_group(backend, rank=rank, world_size=world, **kw)
         own_pg = True
     if world > 1:
         mesh = init_mesh(dp_size=cfg.dp, pp_size=cfg.pp, tp_size=cfg.tp)

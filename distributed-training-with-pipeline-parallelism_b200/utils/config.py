@@ -39,6 +39,7 @@ class RunConfig:
     seed: int = 0
     master_addr: str = "127.0.0.1"
     master_port: Optional[int] = None
+    collective_timeout_s: Optional[float] = None   # a collective / P2P that waits longer aborts the rank (dead-peer detection; torch default 10-30 min)
     trace_path: Optional[str] = None      # chrome trace of the measured timeline
     metrics_path: Optional[str] = None    # JSONL
     recompute: bool = False               # activation recomputation (memory for one extra forward per micro-batch)

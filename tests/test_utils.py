@@ -398,3 +398,36 @@ def test_min_max_partition_is_optimal_against_brute_force():
         assert mine <= best * (1 + 1e-9) + 1e-12, (costs, S, tail, head, got, mine, best)
 
     check()
+
+
+def _dead_peer(rank, world, q, master_port=None):
+    """Rank 1 joins the group and then never sends: rank 0's receive must give up after the configured time."""
+    import datetime
+    import os
+    import time
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(master_port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world, timeout=datetime.timedelta(seconds=3))
+    if rank == 1:
+        time.sleep(60)
+        return
+    try:
+        dist.recv(torch.zeros(4), src=1)
+        q.put({"error": "the receive returned although nothing was sent"})
+    except Exception as e:  # noqa: BLE001  (same error-dict contract as the workers, helper:231-235)
+        q.put({"error": f"peer lost: {type(e).__name__}"})
+
+
+def test_collective_timeout_turns_a_dead_peer_into_an_error_dict():
+    """the reference blocks forever when a rank dies (no timeout anywhere).  With `collective_timeout_s`
+    (RunConfig / worker_process / `ppb200.train --collective-timeout-s`) the survivor raises, the worker reports the
+    error dict and the launcher tears the rest down."""
+    import time
+    from ppb200.parallel.launch import launch_workers
+    from ppb200.utils.config import RunConfig
+    assert RunConfig.from_args(["--collective-timeout-s", "7.5"]).collective_timeout_s == 7.5
+    t0 = time.time()
+    res = launch_workers(_dead_peer, 2, (), timeout=120)
+    assert "error" in res and res["error"].startswith("peer lost"), res
+    assert time.time() - t0 < 45
