@@ -289,3 +289,16 @@ def test_eager_1f1b_extra_warmup_is_valid_and_keeps_more_in_flight():
             return best
         assert peak(eager[r]) == peak(base[r]) + (1 if r < 3 else 0)
     assert simulate(eager, 4).makespan <= simulate(base, 4).makespan
+
+
+def test_simulator_predicts_the_round2_sweep_out_of_sample():
+    """benchmarks/predict_sweep_r2.py --check: per-token cost factors calibrated on the measured 2-rank cells, every
+    measured 4- and 8-rank cell (GPipe / 1F1B / Interleaved x micro-batch counts, B200) predicted within 10 %."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "benchmarks", "predict_sweep_r2.py"), "--check"],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    assert "out of sample" in r.stdout
