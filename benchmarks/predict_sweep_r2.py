@@ -22,7 +22,9 @@ SEQ, GLOBAL_BATCH = 1024, 128
 set_measured_costs(ARGS, SEQ, {"self": 0.3726, "cross": 0.378, "ffn": 0.1882, "head": 1.3209, "embed": 0.0284})
 
 def costs_for(n: int, eff: float) -> UnitCosts:
-    return UnitCosts(layer_f=0.319 * eff, layer_b=0.627 * eff, head_f=0.62 * eff, head_b=0.78 * eff, optim=0.095 * ARGS.n_layers / n + 0.15)
+    # (token_factor switched off: this script calibrates the per-token factor itself, `eff`)
+    return UnitCosts(layer_f=0.319 * eff, layer_b=0.627 * eff, head_f=0.62 * eff, head_b=0.78 * eff, optim=0.095 * ARGS.n_layers / n + 0.15,
+                     token_factor=((1, 1.0), (1 << 30, 1.0)))
 
 
 def cells_of(n: int):

@@ -31,6 +31,23 @@ class UnitCosts:
     i_frac: float = 0.78          # input-gradient share of a backward
     w_frac: float = 0.23
     attn_share: float = 0.8       # share of a layer's cost in its attention sub-blocks (rule 'fine')
+    # Per-token cost relative to a 4096-token micro-batch: kernels are not linear in the micro-batch size (launch / prologue
+    # costs, wave quantisation of the attention grid).  Calibrated on the measured 2-rank cells of the round-2 sweep and
+    # validated out of sample on the 4- and 8-rank cells (profiles/schedule_sweep_predicted_r2.md); log-linear in between.
+    token_factor: tuple = ((2048, 1.33), (4096, 1.0), (8192, 0.875), (16384, 0.83))
+
+    def per_token(self, tokens: float) -> float:
+        import math
+        pts = self.token_factor
+        if tokens <= pts[0][0]:
+            return pts[0][1] * (pts[0][0] / max(tokens, 1.0)) ** 0.4      # smaller still: fixed costs take over
+        if tokens >= pts[-1][0]:
+            return pts[-1][1]
+        for (t0, f0), (t1, f1) in zip(pts, pts[1:]):
+            if t0 <= tokens <= t1:
+                w = (math.log(tokens) - math.log(t0)) / (math.log(t1) - math.log(t0))
+                return f0 + w * (f1 - f0)
+        return 1.0
 
     @staticmethod
     def from_model(args: ModelArgs, seq_len: int, ref: Optional["UnitCosts"] = None) -> "UnitCosts":
@@ -50,7 +67,7 @@ class UnitCosts:
         blocks = 2 if args.cross_attn else 1
         attn = blocks * 8 * args.dim ** 2 / 0.40 + blocks * 4 * seq_len * args.dim * (0.5 if args.causal else 1.0) / 0.20
         return UnitCosts(ref.layer_f * kl, ref.layer_b * kl, ref.head_f * kh, ref.head_b * kh, ref.optim, ref.i_frac,
-                         ref.w_frac, attn / layer(args, seq_len))
+                         ref.w_frac, attn / layer(args, seq_len), ref.token_factor)
 
 
 def predict(args: ModelArgs, pp: int, schedule: str, n_microbatches: int, global_batch: int, seq_len: int,
@@ -67,7 +84,8 @@ def predict(args: ModelArgs, pp: int, schedule: str, n_microbatches: int, global
         for _, part in stage_layer_parts(args.n_layers, S, s, rule, args, seq_len):
             w += sum(uc[u] for u in part_units(part, units)) / layer_total
         weights.append(w)
-    scale = (global_batch / n_microbatches) * seq_len / 4096.0
+    tokens = (global_batch / n_microbatches) * seq_len
+    scale = tokens / 4096.0 * c.per_token(tokens)
 
     def cost(a) -> float:
         f = weights[a.stage] * c.layer_f + (c.head_f if a.stage == S - 1 else 0.0)
